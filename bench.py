@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py — training characters/sec of the char-RNN step on N B200s (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c3] [--impl reference]
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over one batch:
+embedding gather -> L recurrent layers -> projection/softmax/xent -> BPTT -> (all-reduce)
+-> clip + Adam, i.e. the reference's `sess.run([cost, final_state, train_op])`, train.py:199.
+
+  value     chars/s with the id matrices already resident in HBM (device-timed, CUDA events)
+  e2e       the same through Model.step() with HOST id buffers: pinned H2D of x,y and a D2H
+            read of the loss every step (what train.py's loop does)
+  roofline  the dominant phase of the step, timed live with CUDA events (crnn_profile_*)
+  cpu_baseline / --impl reference
+            the CPU restatement of the reference graph (oracle/torch_restatement.py; TF 1.8
+            itself cannot run here) on the box's host cores
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# BASELINE.json configs.  c3 is the default: it is the config the metric
+# "train chars/sec at 1/2/4/8 B200" is quoted on ("... at 1/2/4/8 B200"), and it fits one GPU.
+CONFIGS = {
+    "c1": dict(model="lstm", rnn_size=128, num_layers=2, seq_length=50, batch_size=50, vocab_size=65,
+               desc="LSTM 2x128, S=50, B=50/GPU, V=65 (train.py defaults; tinyshakespeare shape)"),
+    "c3": dict(model="gru", rnn_size=512, num_layers=2, seq_length=100, batch_size=256, vocab_size=96,
+               desc="GRU 2x512, S=100, B=256/GPU, V=96, synthetic Zipf text"),
+    "c4": dict(model="lstm", rnn_size=1024, num_layers=3, seq_length=200, batch_size=128, vocab_size=96,
+               desc="LSTM 3x1024, S=200, B=128/GPU, V=96, synthetic Zipf text"),
+    "c5": dict(model="rnn", rnn_size=2048, num_layers=4, seq_length=256, batch_size=512, vocab_size=256,
+               desc="tanh RNN 4x2048, S=256, B=512/GPU, V=256, synthetic text"),
+}
+GATES = {"lstm": 4, "gru": 3, "rnn": 1}
+L2_BYTES = 126e6
+
+
+def train_flop_per_char(c):
+    H, L, V, G = c["rnn_size"], c["num_layers"], c["vocab_size"], GATES[c["model"]]
+    return 3 * (L * 2 * (2 * H) * (G * H) + 2 * H * V)
+
+
+def phase_flops(c):
+    """Algorithmic FLOPs per step of each GEMM-shaped phase."""
+    H, L, V, G = c["rnn_size"], c["num_layers"], c["vocab_size"], GATES[c["model"]]
+    SB = c["seq_length"] * c["batch_size"]
+    unit = 2.0 * SB * H * G * H * L
+    return {"xproj_gemm": unit, "rec_fwd": unit, "rec_bwd": unit, "input_grads": unit, "weight_grads": 2 * unit,
+            "logits_gemm": 2.0 * SB * H * V, "proj_grads": 4.0 * SB * H * V}
+
+
+def phase_bytes(c, P):
+    """Algorithmic HBM bytes per step of the bandwidth-bound phases."""
+    H, V = c["rnn_size"], c["vocab_size"]
+    SB = c["seq_length"] * c["batch_size"]
+    return {"embed_gather": SB * 4 + V * H * 4 + SB * H * 4, "embed_scatter": SB * 4 + SB * H * 4 + V * H * 4,
+            "clip_adam": 32.0 * P, "softmax_xent": 2.0 * SB * V * 4 + SB * 4}
+
+
+def synthetic_ids(c, nb, seed):
+    """Zipf(s=1) ids over a seeded permutation of the vocab, as the loader's [B, nb*S] matrices."""
+    V, B, S = c["vocab_size"], c["batch_size"], c["seq_length"]
+    rng = np.random.Generator(np.random.PCG64(seed))
+    w = 1.0 / np.arange(1, V + 1)
+    p = w / w.sum()
+    ids = rng.permutation(V)[rng.choice(V, size=B * nb * S, p=p)].astype(np.int32)
+    X = ids.reshape(B, nb * S)
+    Y = np.roll(ids, -1).reshape(B, nb * S)
+    return X, Y
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sus=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sus=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([f.strip() for f in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def summary(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_restatement_rate(c, max_seconds, warmup, steps=None, batch=None, seed=0):
+    """chars/s of the CPU restatement (oracle/torch_restatement.py) on this box's host cores."""
+    import torch
+    from oracle import char_rnn_oracle as O
+    from oracle.torch_restatement import TorchStep
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    B = batch or c["batch_size"]
+    cc = dict(c, batch_size=B)
+    cfg = O.Config(c["model"], c["rnn_size"], c["num_layers"], c["seq_length"], B, c["vocab_size"], 5.0)
+    ts = TorchStep(cfg, O.init_params(cfg, seed), torch.float32)
+    ts.begin_epoch(0)
+    n_need = (steps or 64) + warmup
+    X, Y = synthetic_ids(cc, min(n_need, 8), 1234)
+    S = c["seq_length"]
+    nbm = X.shape[1] // S
+
+    def batch_k(k):
+        k %= nbm
+        return X[:, k * S:(k + 1) * S], Y[:, k * S:(k + 1) * S]
+    for k in range(warmup):
+        ts.step(*batch_k(k))
+    t0 = time.perf_counter()
+    done = 0
+    loss = None
+    while True:
+        loss = ts.step(*batch_k(warmup + done))
+        done += 1
+        el = time.perf_counter() - t0
+        if steps is not None and done >= steps:
+            break
+        if steps is None and (el >= max_seconds or done >= 64):
+            break
+    el = time.perf_counter() - t0
+    return dict(value=B * S * done / el, cores=cores, steps=done, seconds=el, batch=B, loss=loss)
+
+
+def run_reference(args, c, rank, world):
+    """--impl reference: the reference's CPU path (restated; TF 1.8 is not installable)."""
+    if rank != 0:
+        return
+    # bound the per-step sample so K+W steps end within a few minutes: calibrate on B/8 rows
+    B = c["batch_size"]
+    probe_b = max(1, B // 8)
+    probe = cpu_restatement_rate(c, 5.0, 1, steps=1, batch=probe_b)
+    per_row = probe["seconds"] / probe_b
+    budget = 150.0 / max(1, args.steps + args.warmup)
+    bs = B
+    while bs > 1 and per_row * bs > budget:
+        bs //= 2
+    r = cpu_restatement_rate(c, 1e9, args.warmup, steps=args.steps, batch=bs)
+    sample = "%d warm-up + %d steps of [%d of %d sequences x S=%d] per step" % (args.warmup, r["steps"], bs, B, c["seq_length"])
+    line = {"impl": "reference", "metric": "train_chars_per_sec", "value": r["value"], "unit": "chars/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * r["seconds"] / r["steps"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": c["desc"], "name": args.config, "host_threads": r["cores"]},
+            "cpu_baseline": {"value": r["value"], "unit": "chars/s", "cores": r["cores"], "kind": "port", "sample": sample},
+            "e2e": {"value": r["value"], "unit": "chars/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "TF 1.8 (requirements.txt:2) is not installable here; this is the PyTorch-CPU restatement of "
+                    "model.py:8-98 op for op (oracle/torch_restatement.py) on all host threads"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default=os.environ.get("CRNN_BENCH_CONFIG", "c3"), choices=sorted(CONFIGS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    c = CONFIGS[args.config]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, c, rank, world)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (no CPU fallback); use --impl reference for the CPU arm")
+    ge.build()
+    from distributed_char_rnn_b200 import _lib
+    from distributed_char_rnn_b200.model import Model
+    torch.cuda.set_device(local_rank)
+    pg = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        pg = dist.group.WORLD
+    lib = _lib.load()
+
+    margs = argparse.Namespace(grad_clip=5.0, output_keep_prob=1.0, input_keep_prob=1.0,
+                               **{k: v for k, v in c.items() if k != "desc"})
+    model = Model(margs, device="cuda:%d" % local_rank, seed=0, precision=args.precision, process_group=pg)
+    model.assign_lr(0.002)
+    B, S = c["batch_size"], c["seq_length"]
+    K, W = args.steps, args.warmup
+    nb = W + K
+    X, Y = synthetic_ids(c, nb, 1234 + rank)                  # one shard per rank (data_splitter contract)
+    Xd, Yd = torch.from_numpy(X).cuda(), torch.from_numpy(Y).cuda()
+
+    def dev_batch(k):
+        return Xd[:, k * S:(k + 1) * S], Yd[:, k * S:(k + 1) * S]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ws_bytes = model.workspace.numel() + 4 * 4 * model.P
+    flush = ws_bytes < 2 * L2_BYTES
+    flush_buf = torch.empty(int(256e6), dtype=torch.uint8, device="cuda") if flush else None
+
+    # ---- device-resident throughput ------------------------------------------------------
+    for k in range(W):
+        model.step_async(*dev_batch(k))
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = lib.crnn_launch_count()
+    if flush:
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        for k in range(K):
+            flush_buf.zero_()
+            evs[k][0].record()
+            model.step_async(*dev_batch(W + k))
+            evs[k][1].record()
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+    else:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for k in range(K):
+            model.step_async(*dev_batch(W + k))
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+    launches = lib.crnn_launch_count() - l0
+    clocks = sampler.summary()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    final_loss = float(model.grads[model.P + 1]) / world
+    value = world * B * S * K / (ms * 1e-3)
+
+    # ---- end to end: host ids in, loss out, every step -----------------------------------
+    e2e = None
+    if not args.no_e2e:
+        for k in range(2):
+            model.step(X[:, k * S:(k + 1) * S], Y[:, k * S:(k + 1) * S])
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(K):
+            model.step(X[:, (W + k) * S:(W + k + 1) * S], Y[:, (W + k) * S:(W + k + 1) * S])
+        barrier()
+        el = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(el, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * B * S * K / float(el.item()), "unit": "chars/s",
+               "h2d_bytes_per_step": 2 * B * S * 4, "d2h_bytes_per_step": 4}
+
+    # ---- per-phase timing of the same step (CUDA events on the launching stream) ---------
+    pk = peaks()
+    roofline = phases = None
+    if rank == 0:
+        nprof = min(K, 10)
+        arr = (ctypes.c_double * _lib.NUM_PHASES)()
+        _lib.check(lib.crnn_profile_enable(model._h, 1))
+        for k in range(nprof):
+            model.step_async(*dev_batch(W + k))
+            _lib.check(lib.crnn_profile_read(model._h, arr, 0))
+        _lib.check(lib.crnn_profile_enable(model._h, 0))
+        phases = {lib.crnn_profile_phase_name(i).decode(): arr[i] / nprof for i in range(_lib.NUM_PHASES)}
+        fl, by = phase_flops(c), phase_bytes(c, model.P)
+        dom = max((p for p in phases if p != "misc"), key=lambda p: phases[p])
+        dms = phases[dom]
+        if dom in fl:
+            ach = fl[dom] / (dms * 1e-3) / 1e12
+            roofline = {"bound": "tensor", "kernel": dom, "achieved": ach, "peak": pk["tf_sus"], "unit": "TFLOP/s",
+                        "frac": ach / pk["tf_sus"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
+                        "ms": dms, "algorithmic_flops": fl[dom]}
+        else:
+            ach = by[dom] / (dms * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm"], "unit": "GB/s",
+                        "frac": ach / pk["hbm"], "traffic": None, "peak_source": pk["src"], "ms": dms,
+                        "algorithmic_bytes": by[dom]}
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            roofline["traffic"] = json.load(open(tpath)).get(args.config, {}).get(dom)
+        step_tf = value / world * train_flop_per_char(c) / 1e12
+        roofline["step_tflops"] = step_tf
+        roofline["step_frac_of_tensor_peak"] = step_tf / pk["tf_sus"]
+
+    if world > 1:
+        dist.barrier()
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_restatement_rate(c, 12.0, 1)
+        cpu = {"value": r["value"], "unit": "chars/s", "cores": r["cores"], "kind": "port",
+               "sample": "1 warm-up + %d full steps (%d chars each) in %.1f s" % (r["steps"], B * S, r["seconds"])}
+    if rank == 0:
+        line = {"metric": "train_chars_per_sec", "value": value, "unit": "chars/s", "n_gpus": world, "steps": K,
+                "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
+                "config": {"workload": c["desc"], "name": args.config, "global_batch": world * B, "seq_length": S,
+                           "parallelism": "dp%d" % world, "precision": args.precision,
+                           "l2": ("256 MB flush write between timed steps (excluded from timing)" if flush else
+                                  "per-step working set %.0f MB > 126 MB L2, new batch every step" % (ws_bytes / 1e6))},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+                "cpu_baseline": cpu, "phases_ms": phases, "final_loss": final_loss}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,613 @@
+// crnn_api.cu — the C-ABI of include/crnn.h: handle, flat layout, workspace plan and the
+// launch sequence of one training step.  Compiled for sm_100a only.
+#include "../../include/crnn.h"
+#include "common.cuh"
+#include "gemm_simt.cuh"
+#include "recurrence_simt.cuh"
+#include "elementwise.cuh"
+
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string>
+#include <vector>
+
+namespace crnn {
+
+thread_local char g_err[512] = "";
+long long g_launches = 0;
+
+inline int set_err(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+inline int fail_cuda(cudaError_t e, const char* what) {
+    return set_err(CRNN_ERR_CUDA, "CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+}
+
+struct TensorInfo {
+    std::string name;
+    int64_t offset, rows, cols;
+};
+
+struct RecPlan {
+    int HC, BT, nslices, ntiles, TX;
+    size_t smem;
+};
+
+struct WsPlan {
+    size_t scratch;                 // barrier words + double accumulators + norm partials
+    size_t x0;
+    std::vector<size_t> hx, cx, gates;
+    size_t dz, dya, dyb, carry0, carry1, logits;
+    size_t total;
+};
+
+}  // namespace crnn
+
+using namespace crnn;
+
+struct crnn_handle {
+    crnn_config cfg;
+    int G;            // gate blocks in the cell kernel(s): lstm 4, gru 3 (2+1), rnn 1
+    int GS;           // gate-stash width / H
+    int GZ;           // pre-activation-gradient width / H
+    int nstate;       // tensors per layer in the RNN state
+    std::vector<TensorInfo> tensors;
+    int64_t P;
+    int64_t emb_off;
+    RecPlan fwd, bwd;
+    WsPlan ws;
+    int sm_count;
+    int max_smem;
+    // Adam beta powers, tracked like TF's fp32 beta1_power / beta2_power variables
+    int64_t pow_step;
+    float b1p, b2p;
+    // optional per-phase timing (CUDA events on the launching stream)
+    bool prof_on;
+    std::vector<cudaEvent_t> prof_ev;
+    std::vector<int> prof_id;
+    int prof_n;
+    double prof_ms[CRNN_NUM_PHASES];
+};
+
+static const char* kPhaseNames[CRNN_NUM_PHASES] = {
+    "embed_gather", "xproj_gemm", "rec_fwd", "logits_gemm", "softmax_xent", "proj_grads",
+    "rec_bwd", "weight_grads", "input_grads", "embed_scatter", "clip_adam", "misc"};
+
+// Close the running phase and open phase `id` (id < 0: just close).
+static void prof_mark(crnn_handle* h, cudaStream_t st, int id) {
+    if (!h->prof_on) return;
+    if (h->prof_n >= (int)h->prof_ev.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        h->prof_ev.push_back(e);
+        h->prof_id.push_back(-1);
+    }
+    cudaEventRecord(h->prof_ev[h->prof_n], st);
+    h->prof_id[h->prof_n] = id;
+    ++h->prof_n;
+}
+
+static const float kBeta1 = 0.9f, kBeta2 = 0.999f, kEps = 1e-8f;
+
+// scratch layout (bytes): [0,256) barrier words; [256,512) doubles {loss_sum, sq_sum};
+// [1024, 1024 + 8*NORM_BLOCKS) norm partials.
+static const size_t kScratchBytes = 8192;
+static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>(ws) + i; }
+static inline double* ws_loss(void* ws) { return reinterpret_cast<double*>((char*)ws + 256); }
+static inline double* ws_sq(void* ws) { return reinterpret_cast<double*>((char*)ws + 264); }
+static inline double* ws_partials(void* ws) { return reinterpret_cast<double*>((char*)ws + 1024); }
+
+static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+static int env_int(const char* name, int dflt) {
+    const char* s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+// Pick the (hidden slice, batch tile) decomposition of the persistent recurrence kernels.
+static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
+    const int H = h->cfg.rnn_size, B = h->cfg.batch_size, model = h->cfg.model;
+    const int G = h->G;
+    const int gfirst = model == CRNN_MODEL_LSTM ? 4 : (model == CRNN_MODEL_GRU ? 2 : 1);
+    const int max_ctas = h->sm_count;                    // 1 CTA per SM (shared-memory bound)
+    // columns handled by one thread row: fwd NC = gfirst*HC <= 64, bwd NC = HC <= 64
+    int hc_tx = backward ? 64 : 64 / gfirst;
+    // resident weight slice: G*H*HC floats (fwd and bwd alike) within ~128 KB
+    int hc_smem = (int)((128 * 1024 / 4) / ((int64_t)G * ((H + 3) & ~3)));
+    int HC = std::min(std::min(hc_tx, hc_smem), H);
+    if (HC >= 4) HC &= ~3;
+    if (HC < 1) return set_err(CRNN_ERR_UNSUP, "rnn_size %d too large for the fp32 recurrence kernel", H);
+    const double work = (double)B * G * H * (double)H;   // FMAs per step
+    int target = (int)std::min<double>(max_ctas, std::max(8.0, work / 65536.0));
+    int nslices, ntiles;
+    for (;;) {
+        nslices = ceil_div(H, HC);
+        ntiles = std::min(std::max(1, max_ctas / nslices), ceil_div(B, 8));
+        if (nslices * ntiles >= target / 2 || HC <= 4) break;
+        HC = std::max(4, (HC / 2) & ~3);
+    }
+    if (nslices > max_ctas) return set_err(CRNN_ERR_UNSUP, "rnn_size %d needs %d slices > %d SMs", H, nslices, max_ctas);
+    ntiles = std::min(ntiles, std::max(1, target / nslices));
+    int hc_env = env_int(backward ? "CRNN_REC_BWD_HC" : "CRNN_REC_FWD_HC", 0);
+    int nt_env = env_int(backward ? "CRNN_REC_BWD_TILES" : "CRNN_REC_FWD_TILES", 0);
+    if (hc_env > 0) { HC = std::min(hc_env, std::min(std::min(hc_tx, hc_smem), H)); nslices = ceil_div(H, HC); ntiles = std::min(ntiles, std::max(1, max_ctas / nslices)); }
+    if (nt_env > 0) ntiles = std::min(nt_env, std::max(1, max_ctas / nslices));
+    int BT = ceil_div(B, ntiles);
+    ntiles = ceil_div(B, BT);
+    out->HC = HC; out->BT = BT; out->nslices = nslices; out->ntiles = ntiles;
+    const int nc = backward ? HC : gfirst * HC;
+    out->TX = std::max(4, next_pow2(nc));
+    const size_t K4 = (H + 3) & ~3;
+    size_t wfl;
+    if (!backward) wfl = K4 * (size_t)G * HC;
+    else wfl = (size_t)(((int64_t)gfirst * H + 3) & ~3) * HC + (model == CRNN_MODEL_GRU ? K4 * HC : 0);
+    out->smem = (wfl + REC_RB * REC_LDA + (size_t)REC_RB * (nc + 1)) * sizeof(float);
+    if ((int)out->smem > h->max_smem)
+        return set_err(CRNN_ERR_UNSUP, "recurrence kernel needs %zu B shared memory > %d", out->smem, h->max_smem);
+    return CRNN_OK;
+}
+
+static void build_layout(crnn_handle* h) {
+    const int H = h->cfg.rnn_size, V = h->cfg.vocab_size, L = h->cfg.num_layers;
+    int64_t off = 0;
+    auto add = [&](const std::string& name, int64_t r, int64_t c) {
+        TensorInfo t{name, off, r, c};
+        h->tensors.push_back(t);
+        off = round_up64(off + r * c, 64);
+    };
+    add("rnnlm/softmax_w", H, V);
+    add("rnnlm/softmax_b", 1, V);
+    h->emb_off = off;
+    add("embedding", V, H);
+    for (int l = 0; l < L; ++l) {
+        std::string p = "rnnlm/multi_rnn_cell/cell_" + std::to_string(l) + "/";
+        if (h->cfg.model == CRNN_MODEL_LSTM) {
+            add(p + "lstm_cell/kernel", 2 * H, 4 * H);
+            add(p + "lstm_cell/bias", 1, 4 * H);
+        } else if (h->cfg.model == CRNN_MODEL_GRU) {
+            add(p + "gru_cell/gates/kernel", 2 * H, 2 * H);
+            add(p + "gru_cell/gates/bias", 1, 2 * H);
+            add(p + "gru_cell/candidate/kernel", 2 * H, H);
+            add(p + "gru_cell/candidate/bias", 1, H);
+        } else {
+            add(p + "basic_rnn_cell/kernel", 2 * H, H);
+            add(p + "basic_rnn_cell/bias", 1, H);
+        }
+    }
+    h->P = off;
+}
+
+static void build_workspace(crnn_handle* h) {
+    const int64_t H = h->cfg.rnn_size, V = h->cfg.vocab_size, L = h->cfg.num_layers;
+    const int64_t S = h->cfg.seq_length, B = h->cfg.batch_size;
+    size_t off = 0;
+    auto take = [&](int64_t floats) { size_t o = off; off = (size_t)round_up64(off + floats * 4, 256); return o; };
+    WsPlan& w = h->ws;
+    w.scratch = off; off += kScratchBytes;
+    w.x0 = take(S * B * H);
+    for (int l = 0; l < L; ++l) {
+        w.hx.push_back(take((S + 1) * B * H));
+        w.cx.push_back(h->cfg.model == CRNN_MODEL_LSTM ? take((S + 1) * B * H) : 0);
+        w.gates.push_back(take(S * B * h->GS * H));
+    }
+    w.dz = take((S + 1) * B * h->GZ * H);
+    w.dya = take(S * B * H);
+    w.dyb = take(S * B * H);
+    w.carry0 = take(B * H);
+    w.carry1 = take(B * H);
+    w.logits = take(S * B * V);
+    w.total = off;
+}
+
+extern "C" {
+
+const char* crnn_last_error(void) { return g_err; }
+const char* crnn_version(void) { return "crnn-b200 0.1.0 (sm_100a)"; }
+
+int crnn_create(const crnn_config* cfg, crnn_handle** out) {
+    if (!cfg || !out) return set_err(CRNN_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (cfg->model != CRNN_MODEL_RNN && cfg->model != CRNN_MODEL_GRU && cfg->model != CRNN_MODEL_LSTM)
+        return set_err(CRNN_ERR_ARG, "model type not supported: %d", cfg->model);
+    if (cfg->rnn_size < 1 || cfg->num_layers < 1 || cfg->seq_length < 1 || cfg->batch_size < 1 || cfg->vocab_size < 1)
+        return set_err(CRNN_ERR_ARG, "rnn_size, num_layers, seq_length, batch_size and vocab_size must be >= 1");
+    if (cfg->precision != CRNN_PREC_FP32 && cfg->precision != CRNN_PREC_BF16)
+        return set_err(CRNN_ERR_ARG, "unknown precision %d", cfg->precision);
+    if (cfg->precision == CRNN_PREC_BF16)
+        return set_err(CRNN_ERR_UNSUP, "CRNN_PREC_BF16 is not built in this version");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return set_err(CRNN_ERR_CUDA, "no CUDA device: this library has no CPU path (%s)", cudaGetErrorString(e));
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return set_err(CRNN_ERR_ARG, "device %d out of range [0,%d)", cfg->device, ndev);
+    cudaDeviceProp prop;
+    CRNN_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10)
+        return set_err(CRNN_ERR_UNSUP, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
+    crnn_handle* h = new crnn_handle();
+    h->cfg = *cfg;
+    h->G = cfg->model == CRNN_MODEL_LSTM ? 4 : (cfg->model == CRNN_MODEL_GRU ? 3 : 1);
+    h->GS = cfg->model == CRNN_MODEL_RNN ? 1 : 4;     // lstm: i,j,f,o   gru: r,u,cand,r*h
+    h->GZ = h->G;
+    h->nstate = cfg->model == CRNN_MODEL_LSTM ? 2 : 1;
+    h->sm_count = prop.multiProcessorCount;
+    h->max_smem = (int)prop.sharedMemPerBlockOptin;
+    h->pow_step = 0; h->b1p = 1.0f; h->b2p = 1.0f;
+    h->prof_on = false; h->prof_n = 0;
+    for (int i = 0; i < CRNN_NUM_PHASES; ++i) h->prof_ms[i] = 0.0;
+    build_layout(h);
+    int rc = plan_recurrence(h, false, &h->fwd);
+    if (rc == CRNN_OK) rc = plan_recurrence(h, true, &h->bwd);
+    if (rc != CRNN_OK) { delete h; return rc; }
+    build_workspace(h);
+    *out = h;
+    return CRNN_OK;
+}
+
+void crnn_destroy(crnn_handle* h) {
+    if (!h) return;
+    for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
+    delete h;
+}
+
+long long crnn_launch_count(void) { return g_launches; }
+
+int crnn_profile_enable(crnn_handle* h, int32_t on) {
+    if (!h) return set_err(CRNN_ERR_ARG, "null handle");
+    h->prof_on = on != 0;
+    h->prof_n = 0;
+    return CRNN_OK;
+}
+const char* crnn_profile_phase_name(int32_t i) { return (i >= 0 && i < CRNN_NUM_PHASES) ? kPhaseNames[i] : ""; }
+int crnn_profile_read(crnn_handle* h, double* ms_out, int32_t reset) {
+    if (!h || !ms_out) return set_err(CRNN_ERR_ARG, "null argument");
+    if (h->prof_n > 0) {
+        CRNN_CUDA(cudaEventSynchronize(h->prof_ev[h->prof_n - 1]));
+        for (int i = 0; i + 1 < h->prof_n; ++i) {
+            int id = h->prof_id[i];
+            if (id < 0 || id >= CRNN_NUM_PHASES) continue;
+            float ms = 0.f;
+            CRNN_CUDA(cudaEventElapsedTime(&ms, h->prof_ev[i], h->prof_ev[i + 1]));
+            h->prof_ms[id] += ms;
+        }
+        h->prof_n = 0;
+    }
+    for (int i = 0; i < CRNN_NUM_PHASES; ++i) ms_out[i] = h->prof_ms[i];
+    if (reset) for (int i = 0; i < CRNN_NUM_PHASES; ++i) h->prof_ms[i] = 0.0;
+    return CRNN_OK;
+}
+
+int64_t crnn_flat_size(const crnn_handle* h) { return h ? h->P : -1; }
+int32_t crnn_num_tensors(const crnn_handle* h) { return h ? (int32_t)h->tensors.size() : -1; }
+int crnn_param_layout(const crnn_handle* h, int32_t i, char* name, int32_t cap, int64_t* off, int64_t* rows, int64_t* cols) {
+    if (!h || i < 0 || i >= (int32_t)h->tensors.size()) return set_err(CRNN_ERR_ARG, "tensor index out of range");
+    const TensorInfo& t = h->tensors[i];
+    if (name && cap > 0) { strncpy(name, t.name.c_str(), cap - 1); name[cap - 1] = 0; }
+    if (off) *off = t.offset;
+    if (rows) *rows = t.rows;
+    if (cols) *cols = t.cols;
+    return CRNN_OK;
+}
+int64_t crnn_state_size(const crnn_handle* h) {
+    return h ? (int64_t)h->cfg.num_layers * h->nstate * h->cfg.batch_size * h->cfg.rnn_size : -1;
+}
+int64_t crnn_workspace_bytes(const crnn_handle* h) { return h ? (int64_t)h->ws.total : -1; }
+
+}  // extern "C"
+
+// ---- launch helpers ------------------------------------------------------------------
+
+template <int MODEL>
+static int launch_rec(const RecPlan& p, bool backward, RecArgs& a, cudaStream_t st) {
+    void (*fn)(RecArgs) = nullptr;
+#define CRNN_PICK(TXV)                                                                 \
+    case TXV: fn = backward ? rec_bwd_kernel<MODEL, TXV> : rec_fwd_kernel<MODEL, TXV>; break;
+    switch (p.TX) {
+        CRNN_PICK(4) CRNN_PICK(8) CRNN_PICK(16) CRNN_PICK(32) CRNN_PICK(64)
+        default: return set_err(CRNN_ERR_UNSUP, "bad TX %d", p.TX);
+    }
+#undef CRNN_PICK
+    CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+    a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles;
+    void* args[] = {&a};
+    // cooperative launch: all CTAs co-resident, or the launch fails instead of deadlocking
+    CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(REC_THREADS), args, p.smem, st));
+    ++g_launches;
+    return CRNN_OK;
+}
+
+static int launch_rec_model(const crnn_handle* h, bool backward, RecArgs& a, cudaStream_t st) {
+    const RecPlan& p = backward ? h->bwd : h->fwd;
+    switch (h->cfg.model) {
+        case CRNN_MODEL_LSTM: return launch_rec<CRNN_MODEL_LSTM>(p, backward, a, st);
+        case CRNN_MODEL_GRU:  return launch_rec<CRNN_MODEL_GRU>(p, backward, a, st);
+        default:              return launch_rec<CRNN_MODEL_RNN>(p, backward, a, st);
+    }
+}
+
+struct LayerParams {
+    const float *W, *b, *Wc, *bc;   // gru: W/b = gates, Wc/bc = candidate
+    int64_t oW, ob, oWc, obc;       // offsets into the flat buffers
+};
+
+static LayerParams layer_params(const crnn_handle* h, const float* params, int l) {
+    LayerParams lp{};
+    const int per = h->cfg.model == CRNN_MODEL_GRU ? 4 : 2;
+    const TensorInfo* t = &h->tensors[3 + l * per];
+    lp.oW = t[0].offset; lp.ob = t[1].offset;
+    lp.W = params + lp.oW; lp.b = params + lp.ob;
+    if (per == 4) { lp.oWc = t[2].offset; lp.obc = t[3].offset; lp.Wc = params + lp.oWc; lp.bc = params + lp.obc; }
+    return lp;
+}
+
+static inline float* wsf(void* ws, size_t off) { return reinterpret_cast<float*>((char*)ws + off); }
+
+static int grid_for(int64_t n_threads_needed, int sm_count) {
+    int64_t blocks = ceil_div64(n_threads_needed, 256);
+    return (int)std::max<int64_t>(1, std::min<int64_t>(blocks, (int64_t)sm_count * 8));
+}
+
+// Forward pass over all layers; leaves hx/cx/gates stashes in the workspace.
+static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
+                       const float* params, void* ws, cudaStream_t st) {
+    const crnn_config& c = h->cfg;
+    const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
+    const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
+    const int gw = h->GS * H;
+    float* x0 = wsf(ws, h->ws.x0);
+    const float* emb = params + h->emb_off;
+    prof_mark(h, st, CRNN_PHASE_EMBED_GATHER);
+    embed_gather_kernel<<<grid_for(SB * H / 4 + 1, h->sm_count), 256, 0, st>>>(emb, V, H, x, ldx, B, S, x0);
+    CRNN_LAUNCH_CHECK("embed_gather_kernel");
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 256, st));
+    for (int l = 0; l < L; ++l) {
+        LayerParams lp = layer_params(h, params, l);
+        float* hx = wsf(ws, h->ws.hx[l]);
+        float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
+        float* gates = wsf(ws, h->ws.gates[l]);
+        const float* in = l == 0 ? x0 : wsf(ws, h->ws.hx[l - 1]) + BH;
+        const float* sin = state_in + (int64_t)l * h->nstate * BH;
+        if (c.model == CRNN_MODEL_LSTM) {
+            CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, st));
+            CRNN_CUDA(cudaMemcpyAsync(hx, sin + BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+        } else {
+            CRNN_CUDA(cudaMemcpyAsync(hx, sin, BH * 4, cudaMemcpyDeviceToDevice, st));
+        }
+        // hoisted x half of [x,h]*W (+ bias) for all S steps at once
+        prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
+        int rc;
+        if (c.model == CRNN_MODEL_LSTM) {
+            rc = gemm_f32(0, 0, (int)SB, 4 * H, H, in, H, lp.W, 4 * H, gates, gw, lp.b, 0, st, h->sm_count);
+        } else if (c.model == CRNN_MODEL_GRU) {
+            rc = gemm_f32(0, 0, (int)SB, 2 * H, H, in, H, lp.W, 2 * H, gates, gw, lp.b, 0, st, h->sm_count);
+            if (rc == CRNN_OK) rc = gemm_f32(0, 0, (int)SB, H, H, in, H, lp.Wc, H, gates + 2 * H, gw, lp.bc, 0, st, h->sm_count);
+        } else {
+            rc = gemm_f32(0, 0, (int)SB, H, H, in, H, lp.W, H, gates, gw, lp.b, 0, st, h->sm_count);
+        }
+        if (rc != CRNN_OK) return rc;
+        RecArgs a{};
+        a.B = B; a.H = H; a.S = S; a.GS = h->GS;
+        a.W = lp.W; a.Wc = lp.Wc; a.gates = gates; a.hx = hx; a.cx = cx;
+        a.barrier = ws_barrier(ws, 2 * l);
+        prof_mark(h, st, CRNN_PHASE_REC_FWD);
+        rc = launch_rec_model(h, false, a, st);
+        if (rc != CRNN_OK) return rc;
+        prof_mark(h, st, CRNN_PHASE_MISC);
+        float* sout = state_out + (int64_t)l * h->nstate * BH;
+        if (c.model == CRNN_MODEL_LSTM) {
+            CRNN_CUDA(cudaMemcpyAsync(sout, cx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+            CRNN_CUDA(cudaMemcpyAsync(sout + BH, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+        } else {
+            CRNN_CUDA(cudaMemcpyAsync(sout, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    // logits (time-major rows t*B+b) = top outputs * softmax_w + softmax_b   (model.py:76)
+    const float* top = wsf(ws, h->ws.hx[L - 1]) + BH;
+    const float* Wsm = params + h->tensors[0].offset;
+    const float* bsm = params + h->tensors[1].offset;
+    prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
+    int rc = gemm_f32(0, 0, (int)SB, V, H, top, H, Wsm, V, wsf(ws, h->ws.logits), V, bsm, 0, st, h->sm_count);
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    return rc;
+}
+
+static int check_common(crnn_handle* h, const void* a, const void* b, const void* c) {
+    if (!h) return set_err(CRNN_ERR_ARG, "null handle");
+    if (!a || !b || !c) return set_err(CRNN_ERR_ARG, "null device pointer");
+    CRNN_CUDA(cudaSetDevice(h->cfg.device));
+    if (h->cfg.batch_size > 2 * 1024 * 1024) return set_err(CRNN_ERR_ARG, "batch too large");
+    if (h->cfg.num_layers > 32) return set_err(CRNN_ERR_ARG, "at most 32 layers");
+    return CRNN_OK;
+}
+
+extern "C" {
+
+int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, int64_t ld,
+                          const float* state_in, float* state_out, const float* params, float* grads,
+                          void* ws, void* stream) {
+    int rc = check_common(h, x, params, ws);
+    if (rc != CRNN_OK) return rc;
+    if (!y || !state_in || !state_out || !grads) return set_err(CRNN_ERR_ARG, "null device pointer");
+    const crnn_config& c = h->cfg;
+    if (ld < c.seq_length) return set_err(CRNN_ERR_ARG, "ld_xy %lld < seq_length %d", (long long)ld, c.seq_length);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
+    const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
+    const int gw = h->GS * H, zw = h->GZ * H;
+
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
+    CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
+    rc = run_forward(h, x, ld, state_in, state_out, params, ws, st);
+    if (rc != CRNN_OK) return rc;
+    prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
+
+    // loss + dlogits in place, then the three projection-layer gradients
+    float* logits = wsf(ws, h->ws.logits);
+    softmax_xent_kernel<<<grid_for(SB * 32, h->sm_count), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws));
+    CRNN_LAUNCH_CHECK("softmax_xent_kernel");
+    const float* top = wsf(ws, h->ws.hx[L - 1]) + BH;
+    const float* Wsm = params + h->tensors[0].offset;
+    float* dya = wsf(ws, h->ws.dya);
+    float* dyb = wsf(ws, h->ws.dyb);
+    prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
+    rc = gemm_f32(1, 0, H, V, (int)SB, top, H, logits, V, grads + h->tensors[0].offset, V, nullptr, 1, st, h->sm_count);
+    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
+    if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, V, logits, V, Wsm, V, dya, H, nullptr, 0, st, h->sm_count);
+    if (rc != CRNN_OK) return rc;
+
+    float* dz = wsf(ws, h->ws.dz);
+    float* dcur = dya;
+    float* dnext = dyb;
+    for (int l = L - 1; l >= 0; --l) {
+        LayerParams lp = layer_params(h, params, l);
+        float* hx = wsf(ws, h->ws.hx[l]);
+        float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
+        float* gates = wsf(ws, h->ws.gates[l]);
+        const float* in = l == 0 ? wsf(ws, h->ws.x0) : wsf(ws, h->ws.hx[l - 1]) + BH;
+        RecArgs a{};
+        a.B = B; a.H = H; a.S = S; a.GS = h->GS;
+        a.W = lp.W; a.Wc = lp.Wc; a.gates = gates; a.hx = hx; a.cx = cx;
+        a.dy = dcur; a.dz = dz; a.carry0 = wsf(ws, h->ws.carry0); a.carry1 = wsf(ws, h->ws.carry1);
+        a.barrier = ws_barrier(ws, 2 * l + 1);
+        prof_mark(h, st, CRNN_PHASE_REC_BWD);
+        rc = launch_rec_model(h, true, a, st);
+        if (rc != CRNN_OK) return rc;
+        prof_mark(h, st, CRNN_PHASE_WEIGHT_GRADS);
+        float* gW = grads + lp.oW;
+        float* gb = grads + lp.ob;
+        const int sc = h->sm_count;
+        if (c.model == CRNN_MODEL_GRU) {
+            float* gWc = grads + lp.oWc;
+            float* gbc = grads + lp.obc;
+            // gates kernel [2H,2H]: rows 0..H from inputs, rows H..2H from h_{t-1}
+            rc = gemm_f32(1, 0, H, 2 * H, (int)SB, in, H, dz, zw, gW, 2 * H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, 2 * H, (int)SB, hx, H, dz, zw, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, st);
+            // candidate kernel [2H,H]: rows H..2H see r*h_{t-1}
+            if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, H, (int)SB, in, H, dz + 2 * H, zw, gWc, H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, H, (int)SB, gates + 3 * H, gw, dz + 2 * H, zw, gWc + (int64_t)H * H, H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, st);
+            prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
+            if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, 2 * H, dz, zw, lp.W, 2 * H, dnext, H, nullptr, 0, st, sc);
+            if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, H, dz + 2 * H, zw, lp.Wc, H, dnext, H, nullptr, 1, st, sc);
+        } else {
+            const int GH = h->G * H;
+            rc = gemm_f32(1, 0, H, GH, (int)SB, in, H, dz, zw, gW, GH, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, GH, (int)SB, hx, H, dz, zw, gW + (int64_t)H * GH, GH, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, st);
+            prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
+            if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, GH, dz, zw, lp.W, GH, dnext, H, nullptr, 0, st, sc);
+        }
+        if (rc != CRNN_OK) return rc;
+        std::swap(dcur, dnext);
+    }
+    // dcur = dX [S,B,H] = the IndexedSlices values of the embedding gradient
+    prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
+    embed_scatter_kernel<<<grid_for(SB * H, h->sm_count), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, dcur, ws_sq(ws));
+    CRNN_LAUNCH_CHECK("embed_scatter_kernel");
+    finalize_scalars_kernel<<<1, 32, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P);
+    CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
+    prof_mark(h, st, -1);
+    return CRNN_OK;
+}
+
+int crnn_clip_adam(crnn_handle* h, float* params, const float* grads, float* m, float* v, float lr, float clip,
+                   int64_t step, float mult, float* gnorm_out, void* ws, void* stream) {
+    int rc = check_common(h, params, grads, ws);
+    if (rc != CRNN_OK) return rc;
+    if (!m || !v) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (step < 1) return set_err(CRNN_ERR_ARG, "Adam step must be >= 1");
+    cudaStream_t st = (cudaStream_t)stream;
+    // beta powers as TF keeps them: fp32 variables multiplied once per step
+    if (step < h->pow_step) { h->pow_step = 0; h->b1p = 1.0f; h->b2p = 1.0f; }
+    while (h->pow_step < step) { h->b1p *= kBeta1; h->b2p *= kBeta2; ++h->pow_step; }
+    const int64_t emb_end = h->emb_off + (int64_t)h->cfg.vocab_size * h->cfg.rnn_size;
+    int nblk = (int)std::min<int64_t>(NORM_BLOCKS, std::max<int64_t>(1, h->P / 1024));
+    prof_mark(h, st, CRNN_PHASE_CLIP_ADAM);
+    sqnorm_partials_kernel<<<nblk, 256, 0, st>>>(grads, h->P, h->emb_off, emb_end, ws_partials(ws));
+    CRNN_LAUNCH_CHECK("sqnorm_partials_kernel");
+    AdamArgs a{};
+    a.p = params; a.g = grads; a.m = m; a.v = v; a.p_bf16 = nullptr; a.P = h->P;
+    a.partial = ws_partials(ws); a.npartial = nblk;
+    a.lr_t = lr * sqrtf(1.0f - h->b2p) / (1.0f - h->b1p);
+    a.beta1 = kBeta1; a.beta2 = kBeta2; a.eps = kEps; a.clip = clip; a.mult = mult; a.gnorm_out = gnorm_out;
+    clip_adam_kernel<<<grid_for(h->P / 4, h->sm_count), 256, 0, st>>>(a);
+    CRNN_LAUNCH_CHECK("clip_adam_kernel");
+    prof_mark(h, st, -1);
+    return CRNN_OK;
+}
+
+int crnn_train_step(crnn_handle* h, const int32_t* x, const int32_t* y, int64_t ld, float* state, float* params,
+                    float* grads, float* m, float* v, float lr, float clip, int64_t step, void* ws, void* stream) {
+    int rc = crnn_forward_backward(h, x, y, ld, state, state, params, grads, ws, stream);
+    if (rc != CRNN_OK) return rc;
+    return crnn_clip_adam(h, params, grads, m, v, lr, clip, step, 1.0f, nullptr, ws, stream);
+}
+
+int crnn_forward(crnn_handle* h, const int32_t* x, int64_t ld, const float* state_in, float* state_out,
+                 const float* params, float* logits_out, float* probs_out, void* ws, void* stream) {
+    int rc = check_common(h, x, params, ws);
+    if (rc != CRNN_OK) return rc;
+    if (!state_in || !state_out) return set_err(CRNN_ERR_ARG, "null device pointer");
+    const crnn_config& c = h->cfg;
+    if (ld < c.seq_length) return set_err(CRNN_ERR_ARG, "ld_x %lld < seq_length %d", (long long)ld, c.seq_length);
+    cudaStream_t st = (cudaStream_t)stream;
+    CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
+    rc = run_forward(h, x, ld, state_in, state_out, params, ws, st);
+    if (rc != CRNN_OK) return rc;
+    if (logits_out || probs_out) {
+        const int64_t SB = (int64_t)c.seq_length * c.batch_size;
+        logits_out_kernel<<<grid_for(SB * 32, h->sm_count), 256, 0, st>>>(wsf(ws, h->ws.logits), c.batch_size,
+                                                                         c.seq_length, c.vocab_size, logits_out, probs_out);
+        CRNN_LAUNCH_CHECK("logits_out_kernel");
+    }
+    return CRNN_OK;
+}
+
+// ---- single operators ------------------------------------------------------------------
+
+int crnn_embedding_gather(const float* table, int32_t V, int32_t H, const int32_t* x, int64_t ldx, int32_t B, int32_t S,
+                          float* out, void* stream) {
+    if (!table || !x || !out) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (V < 1 || H < 1 || B < 0 || S < 0) return set_err(CRNN_ERR_ARG, "bad shape");
+    if ((int64_t)B * S == 0) return CRNN_OK;
+    embed_gather_kernel<<<grid_for((int64_t)S * B * H / 4 + 1, 148), 256, 0, (cudaStream_t)stream>>>(table, V, H, x, ldx, B, S, out);
+    CRNN_LAUNCH_CHECK("embed_gather_kernel");
+    return CRNN_OK;
+}
+
+int crnn_embedding_scatter_add(float* dtable, int32_t V, int32_t H, const int32_t* x, int64_t ldx, int32_t B, int32_t S,
+                               const float* dout, double* sqnorm, void* stream) {
+    if (!dtable || !x || !dout) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (V < 1 || H < 1 || B < 0 || S < 0) return set_err(CRNN_ERR_ARG, "bad shape");
+    if ((int64_t)B * S == 0) return CRNN_OK;
+    embed_scatter_kernel<<<grid_for((int64_t)S * B * H, 148), 256, 0, (cudaStream_t)stream>>>(dtable, V, H, x, ldx, B, S, dout, sqnorm);
+    CRNN_LAUNCH_CHECK("embed_scatter_kernel");
+    return CRNN_OK;
+}
+
+int crnn_softmax_xent(float* logits, int32_t B, int32_t S, int32_t V, const int32_t* y, int64_t ldy, double* loss_sum, void* stream) {
+    if (!logits || !y) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (V < 1 || B < 0 || S < 0) return set_err(CRNN_ERR_ARG, "bad shape");
+    if ((int64_t)B * S == 0) return CRNN_OK;
+    softmax_xent_kernel<<<grid_for((int64_t)S * B * 32, 148), 256, 0, (cudaStream_t)stream>>>(logits, B, S, V, y, ldy, loss_sum);
+    CRNN_LAUNCH_CHECK("softmax_xent_kernel");
+    return CRNN_OK;
+}
+
+int crnn_gemm_f32(int32_t ta, int32_t tb, int32_t M, int32_t N, int32_t K, const float* A, int64_t lda, const float* B,
+                  int64_t ldb, float* C, int64_t ldc, const float* bias, int32_t accumulate, void* stream) {
+    if (!A || !B || !C) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (M < 0 || N < 0 || K < 0) return set_err(CRNN_ERR_ARG, "bad shape");
+    return gemm_f32(ta, tb, M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, (cudaStream_t)stream);
+}
+
+}  // extern "C"

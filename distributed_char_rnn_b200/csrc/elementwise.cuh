@@ -1,0 +1,212 @@
+// elementwise.cuh — the HBM-bound pieces of the step: embedding gather / scatter-add,
+// softmax + sequence cross-entropy rows, global-norm clip + Adam.
+#pragma once
+#include "common.cuh"
+
+namespace crnn {
+
+// ---- embedding (model.py:54-55,62-63) ---------------------------------------------------
+// out[t,b,:] = table[x[b,t],:]; one float4 per thread, rows of the (tiny, L2-resident) table.
+__global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restrict__ table, int V, int H,
+                                                           const int32_t* __restrict__ x, int64_t ldx,
+                                                           int B, int S, float* __restrict__ out) {
+    const int64_t n = (int64_t)S * B * H;
+    const bool vec = (H & 3) == 0;
+    if (vec) {
+        const int H4 = H >> 2;
+        const int64_t n4 = n >> 2;
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+            int64_t row = i / H4;
+            int c = (int)(i % H4);
+            int t = (int)(row / B), b = (int)(row % B);
+            int id = __ldg(x + (int64_t)b * ldx + t);
+            id = min(max(id, 0), V - 1);
+            float4 v = __ldg(reinterpret_cast<const float4*>(table + (int64_t)id * H) + c);
+            reinterpret_cast<float4*>(out)[i] = v;
+        }
+    } else {
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+            int64_t row = i / H;
+            int c = (int)(i % H);
+            int t = (int)(row / B), b = (int)(row % B);
+            int id = __ldg(x + (int64_t)b * ldx + t);
+            id = min(max(id, 0), V - 1);
+            out[i] = __ldg(table + (int64_t)id * H + c);
+        }
+    }
+}
+
+// dtable[x[b,t],:] += dout[t,b,:]  (IndexedSlices -> dense) and sqnorm += sum dout^2.
+__global__ void __launch_bounds__(256) embed_scatter_kernel(float* __restrict__ dtable, int V, int H,
+                                                            const int32_t* __restrict__ x, int64_t ldx,
+                                                            int B, int S, const float* __restrict__ dout,
+                                                            double* __restrict__ sqnorm) {
+    __shared__ double sh[32];
+    const int64_t n = (int64_t)S * B * H;
+    double ss = 0.0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = i / H;
+        int c = (int)(i % H);
+        int t = (int)(row / B), b = (int)(row % B);
+        int id = __ldg(x + (int64_t)b * ldx + t);
+        id = min(max(id, 0), V - 1);
+        float g = __ldg(dout + i);
+        ss += (double)g * (double)g;
+        atomicAdd(dtable + (int64_t)id * H + c, g);
+    }
+    double tot = block_sum_d(ss, sh);
+    if (threadIdx.x == 0 && sqnorm) atomicAdd(sqnorm, tot);
+}
+
+// ---- softmax + sequence cross-entropy (model.py:77,80-85) ---------------------------------
+// One warp per row of logits [N, V] (row i = t*B + b).  In place: logits -> (softmax-onehot)/N.
+__global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ logits, int B, int S, int V,
+                                                           const int32_t* __restrict__ y, int64_t ldy,
+                                                           double* __restrict__ loss_sum) {
+    __shared__ double sh[32];
+    const int lane = threadIdx.x & 31;
+    const int64_t N = (int64_t)B * S;
+    const float invN = 1.0f / (float)N;
+    double local = 0.0;
+    for (int64_t row = blockIdx.x * 8 + (threadIdx.x >> 5); row < N; row += (int64_t)gridDim.x * 8) {
+        float* z = logits + row * V;
+        int t = (int)(row / B), b = (int)(row % B);
+        int label = __ldg(y + (int64_t)b * ldy + t);
+        float m = -INFINITY;
+        for (int c = lane; c < V; c += 32) m = fmaxf(m, z[c]);
+        m = warp_max(m);
+        float s = 0.f;
+        for (int c = lane; c < V; c += 32) s += expf(z[c] - m);
+        s = warp_sum(s);
+        float lse = logf(s) + m;
+        float inv = 1.0f / s;
+        float zl = 0.f;
+        for (int c = lane; c < V; c += 32) {
+            float v = z[c];
+            if (c == label) zl = v;
+            float p = expf(v - m) * inv;
+            z[c] = (p - (c == label ? 1.0f : 0.0f)) * invN;
+        }
+        zl = warp_sum(zl);
+        if (lane == 0) local += (double)(lse - zl);
+    }
+    double tot = block_sum_d(local, sh);
+    if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, tot);
+}
+
+// probs[b*S+t,:] = softmax(logits_tb[t*B+b,:]); also writes the re-ordered logits.
+__global__ void __launch_bounds__(256) logits_out_kernel(const float* __restrict__ logits_tb, int B, int S, int V,
+                                                         float* __restrict__ logits_bs, float* __restrict__ probs_bs) {
+    const int lane = threadIdx.x & 31;
+    const int64_t N = (int64_t)B * S;
+    for (int64_t row = blockIdx.x * 8 + (threadIdx.x >> 5); row < N; row += (int64_t)gridDim.x * 8) {
+        const float* z = logits_tb + row * V;
+        int t = (int)(row / B), b = (int)(row % B);
+        int64_t orow = (int64_t)b * S + t;
+        float m = -INFINITY;
+        for (int c = lane; c < V; c += 32) m = fmaxf(m, z[c]);
+        m = warp_max(m);
+        float s = 0.f;
+        for (int c = lane; c < V; c += 32) s += expf(z[c] - m);
+        s = warp_sum(s);
+        float inv = 1.0f / s;
+        for (int c = lane; c < V; c += 32) {
+            float v = z[c];
+            if (logits_bs) logits_bs[orow * V + c] = v;
+            if (probs_bs) probs_bs[orow * V + c] = expf(v - m) * inv;
+        }
+    }
+}
+
+// grads[P] = sum |dX|^2 ; grads[P+1] = cost = loss_sum / (B*S)
+__global__ void finalize_scalars_kernel(const double* __restrict__ sq, const double* __restrict__ loss_sum,
+                                        double n, float* __restrict__ tail) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        tail[0] = (float)(*sq);
+        tail[1] = (float)(*loss_sum / n);
+    }
+}
+
+// ---- clip_by_global_norm + Adam (model.py:91-98) ------------------------------------------
+constexpr int NORM_BLOCKS = 592;   // 4 x 148
+
+// partial[blk] = sum of g^2 over this block's share of [0,P) minus the embedding range
+// (the embedding enters the norm through its un-deduplicated slices, grads[P]).
+__global__ void __launch_bounds__(256) sqnorm_partials_kernel(const float* __restrict__ g, int64_t P,
+                                                              int64_t skip_beg, int64_t skip_end,
+                                                              double* __restrict__ partial) {
+    __shared__ double sh[32];
+    double ss = 0.0;
+    const int64_t P4 = P >> 2;   // P is a multiple of 64
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < P4; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t e = i << 2;
+        float4 v = __ldg(reinterpret_cast<const float4*>(g) + i);
+        if (e + 3 < skip_beg || e >= skip_end) {
+            ss += (double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z + (double)v.w * v.w;
+        } else {
+            if (e + 0 < skip_beg || e + 0 >= skip_end) ss += (double)v.x * v.x;
+            if (e + 1 < skip_beg || e + 1 >= skip_end) ss += (double)v.y * v.y;
+            if (e + 2 < skip_beg || e + 2 >= skip_end) ss += (double)v.z * v.z;
+            if (e + 3 < skip_beg || e + 3 >= skip_end) ss += (double)v.w * v.w;
+        }
+    }
+    double tot = block_sum_d(ss, sh);
+    if (threadIdx.x == 0) partial[blockIdx.x] = tot;
+}
+
+struct AdamArgs {
+    float* p; const float* g; float* m; float* v;
+    __nv_bfloat16* p_bf16;       // optional bf16 shadow of the parameters (perf mode)
+    int64_t P;
+    const double* partial; int npartial;
+    float lr_t;                  // lr * sqrt(1-beta2^t) / (1-beta1^t)
+    float beta1, beta2, eps;
+    float clip, mult;
+    float* gnorm_out;
+};
+
+__global__ void __launch_bounds__(256) clip_adam_kernel(AdamArgs a) {
+    __shared__ double sh[32];
+    __shared__ float s_scale;
+    // every block reduces the partials in the same fixed order -> identical scale everywhere
+    double ss = 0.0;
+    for (int i = threadIdx.x; i < a.npartial; i += blockDim.x) ss += a.partial[i];
+    double tot = block_sum_d(ss, sh);
+    if (threadIdx.x == 0) {
+        tot += (double)a.g[a.P];                                   // slices' sum of squares
+        float gn = a.mult * (float)sqrt(tot);
+        // tf.clip_by_global_norm: scale = clip * min(1/norm, 1/clip)
+        s_scale = a.clip * fminf(1.0f / gn, 1.0f / a.clip);
+        if (blockIdx.x == 0 && a.gnorm_out) *a.gnorm_out = gn;
+    }
+    __syncthreads();
+    const float gs = s_scale * a.mult;
+    const float omb1 = 1.0f - a.beta1, omb2 = 1.0f - a.beta2;
+    const int64_t P4 = a.P >> 2;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < P4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 g = __ldg(reinterpret_cast<const float4*>(a.g) + i);
+        float4 m = reinterpret_cast<float4*>(a.m)[i];
+        float4 v = reinterpret_cast<float4*>(a.v)[i];
+        float4 p = reinterpret_cast<float4*>(a.p)[i];
+        float gg[4] = {g.x * gs, g.y * gs, g.z * gs, g.w * gs};
+        float mm[4] = {m.x, m.y, m.z, m.w}, vv[4] = {v.x, v.y, v.z, v.w}, pp[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            // ApplyAdam: m += (g-m)(1-b1); v += (g^2-v)(1-b2); p -= lr_t*m / (sqrt(v)+eps)
+            mm[k] += (gg[k] - mm[k]) * omb1;
+            vv[k] += (gg[k] * gg[k] - vv[k]) * omb2;
+            pp[k] -= (a.lr_t * mm[k]) / (sqrtf(vv[k]) + a.eps);
+        }
+        reinterpret_cast<float4*>(a.m)[i] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        reinterpret_cast<float4*>(a.v)[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        reinterpret_cast<float4*>(a.p)[i] = make_float4(pp[0], pp[1], pp[2], pp[3]);
+        if (a.p_bf16) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(pp[0], pp[1]);
+            __nv_bfloat162 hi = __floats2bfloat162_rn(pp[2], pp[3]);
+            reinterpret_cast<__nv_bfloat162*>(a.p_bf16)[2 * i] = lo;
+            reinterpret_cast<__nv_bfloat162*>(a.p_bf16)[2 * i + 1] = hi;
+        }
+    }
+}
+
+}  // namespace crnn
