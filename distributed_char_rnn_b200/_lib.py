@@ -47,6 +47,8 @@ SIGNATURES = {
     "crnn_embedding_gather": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "crnn_embedding_scatter_add": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "crnn_softmax_xent": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp]),
+    "crnn_gemm_bf16": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
+                               c_i32, c_vp]),
     "crnn_gemm_f32": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
                               c_i32, c_vp]),
 }

@@ -5,6 +5,7 @@
 #include "gemm_simt.cuh"
 #include "recurrence_simt.cuh"
 #include "elementwise.cuh"
+#include "gemm_tc.cuh"
 
 #include <stdarg.h>
 #include <stdlib.h>
@@ -33,7 +34,7 @@ struct TensorInfo {
 };
 
 struct RecPlan {
-    int HC, BT, nslices, ntiles, TX;
+    int HC, BT, nslices, ntiles, TXa, TXb;
     size_t smem;
 };
 
@@ -119,7 +120,7 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
     // resident weight slice: G*H*HC floats (fwd and bwd alike) within ~128 KB
     int hc_smem = (int)((128 * 1024 / 4) / ((int64_t)G * ((H + 3) & ~3)));
     int HC = std::min(std::min(hc_tx, hc_smem), H);
-    if (HC >= 4) HC &= ~3;
+    if (HC >= 4) { int p2 = 4; while (p2 * 2 <= HC) p2 *= 2; HC = p2; }   // power of two: no idle thread columns
     if (HC < 1) return set_err(CRNN_ERR_UNSUP, "rnn_size %d too large for the fp32 recurrence kernel", H);
     const double work = (double)B * G * H * (double)H;   // FMAs per step
     int target = (int)std::min<double>(max_ctas, std::max(8.0, work / 65536.0));
@@ -128,7 +129,7 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
         nslices = ceil_div(H, HC);
         ntiles = std::min(std::max(1, max_ctas / nslices), ceil_div(B, 8));
         if (nslices * ntiles >= target / 2 || HC <= 4) break;
-        HC = std::max(4, (HC / 2) & ~3);
+        HC = std::max(4, HC / 2);
     }
     if (nslices > max_ctas) return set_err(CRNN_ERR_UNSUP, "rnn_size %d needs %d slices > %d SMs", H, nslices, max_ctas);
     ntiles = std::min(ntiles, std::max(1, target / nslices));
@@ -140,12 +141,13 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
     ntiles = ceil_div(B, BT);
     out->HC = HC; out->BT = BT; out->nslices = nslices; out->ntiles = ntiles;
     const int nc = backward ? HC : gfirst * HC;
-    out->TX = std::max(4, next_pow2(nc));
+    out->TXa = std::max(4, next_pow2(nc));
+    out->TXb = std::max(4, next_pow2(HC));
     const size_t K4 = (H + 3) & ~3;
     size_t wfl;
     if (!backward) wfl = K4 * (size_t)G * HC;
     else wfl = (size_t)(((int64_t)gfirst * H + 3) & ~3) * HC + (model == CRNN_MODEL_GRU ? K4 * HC : 0);
-    out->smem = (wfl + REC_RB * REC_LDA + (size_t)REC_RB * (nc + 1)) * sizeof(float);
+    out->smem = (wfl + 2 * REC_RB * REC_LDA + (size_t)REC_RB * (nc + 1)) * sizeof(float);
     if ((int)out->smem > h->max_smem)
         return set_err(CRNN_ERR_UNSUP, "recurrence kernel needs %zu B shared memory > %d", out->smem, h->max_smem);
     return CRNN_OK;
@@ -305,16 +307,9 @@ int64_t crnn_workspace_bytes(const crnn_handle* h) { return h ? (int64_t)h->ws.t
 
 template <int MODEL>
 static int launch_rec(const RecPlan& p, bool backward, RecArgs& a, cudaStream_t st) {
-    void (*fn)(RecArgs) = nullptr;
-#define CRNN_PICK(TXV)                                                                 \
-    case TXV: fn = backward ? rec_bwd_kernel<MODEL, TXV> : rec_fwd_kernel<MODEL, TXV>; break;
-    switch (p.TX) {
-        CRNN_PICK(4) CRNN_PICK(8) CRNN_PICK(16) CRNN_PICK(32) CRNN_PICK(64)
-        default: return set_err(CRNN_ERR_UNSUP, "bad TX %d", p.TX);
-    }
-#undef CRNN_PICK
+    void (*fn)(RecArgs) = backward ? rec_bwd_kernel<MODEL> : rec_fwd_kernel<MODEL>;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-    a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles;
+    a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles; a.TXa = p.TXa; a.TXb = p.TXb;
     void* args[] = {&a};
     // cooperative launch: all CTAs co-resident, or the launch fails instead of deadlocking
     CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(REC_THREADS), args, p.smem, st));
@@ -608,6 +603,14 @@ int crnn_gemm_f32(int32_t ta, int32_t tb, int32_t M, int32_t N, int32_t K, const
     if (!A || !B || !C) return set_err(CRNN_ERR_ARG, "null device pointer");
     if (M < 0 || N < 0 || K < 0) return set_err(CRNN_ERR_ARG, "bad shape");
     return gemm_f32(ta, tb, M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, (cudaStream_t)stream);
+}
+
+int crnn_gemm_bf16(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K, const void* A, int64_t lda,
+                   const void* B, int64_t ldb, float* C, int64_t ldc, const float* bias, int32_t accumulate, void* stream) {
+    if (!A || !B || !C) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (M < 0 || N < 0 || K < 1) return set_err(CRNN_ERR_ARG, "bad shape");
+    return tc::gemm_bf16_tc(M, N, K, (const __nv_bfloat16*)A, lda, a_mn, (const __nv_bfloat16*)B, ldb, b_mn, C, ldc, bias,
+                            accumulate, (cudaStream_t)stream);
 }
 
 }  // extern "C"

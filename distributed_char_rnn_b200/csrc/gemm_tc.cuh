@@ -1,0 +1,221 @@
+// gemm_tc.cuh — bf16 x bf16 -> fp32 GEMM on the 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+//   C[M,N] (fp32, row-major) (+)= op(A)[M,K] * op(B)[K,N] (+ bias[N])
+//
+// The batch-parallel contractions of the training step (CRNN_PREC_BF16): the hoisted
+// x-projection of every layer (NN), the input gradients dIn = dZ * Wx^T (NT) and the weight
+// gradients dW = In^T * dZ (TN, split-K with fp32 atomics).  Operands are bf16 in global
+// memory in whichever orientation their producer wrote them: "K-major" (the contraction
+// index is contiguous) or "MN-major" (the M/N index is contiguous); both are fed to
+// tcgen05.mma directly through the descriptor's major bits, so nothing is transposed in HBM.
+//
+// CTA = 6 warps: warp 0 TMA producer, warp 1 MMA issuer (one thread), warps 2-5 epilogue
+// (TMEM -> registers -> global).  128 x BN accumulator tile in TMEM, BLOCK_K = 64
+// (128-byte swizzled rows), STAGES-deep mbarrier ring between TMA and MMA.
+#pragma once
+#include "tc_common.cuh"
+#include <algorithm>
+
+namespace crnn {
+namespace tc {
+
+constexpr int GT_BM = 128;
+constexpr int GT_BK = 64;
+constexpr int GT_THREADS = 192;
+
+struct GemmTcArgs {
+    float* C; int64_t ldc;
+    const float* bias;
+    int M, N, K;
+    int kblocks_per_split;   // BLOCK_K blocks per blockIdx.z
+    int mode;                // 0 store, 1 C += (no atomics), 2 atomicAdd (split-K)
+    int a_mn, b_mn;          // 1: operand is MN-major in global memory
+};
+
+template <int BN, int STAGES>
+struct GemmTcSmem {
+    static constexpr int A_BYTES = GT_BM * GT_BK * 2;       // 16 KB
+    static constexpr int B_BYTES = BN * GT_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+    static constexpr int TOTAL = BAR_OFF + 256 + 1024;       // + barriers/slot + alignment slack
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                  const __grid_constant__ CUtensorMap tmB,
+                                                                  GemmTcArgs g) {
+    using L = GemmTcSmem<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full = empty_bar + STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * GT_BM, n0 = blockIdx.x * BN;
+    const int total_kb = ceil_div(g.K, GT_BK);
+    const int kb0 = blockIdx.z * g.kblocks_per_split;
+    const int nkb = min(g.kblocks_per_split, total_kb - kb0);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                const uint32_t ph = (i / STAGES) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                uint8_t* sa = smem + s * L::STAGE_BYTES;
+                uint8_t* sb = sa + L::A_BYTES;
+                mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
+                const int k0 = (kb0 + i) * GT_BK;
+                if (!g.a_mn) {
+                    tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < GT_BM / 64; ++j) tma_load_2d(sa + j * 8192, &tmA, &full_bar[s], m0 + 64 * j, k0);
+                }
+                if (!g.b_mn) {
+                    tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * 8192, &tmB, &full_bar[s], n0 + 64 * j, k0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (single thread) =====
+        if (lane == 0) {
+            const uint32_t idesc = idesc_bf16(GT_BM, BN, g.a_mn, g.b_mn);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                const uint32_t ph = (i / STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + s * L::STAGE_BYTES);
+                const uint32_t sb = sa + L::A_BYTES;
+#pragma unroll
+                for (int k = 0; k < GT_BK / 16; ++k) {
+                    const uint64_t ad = g.a_mn ? desc_mnmajor(sa + k * 2048, 8192) : desc_kmajor(sa + k * 32);
+                    const uint64_t bd = g.b_mn ? desc_mnmajor(sb + k * 2048, 8192) : desc_kmajor(sb + k * 32);
+                    mma_bf16(tmem_base, ad, bd, idesc, (i | k) != 0);
+                }
+                mma_commit(&empty_bar[s]);          // frees the smem slot once these MMAs retire
+            }
+            mma_commit(tmem_full);                  // accumulator complete
+        }
+    } else {
+        // ===== epilogue: TMEM -> registers -> global =====
+        const int q = warp & 3;                     // TMEM lane quarter this warp may access
+        const int m = m0 + 32 * q + lane;
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        float v[32];
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            const int nb = n0 + c * 32;
+            if (nb >= g.N) break;                   // warp-uniform
+            tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(c * 32), v);
+            if (m < g.M && nkb > 0) {
+                float* crow = g.C + (int64_t)m * g.ldc + nb;
+                const bool add_bias = g.bias != nullptr && blockIdx.z == 0;
+                const bool vec = (nb + 32 <= g.N) && ((g.ldc & 3) == 0) && (((uintptr_t)g.C & 15) == 0) && g.mode != 2;
+                if (vec) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        if (add_bias) {
+                            float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + nb + j));
+                            o.x += b4.x; o.y += b4.y; o.z += b4.z; o.w += b4.w;
+                        }
+                        float4* dst = reinterpret_cast<float4*>(crow + j);
+                        if (g.mode == 1) { float4 old = *dst; o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w; }
+                        *dst = o;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (nb + j < g.N) {
+                            float o = v[j];
+                            if (add_bias) o += __ldg(g.bias + nb + j);
+                            if (g.mode == 2) atomicAdd(crow + j, o);
+                            else if (g.mode == 1) crow[j] += o;
+                            else crow[j] = o;
+                        }
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN);
+    }
+}
+
+// Host launcher.  A: op(A) is [M,K]; a_mn = 0 -> stored [M,K] row-major (lda), a_mn = 1 -> stored
+// [K,M] row-major.  B: op(B) is [K,N]; b_mn = 0 -> stored [N,K] row-major (i.e. B^T), b_mn = 1 ->
+// stored [K,N] row-major.  accumulate = 1 adds into C (split-K with atomics when that fills the GPU).
+inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda, int a_mn,
+                        const __nv_bfloat16* B, int64_t ldb, int b_mn, float* C, int64_t ldc,
+                        const float* bias, int accumulate, cudaStream_t st, int sm_count = 148) {
+    if (M <= 0 || N <= 0) return CRNN_OK;
+    if (K <= 0) return set_err(CRNN_ERR_ARG, "gemm_bf16_tc: K must be positive");
+    constexpr int BN = 128, STAGES = 3;
+    using L = GemmTcSmem<BN, STAGES>;
+    CUtensorMap tmA, tmB;
+    int rc = a_mn ? make_tmap_bf16(&tmA, A, K, M, lda, 64) : make_tmap_bf16(&tmA, A, M, K, lda, GT_BM);
+    if (rc != CRNN_OK) return rc;
+    rc = b_mn ? make_tmap_bf16(&tmB, B, K, N, ldb, 64) : make_tmap_bf16(&tmB, B, N, K, ldb, BN);
+    if (rc != CRNN_OK) return rc;
+    GemmTcArgs g;
+    g.C = C; g.ldc = ldc; g.bias = bias; g.M = M; g.N = N; g.K = K; g.a_mn = a_mn; g.b_mn = b_mn;
+    dim3 grid(ceil_div(N, BN), ceil_div(M, GT_BM), 1);
+    const int total_kb = ceil_div(K, GT_BK);
+    int splits = 1;
+    const int64_t tiles = (int64_t)grid.x * grid.y;
+    if (accumulate && tiles < 2 * sm_count && total_kb >= 16)
+        splits = (int)std::min<int64_t>(ceil_div64(2 * sm_count, tiles), total_kb / 8);
+    splits = std::max(1, splits);
+    g.kblocks_per_split = ceil_div(total_kb, splits);
+    grid.z = ceil_div(total_kb, g.kblocks_per_split);
+    g.mode = accumulate ? (grid.z > 1 ? 2 : 1) : 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+        attr_set = true;
+    }
+    gemm_bf16_tc_kernel<BN, STAGES><<<grid, GT_THREADS, L::TOTAL, st>>>(tmA, tmB, g);
+    CRNN_LAUNCH_CHECK("gemm_bf16_tc_kernel");
+    return CRNN_OK;
+}
+
+// fp32 -> bf16 cast of a row-major matrix (optionally re-pitched): the bf16 shadow copies.
+__global__ void __launch_bounds__(256) cast_bf16_kernel(const float* __restrict__ src, int64_t lds, int64_t rows, int cols,
+                                                        __nv_bfloat16* __restrict__ dst, int64_t ldd) {
+    const int64_t n = rows * cols;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = i / cols;
+        int c = (int)(i % cols);
+        dst[r * ldd + c] = __float2bfloat16_rn(src[r * lds + c]);
+    }
+}
+
+}  // namespace tc
+}  // namespace crnn

@@ -24,6 +24,7 @@ constexpr int REC_LDA = REC_KC + 4;
 struct RecArgs {
     int B, H, S;
     int HC, BT, nslices, ntiles;
+    int TXa, TXb;           // thread columns for contractions with G*HC / HC output columns
     int GS;                 // gate-stash row width in units of H
     const float* W;         // lstm/rnn kernel [2H, G*H]; gru gates/kernel [2H, 2H]
     const float* Wc;        // gru candidate/kernel [2H, H]
@@ -37,31 +38,32 @@ struct RecArgs {
     unsigned* barrier;      // zeroed before launch
 };
 
-// acc[i] (rows ty + i*TY) += A_s[row][k] * W_s[k][lc]
-template <int TX>
-struct Strip {
-    static constexpr int TY = REC_THREADS / TX;
-    static constexpr int RM = REC_RB / TY;
-};
+constexpr int REC_RM_MAX = 16;   // rows per thread (REC_RB / (REC_THREADS / 64))
 
-// Z_s[r][lc] = sum_k A[(r)*lda + k] * W_s[k*ldw + wcol0 + lc]   for r < nrows, lc < NC.
-// A is global (produced by other CTAs in the previous phase -> read through L2).
-template <int TX>
-__device__ __forceinline__ void cta_gemm(float* __restrict__ Zs, int ldz, const float* __restrict__ A,
-                                         int64_t lda, int nrows, int K, const float* __restrict__ Ws,
-                                         int ldw, int wcol0, int NC, float* __restrict__ As) {
-    constexpr int TY = Strip<TX>::TY, RM = Strip<TX>::RM;
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, int src_bytes) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Stage A[nrows][kc .. kc+kl) into one As buffer ([rows_pad][REC_LDA], zero padded).
+// vec: rows are 16-byte aligned -> cp.async (L2 -> shared, no register staging, all in flight).
+__device__ __forceinline__ void stage_a(float* __restrict__ As, const float* __restrict__ A, int64_t lda,
+                                        int nrows, int rows_pad, int kc, int kl, bool vec) {
     const int tid = threadIdx.x;
-    const int lc = tid % TX, ty = tid / TX;
-    const int nrm = min(RM, ceil_div(nrows, TY));
-    float acc[RM];
-#pragma unroll
-    for (int i = 0; i < RM; ++i) acc[i] = 0.f;
-    for (int kc = 0; kc < K; kc += REC_KC) {
-        const int kl = min(REC_KC, K - kc);
+    if (vec) {
+        const int n4 = (kl + 3) >> 2;
+        for (int idx = tid; idx < rows_pad * (REC_KC / 4); idx += REC_THREADS) {
+            int r = idx / (REC_KC / 4), k4 = idx % (REC_KC / 4);
+            if (k4 < n4) {
+                const bool ok = r < nrows;
+                cp_async16(As + r * REC_LDA + k4 * 4, ok ? A + (int64_t)r * lda + kc + k4 * 4 : A, ok ? 16 : 0);
+            }
+        }
+    } else {
         const int kl4 = (kl + 3) & ~3;
-        // stage A[nrows][kl] -> As (zero padded to kl4 and to nrm*TY rows)
-        const int rows_pad = nrm * TY;
         for (int idx = tid; idx < rows_pad * REC_KC; idx += REC_THREADS) {
             int r = idx / REC_KC, k = idx % REC_KC;
             if (k < kl4) {
@@ -70,20 +72,55 @@ __device__ __forceinline__ void cta_gemm(float* __restrict__ Zs, int ldz, const 
                 As[r * REC_LDA + k] = v;
             }
         }
+    }
+}
+
+// Z_s[r][lc] = sum_k A[r*lda + k] * W_s[k*ldw + wcol0 + lc]   for r < nrows (<= REC_RB), lc < NC.
+// A is global (written by other CTAs in the previous phase -> read through L2, never L1).
+// TX (power of two, 4..64) threads span the columns, 256/TX thread rows span the batch rows,
+// RM rows per thread (compile-time so that no predicated-off FFMA is issued);
+// the K loop is double-buffered with cp.async so the next chunk lands during the FFMAs.
+template <int RM>
+__device__ __forceinline__ void cta_gemm_rm(int TX, float* __restrict__ Zs, int ldz, const float* __restrict__ A,
+                                            int64_t lda, int nrows, int K, const float* __restrict__ Ws,
+                                            int ldw, int wcol0, int NC, float* __restrict__ As, bool vec) {
+    const int TY = REC_THREADS / TX;
+    const int tid = threadIdx.x;
+    const int lc = tid % TX, ty = tid / TX;
+    const int rows_pad = RM * TY;
+    float acc[RM];
+#pragma unroll
+    for (int i = 0; i < RM; ++i) acc[i] = 0.f;
+    const int nchunk = ceil_div(K, REC_KC);
+    stage_a(As, A, lda, nrows, rows_pad, 0, min(REC_KC, K), vec);
+    cp_async_commit();
+    for (int c = 0; c < nchunk; ++c) {
+        const int kc = c * REC_KC;
+        const int kl = min(REC_KC, K - kc);
+        const int kl4 = (kl + 3) & ~3;
+        float* cur = As + (c & 1) * (REC_RB * REC_LDA);
+        if (c + 1 < nchunk) {
+            stage_a(As + ((c + 1) & 1) * (REC_RB * REC_LDA), A, lda, nrows, rows_pad, kc + REC_KC,
+                    min(REC_KC, K - kc - REC_KC), vec);
+            cp_async_commit();
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
         __syncthreads();
         if (lc < NC) {
             const float* w = Ws + (int64_t)kc * ldw + wcol0 + lc;
+            const float* arow = cur + ty * REC_LDA;
+#pragma unroll 2
             for (int k = 0; k < kl4; k += 4) {
                 float w0 = w[(k + 0) * ldw], w1 = w[(k + 1) * ldw], w2 = w[(k + 2) * ldw], w3 = w[(k + 3) * ldw];
 #pragma unroll
                 for (int i = 0; i < RM; ++i) {
-                    if (i < nrm) {
-                        float4 a = *reinterpret_cast<const float4*>(&As[(ty + i * TY) * REC_LDA + k]);
-                        acc[i] = fmaf(a.x, w0, acc[i]);
-                        acc[i] = fmaf(a.y, w1, acc[i]);
-                        acc[i] = fmaf(a.z, w2, acc[i]);
-                        acc[i] = fmaf(a.w, w3, acc[i]);
-                    }
+                    float4 a = *reinterpret_cast<const float4*>(&arow[i * TY * REC_LDA + k]);
+                    acc[i] = fmaf(a.x, w0, acc[i]);
+                    acc[i] = fmaf(a.y, w1, acc[i]);
+                    acc[i] = fmaf(a.z, w2, acc[i]);
+                    acc[i] = fmaf(a.w, w3, acc[i]);
                 }
             }
         }
@@ -93,10 +130,21 @@ __device__ __forceinline__ void cta_gemm(float* __restrict__ Zs, int ldz, const 
 #pragma unroll
         for (int i = 0; i < RM; ++i) {
             int r = ty + i * TY;
-            if (i < nrm && r < nrows) Zs[r * ldz + lc] = acc[i];
+            if (r < nrows) Zs[r * ldz + lc] = acc[i];
         }
     }
     __syncthreads();
+}
+
+__device__ __forceinline__ void cta_gemm(int TX, float* __restrict__ Zs, int ldz, const float* __restrict__ A,
+                                         int64_t lda, int nrows, int K, const float* __restrict__ Ws,
+                                         int ldw, int wcol0, int NC, float* __restrict__ As, bool vec) {
+    const int nrm = ceil_div(nrows, REC_THREADS / TX);       // block-uniform
+    if (nrm <= 1)      cta_gemm_rm<1>(TX, Zs, ldz, A, lda, nrows, K, Ws, ldw, wcol0, NC, As, vec);
+    else if (nrm <= 2) cta_gemm_rm<2>(TX, Zs, ldz, A, lda, nrows, K, Ws, ldw, wcol0, NC, As, vec);
+    else if (nrm <= 4) cta_gemm_rm<4>(TX, Zs, ldz, A, lda, nrows, K, Ws, ldw, wcol0, NC, As, vec);
+    else if (nrm <= 8) cta_gemm_rm<8>(TX, Zs, ldz, A, lda, nrows, K, Ws, ldw, wcol0, NC, As, vec);
+    else               cta_gemm_rm<16>(TX, Zs, ldz, A, lda, nrows, K, Ws, ldw, wcol0, NC, As, vec);
 }
 
 // Copy a slice of a row-major weight matrix into shared memory.
@@ -127,7 +175,7 @@ __device__ __forceinline__ void load_w_slice(float* Ws, int ldw, const float* __
 // ------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------
-template <int MODEL, int TX>
+template <int MODEL>
 __global__ void __launch_bounds__(REC_THREADS, 1) rec_fwd_kernel(RecArgs a) {
     extern __shared__ __align__(16) float smem[];
     const int B = a.B, H = a.H, HC = a.HC;
@@ -140,10 +188,11 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_fwd_kernel(RecArgs a) {
     float* Wsa = smem;                            // [K4][NCA]
     float* Wsb = Wsa + (size_t)K4 * NCA;          // gru: [K4][HC]
     float* As = Wsb + (MODEL == CRNN_MODEL_GRU ? (size_t)K4 * HC : 0);
-    float* Zs = As + REC_RB * REC_LDA;            // [REC_RB][NCA+1]
+    float* Zs = As + 2 * REC_RB * REC_LDA;        // [REC_RB][NCA+1]
     const int ldz = NCA + 1;
     const int64_t gw = (int64_t)a.GS * H;         // gate-stash row width
     const int64_t BH = (int64_t)B * H;
+    const bool vec = (H & 3) == 0;                // 16-byte aligned rows -> cp.async staging
 
     if (MODEL == CRNN_MODEL_LSTM) load_w_slice(Wsa, NCA, a.W, 4 * H, H, H, 4, H, j0, hc, HC, 0);
     if (MODEL == CRNN_MODEL_RNN)  load_w_slice(Wsa, NCA, a.W, H, H, H, 1, H, j0, hc, HC, 0);
@@ -160,7 +209,7 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_fwd_kernel(RecArgs a) {
         float* gt = a.gates + (int64_t)t * B * gw;
         for (int r0 = 0; r0 < bt; r0 += REC_RB) {
             const int nr = min(REC_RB, bt - r0);
-            cta_gemm<TX>(Zs, ldz, hprev + (int64_t)(b0 + r0) * H, H, nr, H, Wsa, NCA, 0, NCA, As);
+            cta_gemm(a.TXa, Zs, ldz, hprev + (int64_t)(b0 + r0) * H, H, nr, H, Wsa, NCA, 0, NCA, As, vec);
             for (int idx = threadIdx.x; idx < nr * hc; idx += REC_THREADS) {
                 const int r = idx / hc, jj = idx % hc;
                 const int64_t b = b0 + r0 + r;
@@ -195,7 +244,7 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_fwd_kernel(RecArgs a) {
             grid_barrier(a.barrier, (++bar) * gridDim.x);
             for (int r0 = 0; r0 < bt; r0 += REC_RB) {
                 const int nr = min(REC_RB, bt - r0);
-                cta_gemm<TX>(Zs, ldz, gt + (int64_t)(b0 + r0) * gw + 3 * H, gw, nr, H, Wsb, HC, 0, HC, As);
+                cta_gemm(a.TXb, Zs, ldz, gt + (int64_t)(b0 + r0) * gw + 3 * H, gw, nr, H, Wsb, HC, 0, HC, As, vec);
                 for (int idx = threadIdx.x; idx < nr * hc; idx += REC_THREADS) {
                     const int r = idx / hc, jj = idx % hc;
                     const int64_t b = b0 + r0 + r;
@@ -218,7 +267,7 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_fwd_kernel(RecArgs a) {
 // backward (BPTT).  dh_t = dy_t + (pre-activation grads of step t+1) * W_h^T, so the
 // CTA keeps rows [j0, j0+HC) of W_h (transposed) resident instead.
 // ------------------------------------------------------------------------------------
-template <int MODEL, int TX>
+template <int MODEL>
 __global__ void __launch_bounds__(REC_THREADS, 1) rec_bwd_kernel(RecArgs a) {
     extern __shared__ __align__(16) float smem[];
     const int B = a.B, H = a.H, HC = a.HC;
@@ -232,11 +281,12 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_bwd_kernel(RecArgs a) {
     float* Wsa = smem;                            // [KA4][HC]   W_h^T slice (gru: gates)
     float* Wsb = Wsa + (size_t)KA4 * HC;          // gru: [K4][HC] candidate W_h^T slice
     float* As = Wsb + (MODEL == CRNN_MODEL_GRU ? (size_t)K4 * HC : 0);
-    float* Zs = As + REC_RB * REC_LDA;            // [REC_RB][HC+1]
+    float* Zs = As + 2 * REC_RB * REC_LDA;        // [REC_RB][HC+1]
     const int ldz = HC + 1;
     const int64_t gw = (int64_t)a.GS * H;
     const int64_t zw = (int64_t)GZ * H;
     const int64_t BH = (int64_t)B * H;
+    const bool vec = (H & 3) == 0;
 
     load_w_slice(Wsa, HC, a.W, (int64_t)G * H, H, KA, 1, 0, j0, hc, HC, 1);
     if (MODEL == CRNN_MODEL_GRU) load_w_slice(Wsb, HC, a.Wc, H, H, H, 1, 0, j0, hc, HC, 1);
@@ -257,7 +307,7 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_bwd_kernel(RecArgs a) {
         const bool has_next = (t + 1 < a.S);
         for (int r0 = 0; r0 < bt; r0 += REC_RB) {
             const int nr = min(REC_RB, bt - r0);
-            if (has_next) cta_gemm<TX>(Zs, ldz, dzn + (int64_t)(b0 + r0) * zw, zw, nr, KA, Wsa, HC, 0, HC, As);
+            if (has_next) cta_gemm(a.TXb, Zs, ldz, dzn + (int64_t)(b0 + r0) * zw, zw, nr, KA, Wsa, HC, 0, HC, As, vec);
             for (int idx = threadIdx.x; idx < nr * hc; idx += REC_THREADS) {
                 const int r = idx / hc, jj = idx % hc;
                 const int64_t b = b0 + r0 + r;
@@ -295,7 +345,7 @@ __global__ void __launch_bounds__(REC_THREADS, 1) rec_bwd_kernel(RecArgs a) {
             grid_barrier(a.barrier, (++bar) * gridDim.x);
             for (int r0 = 0; r0 < bt; r0 += REC_RB) {
                 const int nr = min(REC_RB, bt - r0);
-                cta_gemm<TX>(Zs, ldz, dzt + (int64_t)(b0 + r0) * zw + 2 * H, zw, nr, H, Wsb, HC, 0, HC, As);
+                cta_gemm(a.TXb, Zs, ldz, dzt + (int64_t)(b0 + r0) * zw + 2 * H, zw, nr, H, Wsb, HC, 0, HC, As, vec);
                 for (int idx = threadIdx.x; idx < nr * hc; idx += REC_THREADS) {
                     const int r = idx / hc, jj = idx % hc;
                     const int64_t b = b0 + r0 + r;

@@ -148,6 +148,15 @@ int crnn_gemm_f32(int32_t ta, int32_t tb, int32_t M, int32_t N, int32_t K,
                   const float* d_A, int64_t lda, const float* d_B, int64_t ldb,
                   float* d_C, int64_t ldc, const float* d_bias, int32_t accumulate, void* stream);
 
+/* The tensor-core form of the same contraction (CRNN_PREC_BF16): bf16 operands, fp32
+ * accumulate (tcgen05.mma kind::f16), C fp32.  op(A) is [M,K]: a_mn = 0 -> A stored [M,K]
+ * row-major, a_mn = 1 -> stored [K,M] row-major.  op(B) is [K,N]: b_mn = 0 -> stored [N,K]
+ * row-major, b_mn = 1 -> stored [K,N] row-major.  Leading dimensions are in elements and
+ * must be multiples of 8 (16-byte rows for TMA).                                          */
+int crnn_gemm_bf16(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K,
+                   const void* d_A_bf16, int64_t lda, const void* d_B_bf16, int64_t ldb,
+                   float* d_C, int64_t ldc, const float* d_bias, int32_t accumulate, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
