@@ -6,6 +6,7 @@
 #include "recurrence_simt.cuh"
 #include "elementwise.cuh"
 #include "gemm_tc.cuh"
+#include "recurrence_tc.cuh"
 
 #include <stdarg.h>
 #include <stdlib.h>
@@ -43,7 +44,15 @@ struct WsPlan {
     size_t x0;
     std::vector<size_t> hx, cx, gates;
     size_t dz, dya, dyb, carry0, carry1, logits;
+    // CRNN_PREC_BF16 only: bf16 MMA operands
+    size_t pbf, wsmb, x0b, dzb, dlb;
+    std::vector<size_t> wr, hxb, rsb;
     size_t total;
+};
+
+struct RecPlanTc {
+    int HC, BT, nslices, ntiles, npass, box_rows;
+    size_t smem_fwd, smem_bwd;
 };
 
 }  // namespace crnn
@@ -60,6 +69,9 @@ struct crnn_handle {
     int64_t P;
     int64_t emb_off;
     RecPlan fwd, bwd;
+    RecPlanTc tcp;
+    int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
+    int fast_act;
     WsPlan ws;
     int sm_count;
     int max_smem;
@@ -153,6 +165,45 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
     return CRNN_OK;
 }
 
+// Decomposition of the tensor-core recurrence kernels: HC hidden units (multiple of 16) per slice,
+// BT batch rows per tile.  The resident weight slice (2*GW*H*HC bytes) plus the 64 KB A ring must
+// fit in shared memory; one CTA per SM, all co-resident.
+static int plan_recurrence_tc(const crnn_handle* h, RecPlanTc* out) {
+    const int H = h->cfg.rnn_size, B = h->cfg.batch_size, model = h->cfg.model;
+    if (H % 16 != 0) return set_err(CRNN_ERR_UNSUP, "CRNN_PREC_BF16 needs rnn_size %% 16 == 0 (got %d)", H);
+    const int GW = h->G;
+    const int g1 = model == CRNN_MODEL_LSTM ? 4 : (model == CRNN_MODEL_GRU ? 2 : 1);
+    const int max_ctas = h->sm_count;
+    const int nkb = ceil_div(H, 64);
+    const int64_t wbudget = (int64_t)h->max_smem - tc::RT_STAGES * tc::RT_ASTAGE - 2048;
+    int hc_smem = (int)(wbudget / ((int64_t)nkb * 128 * GW + (model == CRNN_MODEL_GRU ? 0 : 0)));
+    // backward resident slice: ceil(g1*H/64) (+ ceil(H/64) for gru) blocks of HC*128 bytes
+    const int nkb_b = ceil_div(g1 * H, 64) + (model == CRNN_MODEL_GRU ? nkb : 0);
+    hc_smem = std::min(hc_smem, (int)(wbudget / ((int64_t)nkb_b * 128)));
+    int HC = std::min(std::min(hc_smem, 256 / g1), H) & ~15;
+    if (HC < 16) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory", H);
+    // enough slices that every SM has work even with few batch tiles; enough tiles to keep A loads short
+    int want_tiles = std::max(1, std::min(ceil_div(B, 32), max_ctas));
+    while (HC > 16 && ceil_div(H, HC) * want_tiles < max_ctas / 2) HC -= 16;
+    int hc_env = env_int("CRNN_TC_HC", 0);
+    if (hc_env >= 16) HC = std::min(hc_env & ~15, std::min(std::min(hc_smem, 256 / g1), H) & ~15);
+    int nslices = ceil_div(H, HC);
+    if (nslices > max_ctas) return set_err(CRNN_ERR_UNSUP, "rnn_size %d needs %d slices > %d SMs", H, nslices, max_ctas);
+    int ntiles = std::max(1, std::min(max_ctas / nslices, ceil_div(B, 16)));
+    int nt_env = env_int("CRNN_TC_TILES", 0);
+    if (nt_env > 0) ntiles = std::max(1, std::min(nt_env, max_ctas / nslices));
+    int BT = ceil_div(B, ntiles);
+    ntiles = ceil_div(B, BT);
+    out->HC = HC; out->BT = BT; out->nslices = nslices; out->ntiles = ntiles;
+    out->npass = ceil_div(BT, 128);
+    out->box_rows = out->npass > 1 ? 128 : std::min(128, (BT + 7) & ~7);
+    out->smem_fwd = tc::rt_smem_bytes((size_t)nkb * g1 * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
+    out->smem_bwd = tc::rt_smem_bytes((size_t)ceil_div(g1 * H, 64) * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
+    if ((int)std::max(out->smem_fwd, out->smem_bwd) > h->max_smem)
+        return set_err(CRNN_ERR_UNSUP, "tensor-core recurrence needs %zu B shared memory > %d", std::max(out->smem_fwd, out->smem_bwd), h->max_smem);
+    return CRNN_OK;
+}
+
 static void build_layout(crnn_handle* h) {
     const int H = h->cfg.rnn_size, V = h->cfg.vocab_size, L = h->cfg.num_layers;
     int64_t off = 0;
@@ -202,6 +253,20 @@ static void build_workspace(crnn_handle* h) {
     w.carry0 = take(B * H);
     w.carry1 = take(B * H);
     w.logits = take(S * B * V);
+    if (h->cfg.precision == CRNN_PREC_BF16) {
+        auto take2 = [&](int64_t halves) { return take((halves + 1) / 2); };
+        const int64_t GW = h->G;
+        w.pbf = take2(h->P);
+        w.wsmb = take2(H * h->Vp);
+        w.x0b = take2(S * B * H);
+        for (int l = 0; l < L; ++l) {
+            w.wr.push_back(take2((int64_t)h->tcp.nslices * GW * h->tcp.HC * H));
+            w.hxb.push_back(take2((S + 1) * B * H));
+            w.rsb.push_back(h->cfg.model == CRNN_MODEL_GRU ? take2(S * B * H) : 0);
+        }
+        w.dzb = take2((S + 1) * B * h->GZ * H);
+        w.dlb = take2(S * B * h->Vp);
+    }
     w.total = off;
 }
 
@@ -219,8 +284,6 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         return set_err(CRNN_ERR_ARG, "rnn_size, num_layers, seq_length, batch_size and vocab_size must be >= 1");
     if (cfg->precision != CRNN_PREC_FP32 && cfg->precision != CRNN_PREC_BF16)
         return set_err(CRNN_ERR_ARG, "unknown precision %d", cfg->precision);
-    if (cfg->precision == CRNN_PREC_BF16)
-        return set_err(CRNN_ERR_UNSUP, "CRNN_PREC_BF16 is not built in this version");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {
@@ -246,6 +309,9 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     build_layout(h);
     int rc = plan_recurrence(h, false, &h->fwd);
     if (rc == CRNN_OK) rc = plan_recurrence(h, true, &h->bwd);
+    h->Vp = (cfg->vocab_size + 7) & ~7;
+    h->fast_act = env_int("CRNN_FAST_ACT", 1);
+    if (rc == CRNN_OK && cfg->precision == CRNN_PREC_BF16) rc = plan_recurrence_tc(h, &h->tcp);
     if (rc != CRNN_OK) { delete h; return rc; }
     build_workspace(h);
     *out = h;
@@ -358,7 +424,7 @@ static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const floa
     float* x0 = wsf(ws, h->ws.x0);
     const float* emb = params + h->emb_off;
     prof_mark(h, st, CRNN_PHASE_EMBED_GATHER);
-    embed_gather_kernel<<<grid_for(SB * H / 4 + 1, h->sm_count), 256, 0, st>>>(emb, V, H, x, ldx, B, S, x0);
+    embed_gather_kernel<<<grid_for(SB * H / 4 + 1, h->sm_count), 256, 0, st>>>(emb, V, H, x, ldx, B, S, x0, nullptr);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 256, st));
@@ -413,6 +479,227 @@ static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const floa
     return rc;
 }
 
+
+// ======================================================================================
+// CRNN_PREC_BF16: tensor-core path.  Same phase structure as the fp32 path; every
+// contraction runs on tcgen05 with bf16 operands that the producing kernels wrote.
+// ======================================================================================
+typedef __nv_bfloat16 bf16_t;
+static inline bf16_t* wsb(void* ws, size_t off) { return reinterpret_cast<bf16_t*>((char*)ws + off); }
+
+template <int MODEL>
+static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const bf16_t* pbf_W, const bf16_t* pbf_Wc,
+                         const bf16_t* wr, cudaStream_t st) {
+    const RecPlanTc& p = h->tcp;
+    const int H = h->cfg.rnn_size, S = h->cfg.seq_length, B = h->cfg.batch_size;
+    const int g1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
+    const int GW = h->G, GZ = h->GZ;
+    a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles; a.npass = p.npass; a.box_rows = p.box_rows;
+    a.fast_act = h->fast_act;
+    CUtensorMap t0, t1, w0, w1;
+    int rc;
+    if (!backward) {
+        rc = tc::make_tmap_bf16(&t0, a.hxb, (int64_t)(S + 1) * B, H, H, p.box_rows);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&t1, a.rsb, (int64_t)S * B, H, H, p.box_rows) : (t1 = t0, CRNN_OK);
+        if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, wr, (int64_t)p.nslices * GW * p.HC, H, H, g1 * p.HC);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, wr, (int64_t)p.nslices * GW * p.HC, H, H, p.HC) : (w1 = w0, CRNN_OK);
+    } else {
+        const int64_t zw = (int64_t)GZ * H;
+        rc = tc::make_tmap_bf16(&t0, a.dzb, (int64_t)(S + 1) * B, (int64_t)g1 * H, zw, p.box_rows);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&t1, a.dzb + 2 * H, (int64_t)(S + 1) * B, H, zw, p.box_rows) : (t1 = t0, CRNN_OK);
+        if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, pbf_W, 2 * H, (int64_t)g1 * H, (int64_t)g1 * H, p.HC);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, pbf_Wc, 2 * H, H, H, p.HC) : (w1 = w0, CRNN_OK);
+    }
+    if (rc != CRNN_OK) return rc;
+    void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
+        backward ? tc::rec_bwd_tc_kernel<MODEL> : tc::rec_fwd_tc_kernel<MODEL>;
+    const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
+    CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    void* args[] = {&t0, &t1, &w0, &w1, &a};
+    CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(tc::RT_THREADS), args, smem, st));
+    ++g_launches;
+    return CRNN_OK;
+}
+
+static int launch_rec_tc_model(crnn_handle* h, bool backward, tc::RecTcArgs& a, const bf16_t* W, const bf16_t* Wc,
+                               const bf16_t* wr, cudaStream_t st) {
+    switch (h->cfg.model) {
+        case CRNN_MODEL_LSTM: return launch_rec_tc<CRNN_MODEL_LSTM>(h, backward, a, W, Wc, wr, st);
+        case CRNN_MODEL_GRU:  return launch_rec_tc<CRNN_MODEL_GRU>(h, backward, a, W, Wc, wr, st);
+        default:              return launch_rec_tc<CRNN_MODEL_RNN>(h, backward, a, W, Wc, wr, st);
+    }
+}
+
+// bf16 shadows of the parameters: the flat buffer as is (pbf), softmax_w re-pitched to Vp,
+// and the per-layer recurrent halves packed for the forward kernel.
+static int refresh_bf16_params(crnn_handle* h, const float* params, void* ws, cudaStream_t st) {
+    const crnn_config& c = h->cfg;
+    const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers;
+    tc::cast_bf16_kernel<<<grid_for(h->P, h->sm_count), 256, 0, st>>>(params, h->P, 1, (int)h->P, wsb(ws, h->ws.pbf), h->P);
+    CRNN_LAUNCH_CHECK("cast_bf16_kernel");
+    tc::cast_bf16_kernel<<<grid_for((int64_t)H * V, h->sm_count), 256, 0, st>>>(params + h->tensors[0].offset, V, H, V, wsb(ws, h->ws.wsmb), h->Vp);
+    CRNN_LAUNCH_CHECK("cast_bf16_kernel");
+    const int g1 = c.model == CRNN_MODEL_LSTM ? 4 : (c.model == CRNN_MODEL_GRU ? 2 : 1);
+    for (int l = 0; l < L; ++l) {
+        const int per = c.model == CRNN_MODEL_GRU ? 4 : 2;
+        const float* W = params + h->tensors[3 + l * per].offset;
+        const float* Wc = per == 4 ? params + h->tensors[3 + l * per + 2].offset : nullptr;
+        const int64_t n = (int64_t)h->tcp.nslices * h->G * h->tcp.HC * H;
+        tc::pack_rec_weights_kernel<<<grid_for(n, h->sm_count), 256, 0, st>>>(W, Wc, H, h->tcp.HC, h->tcp.nslices, g1, h->G, H, wsb(ws, h->ws.wr[l]));
+        CRNN_LAUNCH_CHECK("pack_rec_weights_kernel");
+    }
+    return CRNN_OK;
+}
+
+static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
+                            const float* params, void* ws, cudaStream_t st) {
+    const crnn_config& c = h->cfg;
+    const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
+    const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
+    const int gw = h->GS * H;
+    const int sc = h->sm_count;
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    int rc = refresh_bf16_params(h, params, ws, st);
+    if (rc != CRNN_OK) return rc;
+    const bf16_t* pbf = wsb(ws, h->ws.pbf);
+    float* x0 = wsf(ws, h->ws.x0);
+    bf16_t* x0b = wsb(ws, h->ws.x0b);
+    prof_mark(h, st, CRNN_PHASE_EMBED_GATHER);
+    embed_gather_kernel<<<grid_for(SB * H / 4 + 1, sc), 256, 0, st>>>(params + h->emb_off, V, H, x, ldx, B, S, x0, x0b);
+    CRNN_LAUNCH_CHECK("embed_gather_kernel");
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 256, st));
+    for (int l = 0; l < L; ++l) {
+        LayerParams lp = layer_params(h, params, l);
+        float* hx = wsf(ws, h->ws.hx[l]);
+        float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
+        float* gates = wsf(ws, h->ws.gates[l]);
+        bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
+        const bf16_t* inb = l == 0 ? x0b : wsb(ws, h->ws.hxb[l - 1]) + BH;
+        const float* sin = state_in + (int64_t)l * h->nstate * BH;
+        const float* hin = c.model == CRNN_MODEL_LSTM ? sin + BH : sin;
+        if (c.model == CRNN_MODEL_LSTM) CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, st));
+        CRNN_CUDA(cudaMemcpyAsync(hx, hin, BH * 4, cudaMemcpyDeviceToDevice, st));
+        tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, st>>>(hin, H, B, H, hxb, H);
+        CRNN_LAUNCH_CHECK("cast_bf16_kernel");
+        prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
+        // x half of [x,h]*W for all S steps: A = inputs (K-major), B = kernel rows 0..H stored [K,N]
+        if (c.model == CRNN_MODEL_GRU) {
+            rc = tc::gemm_bf16_tc((int)SB, 2 * H, H, inb, H, 0, pbf + lp.oW, 2 * H, 1, gates, gw, lp.b, 0, st, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, H, inb, H, 0, pbf + lp.oWc, H, 1, gates + 2 * H, gw, lp.bc, 0, st, sc);
+        } else {
+            const int GH = h->G * H;
+            rc = tc::gemm_bf16_tc((int)SB, GH, H, inb, H, 0, pbf + lp.oW, GH, 1, gates, gw, lp.b, 0, st, sc);
+        }
+        if (rc != CRNN_OK) return rc;
+        tc::RecTcArgs a{};
+        a.B = B; a.H = H; a.S = S; a.GS = h->GS;
+        a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
+        a.rsb = c.model == CRNN_MODEL_GRU ? wsb(ws, h->ws.rsb[l]) : nullptr;
+        a.barrier = ws_barrier(ws, 2 * l);
+        prof_mark(h, st, CRNN_PHASE_REC_FWD);
+        rc = launch_rec_tc_model(h, false, a, nullptr, nullptr, wsb(ws, h->ws.wr[l]), st);
+        if (rc != CRNN_OK) return rc;
+        prof_mark(h, st, CRNN_PHASE_MISC);
+        float* sout = state_out + (int64_t)l * h->nstate * BH;
+        if (c.model == CRNN_MODEL_LSTM) {
+            CRNN_CUDA(cudaMemcpyAsync(sout, cx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+            CRNN_CUDA(cudaMemcpyAsync(sout + BH, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+        } else {
+            CRNN_CUDA(cudaMemcpyAsync(sout, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
+    prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
+    rc = tc::gemm_bf16_tc((int)SB, V, H, topb, H, 0, wsb(ws, h->ws.wsmb), h->Vp, 1, wsf(ws, h->ws.logits), V,
+                          params + h->tensors[1].offset, 0, st, sc);
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    return rc;
+}
+
+static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t* y, int64_t ld, const float* state_in,
+                                 float* state_out, const float* params, float* grads, void* ws, cudaStream_t st) {
+    const crnn_config& c = h->cfg;
+    const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
+    const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
+    const int gw = h->GS * H, zw = h->GZ * H, Vp = h->Vp;
+    const int sc = h->sm_count;
+    prof_mark(h, st, CRNN_PHASE_MISC);
+    CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
+    CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
+    int rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st);
+    if (rc != CRNN_OK) return rc;
+    const bf16_t* pbf = wsb(ws, h->ws.pbf);
+    float* logits = wsf(ws, h->ws.logits);
+    bf16_t* dlb = wsb(ws, h->ws.dlb);
+    prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
+    softmax_xent_kernel<<<grid_for(SB * 32, sc), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp);
+    CRNN_LAUNCH_CHECK("softmax_xent_kernel");
+    const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
+    float* dya = wsf(ws, h->ws.dya);
+    float* dyb = wsf(ws, h->ws.dyb);
+    prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
+    // d softmax_w [H,V] = out^T * dlogits ; d softmax_b = colsum ; d out = dlogits * softmax_w^T
+    rc = tc::gemm_bf16_tc(H, V, (int)SB, topb, H, 1, dlb, Vp, 1, grads + h->tensors[0].offset, V, nullptr, 1, st, sc);
+    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
+    if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, V, dlb, Vp, 0, wsb(ws, h->ws.wsmb), Vp, 0, dya, H, nullptr, 0, st, sc);
+    if (rc != CRNN_OK) return rc;
+
+    float* dz = wsf(ws, h->ws.dz);
+    bf16_t* dzb = wsb(ws, h->ws.dzb);
+    float* dcur = dya;
+    float* dnext = dyb;
+    for (int l = L - 1; l >= 0; --l) {
+        LayerParams lp = layer_params(h, params, l);
+        float* hx = wsf(ws, h->ws.hx[l]);
+        float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
+        float* gates = wsf(ws, h->ws.gates[l]);
+        const bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
+        const bf16_t* inb = l == 0 ? wsb(ws, h->ws.x0b) : wsb(ws, h->ws.hxb[l - 1]) + BH;
+        tc::RecTcArgs a{};
+        a.B = B; a.H = H; a.S = S; a.GS = h->GS;
+        a.gates = gates; a.hx = hx; a.cx = cx;
+        a.dy = dcur; a.dz = dz; a.dzb = dzb; a.carry0 = wsf(ws, h->ws.carry0); a.carry1 = wsf(ws, h->ws.carry1);
+        a.barrier = ws_barrier(ws, 2 * l + 1);
+        prof_mark(h, st, CRNN_PHASE_REC_BWD);
+        rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, st);
+        if (rc != CRNN_OK) return rc;
+        prof_mark(h, st, CRNN_PHASE_WEIGHT_GRADS);
+        float* gW = grads + lp.oW;
+        float* gb = grads + lp.ob;
+        if (c.model == CRNN_MODEL_GRU) {
+            float* gWc = grads + lp.oWc;
+            float* gbc = grads + lp.obc;
+            const bf16_t* rsb = wsb(ws, h->ws.rsb[l]);
+            rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, inb, H, 1, dzb, zw, 1, gW, 2 * H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, st);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, inb, H, 1, dzb + 2 * H, zw, 1, gWc, H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, rsb, H, 1, dzb + 2 * H, zw, 1, gWc + (int64_t)H * H, H, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, st);
+            prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, 2 * H, dzb, zw, 0, pbf + lp.oW, 2 * H, 0, dnext, H, nullptr, 0, st, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, H, dzb + 2 * H, zw, 0, pbf + lp.oWc, H, 0, dnext, H, nullptr, 1, st, sc);
+        } else {
+            const int GH = h->G * H;
+            rc = tc::gemm_bf16_tc(H, GH, (int)SB, inb, H, 1, dzb, zw, 1, gW, GH, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, GH, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * GH, GH, nullptr, 1, st, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, st);
+            prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, GH, dzb, zw, 0, pbf + lp.oW, GH, 0, dnext, H, nullptr, 0, st, sc);
+        }
+        if (rc != CRNN_OK) return rc;
+        std::swap(dcur, dnext);
+    }
+    prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
+    embed_scatter_kernel<<<grid_for(SB * H, sc), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, dcur, ws_sq(ws));
+    CRNN_LAUNCH_CHECK("embed_scatter_kernel");
+    finalize_scalars_kernel<<<1, 32, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P);
+    CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
+    prof_mark(h, st, -1);
+    return CRNN_OK;
+}
+
 static int check_common(crnn_handle* h, const void* a, const void* b, const void* c) {
     if (!h) return set_err(CRNN_ERR_ARG, "null handle");
     if (!a || !b || !c) return set_err(CRNN_ERR_ARG, "null device pointer");
@@ -433,6 +720,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     const crnn_config& c = h->cfg;
     if (ld < c.seq_length) return set_err(CRNN_ERR_ARG, "ld_xy %lld < seq_length %d", (long long)ld, c.seq_length);
     cudaStream_t st = (cudaStream_t)stream;
+    if (c.precision == CRNN_PREC_BF16) return forward_backward_bf16(h, x, y, ld, state_in, state_out, params, grads, ws, st);
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H, zw = h->GZ * H;
@@ -446,7 +734,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
 
     // loss + dlogits in place, then the three projection-layer gradients
     float* logits = wsf(ws, h->ws.logits);
-    softmax_xent_kernel<<<grid_for(SB * 32, h->sm_count), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws));
+    softmax_xent_kernel<<<grid_for(SB * 32, h->sm_count), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), nullptr, 0);
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
     const float* top = wsf(ws, h->ws.hx[L - 1]) + BH;
     const float* Wsm = params + h->tensors[0].offset;
@@ -556,7 +844,8 @@ int crnn_forward(crnn_handle* h, const int32_t* x, int64_t ld, const float* stat
     if (ld < c.seq_length) return set_err(CRNN_ERR_ARG, "ld_x %lld < seq_length %d", (long long)ld, c.seq_length);
     cudaStream_t st = (cudaStream_t)stream;
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
-    rc = run_forward(h, x, ld, state_in, state_out, params, ws, st);
+    rc = c.precision == CRNN_PREC_BF16 ? run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st)
+                                       : run_forward(h, x, ld, state_in, state_out, params, ws, st);
     if (rc != CRNN_OK) return rc;
     if (logits_out || probs_out) {
         const int64_t SB = (int64_t)c.seq_length * c.batch_size;
@@ -574,7 +863,7 @@ int crnn_embedding_gather(const float* table, int32_t V, int32_t H, const int32_
     if (!table || !x || !out) return set_err(CRNN_ERR_ARG, "null device pointer");
     if (V < 1 || H < 1 || B < 0 || S < 0) return set_err(CRNN_ERR_ARG, "bad shape");
     if ((int64_t)B * S == 0) return CRNN_OK;
-    embed_gather_kernel<<<grid_for((int64_t)S * B * H / 4 + 1, 148), 256, 0, (cudaStream_t)stream>>>(table, V, H, x, ldx, B, S, out);
+    embed_gather_kernel<<<grid_for((int64_t)S * B * H / 4 + 1, 148), 256, 0, (cudaStream_t)stream>>>(table, V, H, x, ldx, B, S, out, nullptr);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     return CRNN_OK;
 }
@@ -593,7 +882,7 @@ int crnn_softmax_xent(float* logits, int32_t B, int32_t S, int32_t V, const int3
     if (!logits || !y) return set_err(CRNN_ERR_ARG, "null device pointer");
     if (V < 1 || B < 0 || S < 0) return set_err(CRNN_ERR_ARG, "bad shape");
     if ((int64_t)B * S == 0) return CRNN_OK;
-    softmax_xent_kernel<<<grid_for((int64_t)S * B * 32, 148), 256, 0, (cudaStream_t)stream>>>(logits, B, S, V, y, ldy, loss_sum);
+    softmax_xent_kernel<<<grid_for((int64_t)S * B * 32, 148), 256, 0, (cudaStream_t)stream>>>(logits, B, S, V, y, ldy, loss_sum, nullptr, 0);
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
     return CRNN_OK;
 }

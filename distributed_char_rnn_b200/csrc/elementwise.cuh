@@ -9,7 +9,8 @@ namespace crnn {
 // out[t,b,:] = table[x[b,t],:]; one float4 per thread, rows of the (tiny, L2-resident) table.
 __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restrict__ table, int V, int H,
                                                            const int32_t* __restrict__ x, int64_t ldx,
-                                                           int B, int S, float* __restrict__ out) {
+                                                           int B, int S, float* __restrict__ out,
+                                                           __nv_bfloat16* __restrict__ out_bf16) {
     const int64_t n = (int64_t)S * B * H;
     const bool vec = (H & 3) == 0;
     if (vec) {
@@ -23,6 +24,10 @@ __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restri
             id = min(max(id, 0), V - 1);
             float4 v = __ldg(reinterpret_cast<const float4*>(table + (int64_t)id * H) + c);
             reinterpret_cast<float4*>(out)[i] = v;
+            if (out_bf16) {
+                reinterpret_cast<__nv_bfloat162*>(out_bf16)[2 * i] = __floats2bfloat162_rn(v.x, v.y);
+                reinterpret_cast<__nv_bfloat162*>(out_bf16)[2 * i + 1] = __floats2bfloat162_rn(v.z, v.w);
+            }
         }
     } else {
         for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -32,6 +37,7 @@ __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restri
             int id = __ldg(x + (int64_t)b * ldx + t);
             id = min(max(id, 0), V - 1);
             out[i] = __ldg(table + (int64_t)id * H + c);
+            if (out_bf16) out_bf16[i] = __float2bfloat16_rn(out[i]);
         }
     }
 }
@@ -62,7 +68,8 @@ __global__ void __launch_bounds__(256) embed_scatter_kernel(float* __restrict__ 
 // One warp per row of logits [N, V] (row i = t*B + b).  In place: logits -> (softmax-onehot)/N.
 __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ logits, int B, int S, int V,
                                                            const int32_t* __restrict__ y, int64_t ldy,
-                                                           double* __restrict__ loss_sum) {
+                                                           double* __restrict__ loss_sum,
+                                                           __nv_bfloat16* __restrict__ dl_bf16, int64_t ld_bf16) {
     __shared__ double sh[32];
     const int lane = threadIdx.x & 31;
     const int64_t N = (int64_t)B * S;
@@ -85,7 +92,9 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ l
             float v = z[c];
             if (c == label) zl = v;
             float p = expf(v - m) * inv;
-            z[c] = (p - (c == label ? 1.0f : 0.0f)) * invN;
+            const float d = (p - (c == label ? 1.0f : 0.0f)) * invN;
+            z[c] = d;
+            if (dl_bf16) dl_bf16[row * ld_bf16 + c] = __float2bfloat16_rn(d);
         }
         zl = warp_sum(zl);
         if (lane == 0) local += (double)(lse - zl);

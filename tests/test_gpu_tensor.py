@@ -53,3 +53,101 @@ def test_gemm_bf16_tc(lib, a_mn, b_mn, M, N, K, bias, acc):
         ref = ref + C0
     err = np.abs(C.cpu().numpy() - ref).max()
     assert err <= 1e-4 * max(np.abs(ref).max(), 1.0), err
+
+
+# ---------------------------------------------------------------------------------------
+# CRNN_PREC_BF16: the whole step on tensor cores.  Comparator = the oracle evaluated with
+# every matmul's inputs rounded to bf16 (fp64 accumulation): same rounding points as the
+# kernels (bf16 operands, fp32 accumulate, fp32 state / gates / master weights).
+# Tolerance 1e-2 relative per tensor (stated): a value that lands on the other side of a
+# bf16 rounding boundary moves by 2^-8 = 3.9e-3 relative, and that propagates through S steps.
+# ---------------------------------------------------------------------------------------
+import argparse
+import os
+
+from oracle import char_rnn_oracle as O
+
+BF16_RTOL = 1e-2
+
+
+def _relerr(a, b, floor):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), floor)
+
+
+def _bf16_model(model, H, L, S, B, V, seed=0, env=None):
+    from distributed_char_rnn_b200.model import Model
+    old = {}
+    for k, v in (env or {}).items():
+        old[k] = os.environ.get(k)
+        os.environ[k] = str(v)
+    try:
+        cfg = O.Config(model, H, L, S, B, V, 5.0)
+        params = O.init_params(cfg, seed)
+        rng = np.random.default_rng(seed + 100)
+        for k in params:
+            if k.endswith("bias"):
+                params[k] = (params[k] + rng.normal(size=params[k].shape) * 0.1).astype(np.float32)
+        args = argparse.Namespace(model=model, rnn_size=H, num_layers=L, seq_length=S, batch_size=B, vocab_size=V,
+                                  grad_clip=5.0, output_keep_prob=1.0, input_keep_prob=1.0)
+        m = Model(args, device="cuda:0", precision="bf16")
+        m.set_variables(params)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    return cfg, params, m
+
+
+BF16_SHAPES = [
+    ("lstm", 32, 2, 6, 5, 11, {}), ("gru", 32, 2, 6, 5, 11, {}), ("rnn", 32, 2, 6, 5, 11, {}),
+    ("lstm", 128, 2, 10, 50, 65, {}), ("gru", 64, 2, 8, 70, 96, {}), ("rnn", 48, 3, 7, 33, 40, {}),
+    ("lstm", 64, 1, 5, 150, 20, {"CRNN_TC_TILES": 1}),      # BT = 150 -> two 128-row passes
+    ("gru", 128, 1, 4, 260, 20, {"CRNN_TC_TILES": 2}),      # BT = 130 -> two passes, ragged
+    ("rnn", 96, 2, 5, 40, 30, {"CRNN_TC_HC": 16}),
+]
+
+
+@pytest.mark.parametrize("fast", [0, 1])
+@pytest.mark.parametrize("model,H,L,S,B,V,env", BF16_SHAPES)
+def test_bf16_gradients_match_bf16_oracle(model, H, L, S, B, V, env, fast):
+    import torch
+    cfg, params, m = _bf16_model(model, H, L, S, B, V, seed=H + L, env=dict(env, CRNN_FAST_ACT=fast))
+    rng = np.random.default_rng(S * B)
+    x, y = rng.integers(0, V, (B, S)), rng.integers(0, V, (B, S))
+    st = [tuple((rng.normal(size=s.shape) * 0.5).astype(np.float32) for s in layer) for layer in O.zero_state(cfg)]
+    fb = O.forward_backward(cfg, params, x, y, st, np.float64, bf16_gemm=True)
+    sflat = torch.from_numpy(np.concatenate([np.stack(layer).reshape(-1) for layer in st]).astype(np.float32)).cuda()
+    loss, sout = m.gradients(x.astype(np.int32), y.astype(np.int32), sflat)
+    assert abs(loss - fb["loss"]) <= 2e-3 * abs(fb["loss"])
+    got = m.gradients_numpy()
+    gmax = max(np.abs(g).max() for g in fb["grads"].values())
+    for k, g in fb["grads"].items():
+        assert _relerr(got[k], g, 1e-2 * gmax) < BF16_RTOL, k
+    ref_state = np.concatenate([np.stack(layer).reshape(-1) for layer in fb["final_state"]])
+    assert _relerr(sout.cpu().numpy(), ref_state, 1e-2) < BF16_RTOL
+    # and the bf16 path stays close to the exact fp32 graph (the reference's arithmetic)
+    fb32 = O.forward_backward(cfg, params, x, y, st, np.float64)
+    assert abs(loss - fb32["loss"]) <= 5e-3 * abs(fb32["loss"])
+
+
+@pytest.mark.parametrize("model", ["lstm", "gru", "rnn"])
+def test_bf16_training_tracks_fp32_oracle(model):
+    """Loss curve of the bf16 tensor-core path against the fp32 oracle over 20 steps with state carry."""
+    H, L, S, B, V = 64, 2, 12, 24, 30
+    cfg, params, m = _bf16_model(model, H, L, S, B, V, seed=7)
+    tr = O.Trainer(cfg, params, np.float32)
+    tr.begin_epoch(0)
+    m.assign_lr(0.002)
+    rng = np.random.default_rng(2)
+    # a learnable stream: next id = (id + 1) % V with noise
+    base = rng.integers(0, V, (B, 1))
+    for k in range(20):
+        x = (base + np.arange(S)[None, :] + k * S) % V
+        y = (x + 1) % V
+        loss, _ = m.step(x.astype(np.int32), y.astype(np.int32))
+        ref = float(tr.step(x, y))
+        assert abs(loss - ref) <= 2e-2 * ref, (k, loss, ref)
+    assert loss < 0.98 * np.log(V)            # it is learning
