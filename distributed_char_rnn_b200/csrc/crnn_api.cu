@@ -51,7 +51,7 @@ struct WsPlan {
 };
 
 struct RecPlanTc {
-    int HC, BT, nslices, ntiles, npass, box_rows;
+    int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd;
     size_t smem_fwd, smem_bwd;
 };
 
@@ -108,8 +108,9 @@ static const float kBeta1 = 0.9f, kBeta2 = 0.999f, kEps = 1e-8f;
 
 // scratch layout (bytes): [0,256) barrier words; [256,512) doubles {loss_sum, sq_sum};
 // [1024, 1024 + 8*NORM_BLOCKS) norm partials.
-static const size_t kScratchBytes = 8192;
-static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>(ws) + i; }
+static const size_t kScratchBytes = 32768;
+// one 256-byte block of barrier counters per recurrence launch (2 per layer), after the first 8 KB
+static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>((char*)ws + 8192 + (size_t)i * 256); }
 static inline double* ws_loss(void* ws) { return reinterpret_cast<double*>((char*)ws + 256); }
 static inline double* ws_sq(void* ws) { return reinterpret_cast<double*>((char*)ws + 264); }
 static inline double* ws_partials(void* ws) { return reinterpret_cast<double*>((char*)ws + 1024); }
@@ -171,36 +172,39 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
 static int plan_recurrence_tc(const crnn_handle* h, RecPlanTc* out) {
     const int H = h->cfg.rnn_size, B = h->cfg.batch_size, model = h->cfg.model;
     if (H % 16 != 0) return set_err(CRNN_ERR_UNSUP, "CRNN_PREC_BF16 needs rnn_size %% 16 == 0 (got %d)", H);
-    const int GW = h->G;
     const int g1 = model == CRNN_MODEL_LSTM ? 4 : (model == CRNN_MODEL_GRU ? 2 : 1);
     const int max_ctas = h->sm_count;
     const int nkb = ceil_div(H, 64);
-    const int64_t wbudget = (int64_t)h->max_smem - tc::RT_STAGES * tc::RT_ASTAGE - 2048;
-    int hc_smem = (int)(wbudget / ((int64_t)nkb * 128 * GW + (model == CRNN_MODEL_GRU ? 0 : 0)));
-    // backward resident slice: ceil(g1*H/64) (+ ceil(H/64) for gru) blocks of HC*128 bytes
-    const int nkb_b = ceil_div(g1 * H, 64) + (model == CRNN_MODEL_GRU ? nkb : 0);
-    hc_smem = std::min(hc_smem, (int)(wbudget / ((int64_t)nkb_b * 128)));
-    int HC = std::min(std::min(hc_smem, 256 / g1), H) & ~15;
-    if (HC < 16) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory", H);
-    // enough slices that every SM has work even with few batch tiles; enough tiles to keep A loads short
-    int want_tiles = std::max(1, std::min(ceil_div(B, 32), max_ctas));
-    while (HC > 16 && ceil_div(H, HC) * want_tiles < max_ctas / 2) HC -= 16;
-    int hc_env = env_int("CRNN_TC_HC", 0);
-    if (hc_env >= 16) HC = std::min(hc_env & ~15, std::min(std::min(hc_smem, 256 / g1), H) & ~15);
-    int nslices = ceil_div(H, HC);
-    if (nslices > max_ctas) return set_err(CRNN_ERR_UNSUP, "rnn_size %d needs %d slices > %d SMs", H, nslices, max_ctas);
-    int ntiles = std::max(1, std::min(max_ctas / nslices, ceil_div(B, 16)));
-    int nt_env = env_int("CRNN_TC_TILES", 0);
-    if (nt_env > 0) ntiles = std::max(1, std::min(nt_env, max_ctas / nslices));
-    int BT = ceil_div(B, ntiles);
-    ntiles = ceil_div(B, BT);
-    out->HC = HC; out->BT = BT; out->nslices = nslices; out->ntiles = ntiles;
-    out->npass = ceil_div(BT, 128);
-    out->box_rows = out->npass > 1 ? 128 : std::min(128, (BT + 7) & ~7);
-    out->smem_fwd = tc::rt_smem_bytes((size_t)nkb * g1 * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
-    out->smem_bwd = tc::rt_smem_bytes((size_t)ceil_div(g1 * H, 64) * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
-    if ((int)std::max(out->smem_fwd, out->smem_bwd) > h->max_smem)
-        return set_err(CRNN_ERR_UNSUP, "tensor-core recurrence needs %zu B shared memory > %d", std::max(out->smem_fwd, out->smem_bwd), h->max_smem);
+    const int hc_env = env_int("CRNN_TC_HC", 0), nt_env = env_int("CRNN_TC_TILES", 0);
+    auto fill = [&](int HC, RecPlanTc* o) -> bool {
+        const int nslices = ceil_div(H, HC);
+        if (nslices > max_ctas) return false;
+        int ntiles = std::max(1, std::min(max_ctas / nslices, ceil_div(B, 16)));
+        if (nt_env > 0) ntiles = std::max(1, std::min(nt_env, max_ctas / nslices));
+        if (ntiles > 64) ntiles = 64;                        // 64 barrier words per launch
+        const int BT = ceil_div(B, ntiles);
+        o->HC = HC; o->BT = BT; o->nslices = nslices; o->ntiles = ceil_div(B, BT);
+        o->npass = ceil_div(BT, 128);
+        o->box_rows = o->npass > 1 ? 128 : std::min(128, (BT + 7) & ~7);
+        const int rows = std::min(128, BT);
+        o->zs_fwd = rows * (g1 * HC + 1);
+        o->zs_bwd = rows * (HC + 1);
+        o->smem_fwd = tc::rt_smem_bytes((size_t)nkb * g1 * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, o->zs_fwd);
+        o->smem_bwd = tc::rt_smem_bytes((size_t)ceil_div(g1 * H, 64) * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, o->zs_bwd);
+        return (int)std::max(o->smem_fwd, o->smem_bwd) <= h->max_smem;
+    };
+    // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
+    // while that leaves SMs idle: every SM should hold a (slice, tile) pair.
+    const int hc_max = std::min(256 / g1, H) & ~15;
+    int best = 0;
+    RecPlanTc cand;
+    for (int HC = hc_max; HC >= 16; HC -= 16) {
+        if (hc_env >= 16 && HC > hc_env) continue;
+        if (!fill(HC, &cand)) continue;
+        if (best == 0 || cand.nslices * cand.ntiles > out->nslices * out->ntiles) { best = HC; *out = cand; }
+        if (hc_env >= 16 || cand.nslices * cand.ntiles >= (max_ctas * 3) / 4) break;
+    }
+    if (best == 0) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory", H);
     return CRNN_OK;
 }
 
@@ -427,7 +431,7 @@ static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const floa
     embed_gather_kernel<<<grid_for(SB * H / 4 + 1, h->sm_count), 256, 0, st>>>(emb, V, H, x, ldx, B, S, x0, nullptr);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     prof_mark(h, st, CRNN_PHASE_MISC);
-    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 256, st));
+    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 64 * 256, st));
     for (int l = 0; l < L; ++l) {
         LayerParams lp = layer_params(h, params, l);
         float* hx = wsf(ws, h->ws.hx[l]);
@@ -496,6 +500,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const int GW = h->G, GZ = h->GZ;
     a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles; a.npass = p.npass; a.box_rows = p.box_rows;
     a.fast_act = h->fast_act;
+    a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
     CUtensorMap t0, t1, w0, w1;
     int rc;
     if (!backward) {
@@ -568,7 +573,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     embed_gather_kernel<<<grid_for(SB * H / 4 + 1, sc), 256, 0, st>>>(params + h->emb_off, V, H, x, ldx, B, S, x0, x0b);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     prof_mark(h, st, CRNN_PHASE_MISC);
-    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 256, st));
+    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 64 * 256, st));
     for (int l = 0; l < L; ++l) {
         LayerParams lp = layer_params(h, params, l);
         float* hx = wsf(ws, h->ws.hx[l]);

@@ -29,6 +29,7 @@ struct RecTcArgs {
     int GS;                     // gate-stash row width / H
     int box_rows;               // rows per A-tile TMA box
     int fast_act;               // 1: MUFU.TANH activations
+    int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
     float* gates;               // [S,B,GS*H]  in: x-projection + bias, out: activations
     float* hx;                  // [(S+1),B,H]
     float* cx;                  // lstm [(S+1),B,H]
@@ -39,7 +40,7 @@ struct RecTcArgs {
     __nv_bfloat16* hxb;         // [(S+1),B,H] bf16 copy of hx (fwd out; MMA operand)
     __nv_bfloat16* rsb;         // gru [S,B,H] bf16 r*h (fwd out; MMA operand)
     __nv_bfloat16* dzb;         // bwd [(S+1),B,GZ*H] bf16 copy of dz (MMA operand)
-    unsigned* barrier;
+    unsigned* barrier;          // one zeroed counter per batch tile: rows of different tiles never interact
 };
 
 __device__ __forceinline__ float tanh_mufu(float x) {
@@ -60,17 +61,18 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 }
 
 struct RtSmem {
-    uint8_t* wsa; uint8_t* wsb; uint8_t* ring;
+    uint8_t* wsa; uint8_t* wsb; uint8_t* ring; float* zs;
     uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar;
     uint32_t* tmem_slot;
 };
 
-__device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, size_t wsb_bytes) {
+__device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, size_t wsb_bytes, int zs_floats) {
     RtSmem s;
     uint8_t* p = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     s.wsa = p; p += wsa_bytes;
     s.wsb = p; p += wsb_bytes;
     s.ring = p; p += RT_STAGES * RT_ASTAGE;
+    s.zs = reinterpret_cast<float*>(p); p += (size_t)((zs_floats + 3) & ~3) * 4;
     s.a_full = reinterpret_cast<uint64_t*>(p);
     s.a_empty = s.a_full + RT_STAGES;
     s.z_full = s.a_empty + RT_STAGES;
@@ -80,8 +82,8 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     return s;
 }
 
-inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes) {
-    return wsa_bytes + wsb_bytes + RT_STAGES * RT_ASTAGE + 256 + 1024;
+inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats) {
+    return wsa_bytes + wsb_bytes + RT_STAGES * RT_ASTAGE + (size_t)((zs_floats + 3) & ~3) * 4 + 256 + 1024;
 }
 
 // Role-private pipeline state.
@@ -135,11 +137,63 @@ __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned targe
     asm volatile("fence.proxy.async;" ::: "memory");
 }
 
+// TMEM accumulator rows [0,nr) x columns [0,nc) -> shared Zs[r*ldz + c] (ldz odd: conflict-free).
+// A warp can only read its own TMEM lane quarter; quarters with no valid row skip the load.
+__device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int lane, int nr, int nc, float* __restrict__ Zs, int ldz) {
+    if (32 * q < nr) {
+        float v[32];
+        const int r = 32 * q + lane;
+        for (int c0 = 0; c0 < nc; c0 += 32) {
+            tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
+            if (r < nr) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (c0 + i < nc) Zs[r * ldz + c0 + i] = v[i];
+            }
+        }
+    }
+}
+
+constexpr int RT_UB = 8;     // (row, unit) elements per epilogue thread per batch
+
+// Element -> (row, unit) mapping shared by all epilogues: consecutive threads take consecutive
+// hidden units of one batch row, so every global access of a warp is one contiguous segment.
+struct EpiIdx {
+    bool ok;
+    int zi;          // r*ldz + jj*gstride: index of the unit's first accumulator column in Zs
+    int64_t o;       // b*H + j
+    int64_t row;     // t*B + b
+    int j;
+};
+__device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ldz, int gstride, int b0row, int j0,
+                                            int H, int64_t tB) {
+    EpiIdx e;
+    e.ok = idx < nunits;
+    const int r = e.ok ? idx / hcv : 0;
+    const int jj = e.ok ? idx - r * hcv : 0;
+    e.zi = r * ldz + jj * gstride;
+    e.j = j0 + jj;
+    e.o = (int64_t)(b0row + r) * H + e.j;
+    e.row = tB + b0row + r;
+    return e;
+}
+
+// Wait for the accumulator, move it to shared memory, release TMEM to the MMA thread.
+#define RT_TAKE_ACC(nr_, nc_)                                                     \
+    do {                                                                          \
+        mbar_wait(s.z_full, p.z_i & 1);                                           \
+        tc_fence_after();                                                         \
+        zs_dump(tmem, q, lane, nr_, nc_, Zs, ldz);                                \
+        tc_fence_before();                                                        \
+        mbar_arrive(s.z_empty);                                                   \
+        ++p.z_i;                                                                  \
+        epi_bar_sync();                                                           \
+    } while (0)
+
 // ------------------------------------------------------------------------------------------
-// forward.  Packed weights (pack_rec_weights_kernel): row (slice*NCW + lc) of Wr is the column of
-// W_h this CTA's local column lc contracts with, K contiguous.  lc = jj*G1 + g for the first
-// contraction (all gates of one unit adjacent -> one tcgen05.ld chunk holds whole units);
-// GRU candidate rows follow at lc = 2*HC + jj.
+// forward.  Packed weights (pack_rec_weights_kernel): row (slice*GW*HC + lc) of Wr is the column
+// of W_h this CTA's local column lc contracts with, K contiguous.  lc = jj*G1 + g for the first
+// contraction; GRU candidate rows follow at lc = 2*HC + jj.
 // ------------------------------------------------------------------------------------------
 template <int MODEL>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmH,
@@ -153,10 +207,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const int B = a.B, H = a.H, HC = a.HC;
     const int NCA = G1 * HC;
     const int nkb = ceil_div(H, 64);
-    const RtSmem s = rt_carve(smem_raw, (size_t)nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
+    const RtSmem s = rt_carve(smem_raw, (size_t)nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, a.zs_floats);
+    float* Zs = s.zs;
+    const int ldz = NCA + 1;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
-    const int j0 = slice * HC;
+    const int j0 = slice * HC, hcv = min(HC, H - j0);
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
@@ -194,11 +250,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
             }
             for (int t = 0; t < a.S; ++t) {
                 for (int ph = 0; ph < nphase; ++ph) {
-                    if (phases_done > 0) rt_await(a.barrier, phases_done * gridDim.x);
-                    for (int ps = 0; ps < a.npass; ++ps) {
-                        const int row = (ph == 0 ? t * B : t * B) + b0 + ps * 128;
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, row, nkb, a.box_rows);
-                    }
+                    if (phases_done > 0) rt_await(a.barrier + tile, phases_done * a.nslices);
+                    for (int ps = 0; ps < a.npass; ++ps)
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows);
                     ++phases_done;
                 }
             }
@@ -214,111 +268,79 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     } else {
         const int q = warp & 3;
         const int epi_tid = (warp - 2) * 32 + lane;
-        const uint32_t tlane = tmem + ((uint32_t)(32 * q) << 16);
-        float v[32];
         for (int t = 0; t < a.S; ++t) {
+            const int64_t tB = (int64_t)t * B;
+            float* gt = a.gates;
+            const float* hprev = a.hx + (int64_t)t * BH;
+            float* hnext = a.hx + (int64_t)(t + 1) * BH;
+            __nv_bfloat16* hnb = a.hxb + (int64_t)(t + 1) * BH;
             for (int ph = 0; ph < nphase; ++ph) {
                 for (int ps = 0; ps < a.npass; ++ps) {
-                    const int r = ps * 128 + 32 * q + lane;       // row within the batch tile
-                    const bool row_ok = r < bt;
-                    const int64_t b = b0 + r;
-                    float* g = a.gates + ((int64_t)t * B + b) * gw;
-                    const float* hprev = a.hx + (int64_t)t * BH + b * H;
-                    float* hnext = a.hx + (int64_t)(t + 1) * BH + b * H;
-                    __nv_bfloat16* hnb = a.hxb + ((int64_t)(t + 1) * B + b) * H;
-                    mbar_wait(s.z_full, p.z_i & 1);
-                    tc_fence_after();
-                    const int nc = ph == 0 ? NCA : HC;
-                    for (int c0 = 0; c0 < nc; c0 += 32) {
-                        tmem_ld32(tlane + (uint32_t)c0, v);
-                        if (!row_ok) continue;
-                        if (MODEL == CRNN_MODEL_LSTM) {
-                            // 8 units x (i,j,f,o)
-                            const int jb = j0 + c0 / 4;
-                            float hn[8];
+                    const int nr = min(128, bt - ps * 128);
+                    const int nunits = nr * hcv;
+                    const int b0row = b0 + ps * 128;
+                    const int gstride = ph == 0 ? G1 : 1;
+                    for (int base = 0; base < nunits; base += 128 * RT_UB) {
+                        // ---- issue every global load of this batch before touching the accumulator
+                        EpiIdx e[RT_UB];
+                        float x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], ax[RT_UB];
 #pragma unroll
-                            for (int u = 0; u < 8; ++u) {
-                                const int j = jb + u;
-                                hn[u] = 0.f;
-                                if (j < H) {
-                                    float si = fast_sigmoid(v[4 * u] + g[j]);
-                                    float tj = fast_tanh(v[4 * u + 1] + g[H + j]);
-                                    float sf = fast_sigmoid(v[4 * u + 2] + g[2 * H + j] + 1.0f);
-                                    float so = fast_sigmoid(v[4 * u + 3] + g[3 * H + j]);
-                                    float cp = a.cx[(int64_t)t * BH + b * H + j];
-                                    float cn = fmaf(sf, cp, si * tj);
-                                    hn[u] = so * fast_tanh(cn);
-                                    g[j] = si; g[H + j] = tj; g[2 * H + j] = sf; g[3 * H + j] = so;
-                                    a.cx[(int64_t)(t + 1) * BH + b * H + j] = cn;
-                                    hnext[j] = hn[u];
-                                }
-                            }
-                            if (jb < H) {   // H % 8 == 0: the 8 units are all valid or all past the end
-                                uint4 pk = make_uint4(pack_bf16x2(hn[0], hn[1]), pack_bf16x2(hn[2], hn[3]),
-                                                      pack_bf16x2(hn[4], hn[5]), pack_bf16x2(hn[6], hn[7]));
-                                *reinterpret_cast<uint4*>(hnb + jb) = pk;
-                            }
-                        } else if (MODEL == CRNN_MODEL_RNN) {
-#pragma unroll
-                            for (int u = 0; u < 32; u += 8) {
-                                const int jb = j0 + c0 + u;
-                                if (c0 + u < HC && jb < H) {
-                                    float hn[8];
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        hn[e] = fast_tanh(v[u + e] + g[jb + e]);
-                                        hnext[jb + e] = hn[e];
-                                    }
-                                    *reinterpret_cast<uint4*>(hnb + jb) = make_uint4(pack_bf16x2(hn[0], hn[1]), pack_bf16x2(hn[2], hn[3]),
-                                                                                    pack_bf16x2(hn[4], hn[5]), pack_bf16x2(hn[6], hn[7]));
-                                }
-                            }
-                        } else if (ph == 0) {
-                            // GRU gates: 16 units x (r,u); publish r*h for the candidate contraction
-                            __nv_bfloat16* rsb = a.rsb + ((int64_t)t * B + b) * H;
-#pragma unroll
-                            for (int u = 0; u < 16; u += 8) {
-                                const int jb = j0 + c0 / 2 + u;
-                                if (jb < H) {
-                                    float rs[8];
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        const int j = jb + e;
-                                        float r_ = fast_sigmoid(v[2 * (u + e)] + g[j]);
-                                        float u_ = fast_sigmoid(v[2 * (u + e) + 1] + g[H + j]);
-                                        rs[e] = r_ * hprev[j];
-                                        g[j] = r_; g[H + j] = u_; g[3 * H + j] = rs[e];
-                                    }
-                                    *reinterpret_cast<uint4*>(rsb + jb) = make_uint4(pack_bf16x2(rs[0], rs[1]), pack_bf16x2(rs[2], rs[3]),
-                                                                                    pack_bf16x2(rs[4], rs[5]), pack_bf16x2(rs[6], rs[7]));
-                                }
-                            }
-                        } else {
-#pragma unroll
-                            for (int u = 0; u < 32; u += 8) {
-                                const int jb = j0 + c0 + u;
-                                if (c0 + u < HC && jb < H) {
-                                    float hn[8];
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        const int j = jb + e;
-                                        float cand = fast_tanh(v[u + e] + g[2 * H + j]);
-                                        float u_ = g[H + j];
-                                        hn[e] = fmaf(u_, hprev[j] - cand, cand);     // u*h + (1-u)*cand
-                                        g[2 * H + j] = cand;
-                                        hnext[j] = hn[e];
-                                    }
-                                    *reinterpret_cast<uint4*>(hnb + jb) = make_uint4(pack_bf16x2(hn[0], hn[1]), pack_bf16x2(hn[2], hn[3]),
-                                                                                    pack_bf16x2(hn[4], hn[5]), pack_bf16x2(hn[6], hn[7]));
+                        for (int u = 0; u < RT_UB; ++u) {
+                            e[u] = epi_index(base + u * 128 + epi_tid, nunits, hcv, ldz, gstride, b0row, j0, H, tB);
+                            x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = 0.f;
+                            if (e[u].ok) {
+                                const float* g = gt + e[u].row * gw + e[u].j;
+                                if (MODEL == CRNN_MODEL_LSTM) {
+                                    x0[u] = g[0]; x1[u] = g[H]; x2[u] = g[2 * H]; x3[u] = g[3 * H];
+                                    ax[u] = a.cx[(int64_t)t * BH + e[u].o];
+                                } else if (MODEL == CRNN_MODEL_RNN) {
+                                    x0[u] = g[0];
+                                } else if (ph == 0) {
+                                    x0[u] = g[0]; x1[u] = g[H]; ax[u] = hprev[e[u].o];
+                                } else {
+                                    x0[u] = g[2 * H]; x1[u] = g[H]; ax[u] = hprev[e[u].o];
                                 }
                             }
                         }
+                        if (base == 0) RT_TAKE_ACC(nr, ph == 0 ? NCA : HC);
+#pragma unroll
+                        for (int u = 0; u < RT_UB; ++u) {
+                            if (!e[u].ok) continue;
+                            float* g = gt + e[u].row * gw + e[u].j;
+                            const float* z = Zs + e[u].zi;
+                            if (MODEL == CRNN_MODEL_LSTM) {
+                                float si = fast_sigmoid(z[0] + x0[u]);
+                                float tj = fast_tanh(z[1] + x1[u]);
+                                float sf = fast_sigmoid(z[2] + x2[u] + 1.0f);          // forget_bias
+                                float so = fast_sigmoid(z[3] + x3[u]);
+                                float cn = fmaf(sf, ax[u], si * tj);
+                                float hn = so * fast_tanh(cn);
+                                hnext[e[u].o] = hn;
+                                hnb[e[u].o] = __float2bfloat16_rn(hn);
+                                a.cx[(int64_t)(t + 1) * BH + e[u].o] = cn;
+                                g[0] = si; g[H] = tj; g[2 * H] = sf; g[3 * H] = so;
+                            } else if (MODEL == CRNN_MODEL_RNN) {
+                                float hn = fast_tanh(z[0] + x0[u]);
+                                hnext[e[u].o] = hn;
+                                hnb[e[u].o] = __float2bfloat16_rn(hn);
+                            } else if (ph == 0) {
+                                float r_ = fast_sigmoid(z[0] + x0[u]);
+                                float u_ = fast_sigmoid(z[1] + x1[u]);
+                                float rs = r_ * ax[u];                                   // reset BEFORE the matmul
+                                a.rsb[e[u].row * H + e[u].j] = __float2bfloat16_rn(rs);
+                                g[0] = r_; g[H] = u_; g[3 * H] = rs;
+                            } else {
+                                float cand = fast_tanh(z[0] + x0[u]);
+                                float hn = fmaf(x1[u], ax[u] - cand, cand);              // u*h + (1-u)*cand
+                                hnext[e[u].o] = hn;
+                                hnb[e[u].o] = __float2bfloat16_rn(hn);
+                                g[2 * H] = cand;
+                            }
+                        }
                     }
-                    tc_fence_before();
-                    mbar_arrive(s.z_empty);
-                    ++p.z_i;
+                    epi_bar_sync();          // Zs is reused by the next pass / phase
                 }
-                rt_publish(a.barrier, epi_tid);
+                rt_publish(a.barrier + tile, epi_tid);
             }
         }
     }
@@ -345,10 +367,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     const int B = a.B, H = a.H, HC = a.HC;
     const int nkb0 = ceil_div(G1 * H, 64);
     const int nkb1 = ceil_div(H, 64);
-    const RtSmem s = rt_carve(smem_raw, (size_t)nkb0 * HC * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb1 * HC * 128 : 0);
+    const RtSmem s = rt_carve(smem_raw, (size_t)nkb0 * HC * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb1 * HC * 128 : 0, a.zs_floats);
+    float* Zs = s.zs;
+    const int ldz = HC + 1;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
-    const int j0 = slice * HC;
+    const int j0 = slice * HC, hcv = min(HC, H - j0);
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, zw = (int64_t)GZ * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
@@ -382,13 +406,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             for (int t = a.S - 1; t >= 0; --t) {
                 // contraction 0 reads dz_{t+1} (all CTAs, previous step)
                 if (t + 1 < a.S) {
-                    rt_await(a.barrier, phases_done * gridDim.x);
+                    rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
-                    rt_await(a.barrier, phases_done * gridDim.x);
+                    rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows);
                     ++phases_done;
@@ -408,118 +432,116 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     } else {
         const int q = warp & 3;
         const int epi_tid = (warp - 2) * 32 + lane;
-        const uint32_t tlane = tmem + ((uint32_t)(32 * q) << 16);
-        float v[32];
         // zero the CTA-private carries
         if (MODEL != CRNN_MODEL_RNN) {
-            for (int ps = 0; ps < a.npass; ++ps) {
-                const int r = ps * 128 + 32 * q + lane;
-                if (r < bt)
-                    for (int jj = 0; jj < HC && j0 + jj < H; ++jj) a.carry0[(int64_t)(b0 + r) * H + j0 + jj] = 0.f;
+            for (int idx = epi_tid; idx < bt * hcv; idx += 128) {
+                const int r = idx / hcv, jj = idx - r * hcv;
+                a.carry0[(int64_t)(b0 + r) * H + j0 + jj] = 0.f;
             }
         }
         for (int t = a.S - 1; t >= 0; --t) {
             const bool has_next = t + 1 < a.S;
+            const int64_t tB = (int64_t)t * B;
             for (int ps = 0; ps < a.npass; ++ps) {
-                const int r = ps * 128 + 32 * q + lane;
-                const bool row_ok = r < bt;
-                const int64_t b = b0 + r;
-                const int64_t o0 = b * H;
-                const float* g = a.gates + ((int64_t)t * B + b) * gw;
-                float* dz = a.dz + ((int64_t)t * B + b) * zw;
-                __nv_bfloat16* dzb = a.dzb + ((int64_t)t * B + b) * zw;
-                const float* dyt = a.dy + (int64_t)t * BH + o0;
-                if (has_next) { mbar_wait(s.z_full, p.z_i & 1); tc_fence_after(); }
-                for (int c0 = 0; c0 < HC; c0 += 32) {
-                    if (has_next) tmem_ld32(tlane + (uint32_t)c0, v);
-                    if (!row_ok) continue;
+                const int nr = min(128, bt - ps * 128);
+                const int nunits = nr * hcv;
+                const int b0row = b0 + ps * 128;
+                for (int base = 0; base < nunits; base += 128 * RT_UB) {
+                    EpiIdx e[RT_UB];
+                    float dyv[RT_UB], x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], c0v[RT_UB], c1v[RT_UB], cr[RT_UB];
 #pragma unroll
-                    for (int u = 0; u < 32; u += 8) {
-                        const int jb = j0 + c0 + u;
-                        if (c0 + u >= HC || jb >= H) continue;
-                        float o_a[8], o_b[8], o_c[8], o_d[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const int j = jb + e;
-                            float dht = dyt[j] + (has_next ? v[u + e] : 0.f);
+                    for (int u = 0; u < RT_UB; ++u) {
+                        e[u] = epi_index(base + u * 128 + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
+                        dyv[u] = x0[u] = x1[u] = x2[u] = x3[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
+                        if (e[u].ok) {
+                            const float* g = a.gates + e[u].row * gw + e[u].j;
+                            dyv[u] = a.dy[(int64_t)t * BH + e[u].o];
                             if (MODEL == CRNN_MODEL_LSTM) {
-                                float si = g[j], tj = g[H + j], sf = g[2 * H + j], so = g[3 * H + j];
-                                float cp = a.cx[(int64_t)t * BH + o0 + j];
-                                float tc_ = fast_tanh(a.cx[(int64_t)(t + 1) * BH + o0 + j]);
-                                float dct = a.carry0[o0 + j] + dht * so * (1.0f - tc_ * tc_);
-                                o_a[e] = dct * tj * si * (1.0f - si);
-                                o_b[e] = dct * si * (1.0f - tj * tj);
-                                o_c[e] = dct * cp * sf * (1.0f - sf);
-                                o_d[e] = dht * tc_ * so * (1.0f - so);
-                                a.carry0[o0 + j] = dct * sf;
-                                dz[j] = o_a[e]; dz[H + j] = o_b[e]; dz[2 * H + j] = o_c[e]; dz[3 * H + j] = o_d[e];
+                                x0[u] = g[0]; x1[u] = g[H]; x2[u] = g[2 * H]; x3[u] = g[3 * H];
+                                c0v[u] = a.cx[(int64_t)t * BH + e[u].o];
+                                c1v[u] = a.cx[(int64_t)(t + 1) * BH + e[u].o];
+                                cr[u] = a.carry0[e[u].o];
                             } else if (MODEL == CRNN_MODEL_RNN) {
-                                float hn = a.hx[(int64_t)(t + 1) * BH + o0 + j];
-                                o_a[e] = dht * (1.0f - hn * hn);
-                                dz[j] = o_a[e];
+                                x0[u] = a.hx[(int64_t)(t + 1) * BH + e[u].o];
                             } else {
-                                dht += a.carry0[o0 + j];
-                                float u_ = g[H + j], cand = g[2 * H + j];
-                                float hp = a.hx[(int64_t)t * BH + o0 + j];
-                                o_c[e] = dht * (1.0f - u_) * (1.0f - cand * cand);      // d candidate pre-activation
-                                o_b[e] = dht * (hp - cand) * u_ * (1.0f - u_);          // d update-gate pre-activation
-                                dz[2 * H + j] = o_c[e]; dz[H + j] = o_b[e];
-                                a.carry1[o0 + j] = dht;
+                                x1[u] = g[H]; x2[u] = g[2 * H];
+                                c0v[u] = a.hx[(int64_t)t * BH + e[u].o];
+                                cr[u] = a.carry0[e[u].o];
                             }
                         }
-#define CRNN_ST8(ptr, arr) *reinterpret_cast<uint4*>(ptr) = make_uint4(pack_bf16x2(arr[0], arr[1]), pack_bf16x2(arr[2], arr[3]), \
-                                                                       pack_bf16x2(arr[4], arr[5]), pack_bf16x2(arr[6], arr[7]))
+                    }
+                    if (base == 0 && has_next) RT_TAKE_ACC(nr, HC);
+#pragma unroll
+                    for (int u = 0; u < RT_UB; ++u) {
+                        if (!e[u].ok) continue;
+                        float dht = dyv[u] + (has_next ? Zs[e[u].zi] : 0.f);
+                        float* dz = a.dz + e[u].row * zw + e[u].j;
+                        __nv_bfloat16* dzb = a.dzb + e[u].row * zw + e[u].j;
                         if (MODEL == CRNN_MODEL_LSTM) {
-                            CRNN_ST8(dzb + jb, o_a); CRNN_ST8(dzb + H + jb, o_b); CRNN_ST8(dzb + 2 * H + jb, o_c); CRNN_ST8(dzb + 3 * H + jb, o_d);
+                            const float si = x0[u], tj = x1[u], sf = x2[u], so = x3[u];
+                            const float tcn = fast_tanh(c1v[u]);
+                            const float dct = cr[u] + dht * so * (1.0f - tcn * tcn);
+                            const float di = dct * tj * si * (1.0f - si);
+                            const float dj = dct * si * (1.0f - tj * tj);
+                            const float df = dct * c0v[u] * sf * (1.0f - sf);
+                            const float dO = dht * tcn * so * (1.0f - so);
+                            a.carry0[e[u].o] = dct * sf;
+                            dz[0] = di; dz[H] = dj; dz[2 * H] = df; dz[3 * H] = dO;
+                            dzb[0] = __float2bfloat16_rn(di); dzb[H] = __float2bfloat16_rn(dj);
+                            dzb[2 * H] = __float2bfloat16_rn(df); dzb[3 * H] = __float2bfloat16_rn(dO);
                         } else if (MODEL == CRNN_MODEL_RNN) {
-                            CRNN_ST8(dzb + jb, o_a);
+                            const float d = dht * (1.0f - x0[u] * x0[u]);
+                            dz[0] = d;
+                            dzb[0] = __float2bfloat16_rn(d);
                         } else {
-                            CRNN_ST8(dzb + 2 * H + jb, o_c); CRNN_ST8(dzb + H + jb, o_b);
+                            dht += cr[u];
+                            const float u_ = x1[u], cand = x2[u], hp = c0v[u];
+                            const float dc = dht * (1.0f - u_) * (1.0f - cand * cand);   // d candidate pre-activation
+                            const float du = dht * (hp - cand) * u_ * (1.0f - u_);       // d update-gate pre-activation
+                            dz[2 * H] = dc; dz[H] = du;
+                            dzb[2 * H] = __float2bfloat16_rn(dc); dzb[H] = __float2bfloat16_rn(du);
+                            a.carry1[e[u].o] = dht;
                         }
                     }
                 }
-                if (has_next) { tc_fence_before(); mbar_arrive(s.z_empty); ++p.z_i; }
+                epi_bar_sync();
             }
-            rt_publish(a.barrier, epi_tid);
+            rt_publish(a.barrier + tile, epi_tid);
             if (MODEL == CRNN_MODEL_GRU) {
                 for (int ps = 0; ps < a.npass; ++ps) {
-                    const int r = ps * 128 + 32 * q + lane;
-                    const bool row_ok = r < bt;
-                    const int64_t b = b0 + r;
-                    const int64_t o0 = b * H;
-                    const float* g = a.gates + ((int64_t)t * B + b) * gw;
-                    float* dz = a.dz + ((int64_t)t * B + b) * zw;
-                    __nv_bfloat16* dzb = a.dzb + ((int64_t)t * B + b) * zw;
-                    mbar_wait(s.z_full, p.z_i & 1);
-                    tc_fence_after();
-                    for (int c0 = 0; c0 < HC; c0 += 32) {
-                        tmem_ld32(tlane + (uint32_t)c0, v);
-                        if (!row_ok) continue;
+                    const int nr = min(128, bt - ps * 128);
+                    const int nunits = nr * hcv;
+                    const int b0row = b0 + ps * 128;
+                    for (int base = 0; base < nunits; base += 128 * RT_UB) {
+                        EpiIdx e[RT_UB];
+                        float x0[RT_UB], x1[RT_UB], hp[RT_UB], c1v[RT_UB];
 #pragma unroll
-                        for (int u = 0; u < 32; u += 8) {
-                            const int jb = j0 + c0 + u;
-                            if (c0 + u >= HC || jb >= H) continue;
-                            float o_a[8];
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                const int j = jb + e;
-                                float r_ = g[j], u_ = g[H + j];
-                                float hp = a.hx[(int64_t)t * BH + o0 + j];
-                                float drs = v[u + e];
-                                o_a[e] = drs * hp * r_ * (1.0f - r_);
-                                dz[j] = o_a[e];
-                                a.carry0[o0 + j] = fmaf(a.carry1[o0 + j], u_, drs * r_);
+                        for (int u = 0; u < RT_UB; ++u) {
+                            e[u] = epi_index(base + u * 128 + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
+                            x0[u] = x1[u] = hp[u] = c1v[u] = 0.f;
+                            if (e[u].ok) {
+                                const float* g = a.gates + e[u].row * gw + e[u].j;
+                                x0[u] = g[0]; x1[u] = g[H];
+                                hp[u] = a.hx[(int64_t)t * BH + e[u].o];
+                                c1v[u] = a.carry1[e[u].o];
                             }
-                            CRNN_ST8(dzb + jb, o_a);
+                        }
+                        if (base == 0) RT_TAKE_ACC(nr, HC);
+#pragma unroll
+                        for (int u = 0; u < RT_UB; ++u) {
+                            if (!e[u].ok) continue;
+                            const float drs = Zs[e[u].zi];
+                            const float r_ = x0[u], u_ = x1[u];
+                            const float dr = drs * hp[u] * r_ * (1.0f - r_);
+                            a.dz[e[u].row * zw + e[u].j] = dr;
+                            a.dzb[e[u].row * zw + e[u].j] = __float2bfloat16_rn(dr);
+                            a.carry0[e[u].o] = fmaf(c1v[u], u_, drs * r_);
                         }
                     }
-                    tc_fence_before();
-                    mbar_arrive(s.z_empty);
-                    ++p.z_i;
+                    epi_bar_sync();
                 }
-                rt_publish(a.barrier, epi_tid);
+                rt_publish(a.barrier + tile, epi_tid);
             }
-#undef CRNN_ST8
         }
     }
     __syncthreads();
@@ -529,6 +551,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     }
 }
 
+#undef RT_TAKE_ACC
 #undef fast_tanh
 #undef fast_sigmoid
 
