@@ -126,12 +126,24 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_restatement_rate(c, max_seconds, warmup, steps=None, batch=None, seed=0):
+def best_cpu_threads(c):
+    """Thread count that makes the CPU restatement fastest on this box (tiny ops lose to the
+    thread pool's hand-offs; large ones want every core).  One probe step per candidate."""
+    ncpu = os.cpu_count() or 1
+    best, best_t = ncpu, None
+    for th in sorted({ncpu, max(1, ncpu // 2), max(1, ncpu // 4), 1}, reverse=True):
+        r = cpu_restatement_rate(c, 2.0, 1, steps=1, batch=max(1, c["batch_size"] // 8), threads=th)
+        if best_t is None or r["seconds"] < best_t:
+            best, best_t = th, r["seconds"]
+    return best
+
+
+def cpu_restatement_rate(c, max_seconds, warmup, steps=None, batch=None, seed=0, threads=None):
     """chars/s of the CPU restatement (oracle/torch_restatement.py) on this box's host cores."""
     import torch
     from oracle import char_rnn_oracle as O
     from oracle.torch_restatement import TorchStep
-    cores = os.cpu_count() or 1
+    cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     B = batch or c["batch_size"]
     cc = dict(c, batch_size=B)
@@ -146,13 +158,15 @@ def cpu_restatement_rate(c, max_seconds, warmup, steps=None, batch=None, seed=0)
     def batch_k(k):
         k %= nbm
         return X[:, k * S:(k + 1) * S], Y[:, k * S:(k + 1) * S]
+    losses = []
     for k in range(warmup):
-        ts.step(*batch_k(k))
+        losses.append(ts.step(*batch_k(k)))
     t0 = time.perf_counter()
     done = 0
     loss = None
     while True:
         loss = ts.step(*batch_k(warmup + done))
+        losses.append(loss)
         done += 1
         el = time.perf_counter() - t0
         if steps is not None and done >= steps:
@@ -160,7 +174,7 @@ def cpu_restatement_rate(c, max_seconds, warmup, steps=None, batch=None, seed=0)
         if steps is None and (el >= max_seconds or done >= 64):
             break
     el = time.perf_counter() - t0
-    return dict(value=B * S * done / el, cores=cores, steps=done, seconds=el, batch=B, loss=loss)
+    return dict(value=B * S * done / el, cores=cores, steps=done, seconds=el, batch=B, loss=loss, losses=losses)
 
 
 def run_reference(args, c, rank, world):
@@ -170,19 +184,20 @@ def run_reference(args, c, rank, world):
     # bound the per-step sample so K+W steps end within a few minutes: calibrate on B/8 rows
     B = c["batch_size"]
     probe_b = max(1, B // 8)
-    probe = cpu_restatement_rate(c, 5.0, 1, steps=1, batch=probe_b)
+    th = best_cpu_threads(c)
+    probe = cpu_restatement_rate(c, 5.0, 1, steps=1, batch=probe_b, threads=th)
     per_row = probe["seconds"] / probe_b
     budget = 150.0 / max(1, args.steps + args.warmup)
     bs = B
     while bs > 1 and per_row * bs > budget:
         bs //= 2
-    r = cpu_restatement_rate(c, 1e9, args.warmup, steps=args.steps, batch=bs)
+    r = cpu_restatement_rate(c, 1e9, args.warmup, steps=args.steps, batch=bs, threads=th)
     sample = "%d warm-up + %d steps of [%d of %d sequences x S=%d] per step" % (args.warmup, r["steps"], bs, B, c["seq_length"])
     line = {"impl": "reference", "metric": "train_chars_per_sec", "value": r["value"], "unit": "chars/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * r["seconds"] / r["steps"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": c["desc"], "name": args.config, "host_threads": r["cores"]},
+            "config": {"workload": c["desc"], "name": args.config, "host_threads": r["cores"], "host_cpus": os.cpu_count()},
             "cpu_baseline": {"value": r["value"], "unit": "chars/s", "cores": r["cores"], "kind": "port", "sample": sample},
             "e2e": {"value": r["value"], "unit": "chars/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "TF 1.8 (requirements.txt:2) is not installable here; this is the PyTorch-CPU restatement of "
@@ -197,11 +212,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", default=os.environ.get("CRNN_BENCH_CONFIG", "c3"), choices=sorted(CONFIGS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default=None, choices=["fp32", "bf16"],
+                    help="default: fp32 for c1 (the 1e-4 parity mode), bf16 tensor-core contractions for c3-c5 (BASELINE.md 4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     c = CONFIGS[args.config]
+    if args.precision is None:
+        args.precision = "fp32" if args.config == "c1" else "bf16"
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -330,11 +348,22 @@ def main():
 
     if world > 1:
         dist.barrier()
-    cpu = None
+    cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_restatement_rate(c, 12.0, 1)
+        r = cpu_restatement_rate(c, 12.0, 1, threads=best_cpu_threads(c))
         cpu = {"value": r["value"], "unit": "chars/s", "cores": r["cores"], "kind": "port",
                "sample": "1 warm-up + %d full steps (%d chars each) in %.1f s" % (r["steps"], B * S, r["seconds"])}
+        # loss parity: the same first steps (same seed-0 weights, same batches) on the GPU path
+        m2 = Model(margs, device="cuda:%d" % local_rank, seed=0, precision=args.precision)
+        m2.assign_lr(0.002)
+        X0, Y0 = synthetic_ids(c, min(64 + 1, 8), 1234)
+        nbm = X0.shape[1] // S
+        gl = [m2.step(X0[:, (k % nbm) * S:(k % nbm + 1) * S], Y0[:, (k % nbm) * S:(k % nbm + 1) * S])[0]
+              for k in range(min(len(r["losses"]), 4))]
+        rel = max(abs(a_ - b_) / abs(b_) for a_, b_ in zip(gl, r["losses"]))
+        parity = {"steps": len(gl), "max_rel_loss_diff": rel, "gpu": gl, "cpu": r["losses"][:len(gl)],
+                  "tolerance": 1e-4 if args.precision == "fp32" else 2e-2}
+        del m2
     if rank == 0:
         line = {"metric": "train_chars_per_sec", "value": value, "unit": "chars/s", "n_gpus": world, "steps": K,
                 "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -344,7 +373,7 @@ def main():
                            "l2": ("256 MB flush write between timed steps (excluded from timing)" if flush else
                                   "per-step working set %.0f MB > 126 MB L2, new batch every step" % (ws_bytes / 1e6))},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-                "cpu_baseline": cpu, "phases_ms": phases, "final_loss": final_loss}
+                "cpu_baseline": cpu, "loss_parity": parity, "phases_ms": phases, "final_loss": final_loss}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
