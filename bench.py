@@ -177,7 +177,7 @@ def cpu_restatement_rate(c, max_seconds, warmup, steps=None, batch=None, seed=0,
     return dict(value=B * S * done / el, cores=cores, steps=done, seconds=el, batch=B, loss=loss, losses=losses)
 
 
-def run_reference(args, c, rank, world):
+def run_reference(args, c, rank, world, emit):
     """--impl reference: the reference's CPU path (restated; TF 1.8 is not installable)."""
     if rank != 0:
         return
@@ -202,10 +202,21 @@ def run_reference(args, c, rank, world):
             "e2e": {"value": r["value"], "unit": "chars/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "TF 1.8 (requirements.txt:2) is not installable here; this is the PyTorch-CPU restatement of "
                     "model.py:8-98 op for op (oracle/torch_restatement.py) on all host threads"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
+    # Only the JSON line may reach stdout: libraries (NCCL's version banner, torchrun notices)
+    # print there too, so stdout is pointed at stderr until the line is ready.
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
+
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -224,7 +235,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        run_reference(args, c, rank, world)
+        run_reference(args, c, rank, world, emit)
         return
     args.warmup = max(args.warmup, 3)
 
@@ -317,13 +328,16 @@ def main():
     # ---- per-phase timing of the same step (CUDA events on the launching stream) ---------
     pk = peaks()
     roofline = phases = None
+    nprof = min(K, 10)
+    arr = (ctypes.c_double * _lib.NUM_PHASES)()
     if rank == 0:
-        nprof = min(K, 10)
-        arr = (ctypes.c_double * _lib.NUM_PHASES)()
         _lib.check(lib.crnn_profile_enable(model._h, 1))
-        for k in range(nprof):
-            model.step_async(*dev_batch(W + k))
+    for k in range(nprof):                                    # every rank steps (the all-reduce is collective)
+        model.step_async(*dev_batch(W + k))
+        if rank == 0:
             _lib.check(lib.crnn_profile_read(model._h, arr, 0))
+    barrier()
+    if rank == 0:
         _lib.check(lib.crnn_profile_enable(model._h, 0))
         phases = {lib.crnn_profile_phase_name(i).decode(): arr[i] / nprof for i in range(_lib.NUM_PHASES)}
         fl, by = phase_flops(c), phase_bytes(c, model.P)
@@ -374,7 +388,7 @@ def main():
                                   "per-step working set %.0f MB > 126 MB L2, new batch every step" % (ws_bytes / 1e6))},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "cpu_baseline": cpu, "loss_parity": parity, "phases_ms": phases, "final_loss": final_loss}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
