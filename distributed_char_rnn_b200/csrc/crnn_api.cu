@@ -51,7 +51,7 @@ struct WsPlan {
 };
 
 struct RecPlanTc {
-    int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd;
+    int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
     size_t smem_fwd, smem_bwd;
 };
 
@@ -70,6 +70,7 @@ struct crnn_handle {
     int64_t emb_off;
     RecPlan fwd, bwd;
     RecPlanTc tcp;
+    long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
     int fast_act;
     WsPlan ws;
@@ -187,6 +188,13 @@ static int plan_recurrence_tc(const crnn_handle* h, RecPlanTc* out) {
         o->npass = ceil_div(BT, 128);
         o->box_rows = o->npass > 1 ? 128 : std::min(128, (BT + 7) & ~7);
         const int rows = std::min(128, BT);
+        // MMA orientation: cost ~ N with M fixed at 128, so put the smaller of (gate columns, rows) on N
+        const int rows16 = (rows + 15) & ~15;
+        const int sw_env = env_int("CRNN_TC_SWAP", -1);
+        o->swap_fwd = (g1 * HC <= 128 && rows16 < g1 * HC) ? 1 : 0;
+        o->swap_bwd = (HC <= 128 && rows16 < HC) ? 1 : 0;
+        if (sw_env == 0) o->swap_fwd = o->swap_bwd = 0;
+        if (sw_env == 1) { o->swap_fwd = g1 * HC <= 128; o->swap_bwd = HC <= 128; }
         o->zs_fwd = rows * (g1 * HC + 1);
         o->zs_bwd = rows * (HC + 1);
         o->smem_fwd = tc::rt_smem_bytes((size_t)nkb * g1 * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, o->zs_fwd);
@@ -501,17 +509,26 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles; a.npass = p.npass; a.box_rows = p.box_rows;
     a.fast_act = h->fast_act;
     a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
+    a.swap = backward ? p.swap_bwd : p.swap_fwd;
+    a.dbg = (!backward && env_int("CRNN_TC_DEBUG", 0)) ? h->dbg_ptr : nullptr;
     CUtensorMap t0, t1, w0, w1;
     int rc;
+    // ring geometry is per launch (every contraction of the kernel shares the ring and its barriers):
+    // sized for the shortest K extent, H
+    a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64));
+    a.nst = tc::rt_num_stages(p.box_rows, a.ckb);
+    auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
+        return tc::make_tmap_bf16(m, base, rows, cols, ld, p.box_rows);
+    };
     if (!backward) {
-        rc = tc::make_tmap_bf16(&t0, a.hxb, (int64_t)(S + 1) * B, H, H, p.box_rows);
-        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&t1, a.rsb, (int64_t)S * B, H, H, p.box_rows) : (t1 = t0, CRNN_OK);
+        rc = amap(&t0, a.hxb, (int64_t)(S + 1) * B, H, H);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1, a.rsb, (int64_t)S * B, H, H) : (t1 = t0, CRNN_OK);
         if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, wr, (int64_t)p.nslices * GW * p.HC, H, H, g1 * p.HC);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, wr, (int64_t)p.nslices * GW * p.HC, H, H, p.HC) : (w1 = w0, CRNN_OK);
     } else {
         const int64_t zw = (int64_t)GZ * H;
-        rc = tc::make_tmap_bf16(&t0, a.dzb, (int64_t)(S + 1) * B, (int64_t)g1 * H, zw, p.box_rows);
-        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&t1, a.dzb + 2 * H, (int64_t)(S + 1) * B, H, zw, p.box_rows) : (t1 = t0, CRNN_OK);
+        rc = amap(&t0, a.dzb, (int64_t)(S + 1) * B, (int64_t)g1 * H, zw);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1, a.dzb + 2 * H, (int64_t)(S + 1) * B, H, zw) : (t1 = t0, CRNN_OK);
         if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, pbf_W, 2 * H, (int64_t)g1 * H, (int64_t)g1 * H, p.HC);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, pbf_Wc, 2 * H, H, H, p.HC) : (w1 = w0, CRNN_OK);
     }
@@ -564,6 +581,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     const int gw = h->GS * H;
     const int sc = h->sm_count;
     prof_mark(h, st, CRNN_PHASE_MISC);
+    h->dbg_ptr = reinterpret_cast<long long*>((char*)ws + 24576);      // 8 KB after the barrier blocks
     int rc = refresh_bf16_params(h, params, ws, st);
     if (rc != CRNN_OK) return rc;
     const bf16_t* pbf = wsb(ws, h->ws.pbf);

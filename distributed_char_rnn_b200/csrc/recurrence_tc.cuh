@@ -20,15 +20,37 @@ namespace crnn {
 namespace tc {
 
 constexpr int RT_THREADS = 192;
-constexpr int RT_STAGES = 4;
-constexpr int RT_ASTAGE = 128 * 128;      // bytes: 128 rows x 64 bf16 (one K block of the A tile)
+constexpr int RT_RING_BYTES = 64 * 1024;  // TMA ring for the streamed operand
+constexpr int RT_MAX_STAGES = 32;
+constexpr int RT_MROWS_BYTES = 128 * 128; // bytes an M=128 operand reads from a tile base (128 rows x 64 bf16)
+// Ring geometry.  A tile is one K block (64 bf16 = 128 B per row) of `box_rows` rows; a STAGE is
+// `chunk_kb` consecutive tiles whose TMA loads are issued back to back on ONE mbarrier (one wait /
+// expect_tx / commit per chunk instead of per tile).  Tiles are packed, so an M=128 read that runs past a short
+// tile sees later tiles / the slack at the ring's end; those products fall in accumulator rows nobody
+// reads.  Small batch tiles get a whole phase's K extent in one or two instructions.
+__host__ __device__ inline int rt_tile_bytes(int box_rows) { return ((box_rows + 7) & ~7) * 128; }
+__host__ __device__ inline int rt_chunk_kb(int box_rows, int nkb) {
+    int c = (24 * 1024) / rt_tile_bytes(box_rows);
+    if (c < 1) c = 1;
+    if (c > nkb) c = nkb;
+    if (c > 256) c = 256;
+    if (c == nkb && nkb >= 4 && (nkb & 1) == 0) c = nkb / 2;     // two instructions: MMAs start on the first half
+    return c;
+}
+__host__ __device__ inline int rt_num_stages(int box_rows, int chunk_kb) {
+    int n = (RT_RING_BYTES - RT_MROWS_BYTES + rt_tile_bytes(box_rows)) / (rt_tile_bytes(box_rows) * chunk_kb);
+    if (n < 2) n = 2;
+    return n > RT_MAX_STAGES ? RT_MAX_STAGES : n;
+}
 
 struct RecTcArgs {
     int B, H, S;
     int HC, BT, nslices, ntiles, npass;
     int GS;                     // gate-stash row width / H
     int box_rows;               // rows per A-tile TMA box
+    int ckb, nst;               // ring geometry, fixed per launch: K tiles per stage, number of stages
     int fast_act;               // 1: MUFU.TANH activations
+    int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
     float* gates;               // [S,B,GS*H]  in: x-projection + bias, out: activations
     float* hx;                  // [(S+1),B,H]
@@ -40,6 +62,7 @@ struct RecTcArgs {
     __nv_bfloat16* hxb;         // [(S+1),B,H] bf16 copy of hx (fwd out; MMA operand)
     __nv_bfloat16* rsb;         // gru [S,B,H] bf16 r*h (fwd out; MMA operand)
     __nv_bfloat16* dzb;         // bwd [(S+1),B,GZ*H] bf16 copy of dz (MMA operand)
+    long long* dbg;             // optional: CTA 0 writes clock64 stamps [phase][8] (CRNN_TC_DEBUG)
     unsigned* barrier;          // one zeroed counter per batch tile: rows of different tiles never interact
 };
 
@@ -60,6 +83,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+#define RT_STAMP(slot)                                                                     \
+    do {                                                                                   \
+        if (a.dbg && blockIdx.x == 0 && dbg_phase < 120) a.dbg[dbg_phase * 8 + (slot)] = clock64(); \
+    } while (0)
+
 struct RtSmem {
     uint8_t* wsa; uint8_t* wsb; uint8_t* ring; float* zs;
     uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar;
@@ -71,11 +99,11 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     uint8_t* p = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     s.wsa = p; p += wsa_bytes;
     s.wsb = p; p += wsb_bytes;
-    s.ring = p; p += RT_STAGES * RT_ASTAGE;
+    s.ring = p; p += RT_RING_BYTES;
     s.zs = reinterpret_cast<float*>(p); p += (size_t)((zs_floats + 3) & ~3) * 4;
     s.a_full = reinterpret_cast<uint64_t*>(p);
-    s.a_empty = s.a_full + RT_STAGES;
-    s.z_full = s.a_empty + RT_STAGES;
+    s.a_empty = s.a_full + RT_MAX_STAGES;
+    s.z_full = s.a_empty + RT_MAX_STAGES;
     s.z_empty = s.z_full + 1;
     s.w_bar = s.z_empty + 1;
     s.tmem_slot = reinterpret_cast<uint32_t*>(s.w_bar + 1);
@@ -83,7 +111,7 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
 }
 
 inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats) {
-    return wsa_bytes + wsb_bytes + RT_STAGES * RT_ASTAGE + (size_t)((zs_floats + 3) & ~3) * 4 + 256 + 1024;
+    return wsa_bytes + wsb_bytes + RT_RING_BYTES + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024;
 }
 
 // Role-private pipeline state.
@@ -94,28 +122,45 @@ struct RtPipe {
 
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
-__device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows) {
-    for (int kb = 0; kb < nkb; ++kb, ++p.ring_i) {
-        const int st = p.ring_i % RT_STAGES;
-        mbar_wait(&s.a_empty[st], ((p.ring_i / RT_STAGES) & 1) ^ 1);
-        mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u);
-        tma_load_2d(s.ring + st * RT_ASTAGE, tmA, &s.a_full[st], kb * 64, arow);
+__device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
+                                           int ckb, int nst) {
+    const int tile = rt_tile_bytes(box_rows);
+    for (int kb = 0; kb < nkb; kb += ckb, ++p.ring_i) {
+        const int st = p.ring_i % nst;
+        const int n = min(ckb, nkb - kb);
+        mbar_wait(&s.a_empty[st], ((p.ring_i / nst) & 1) ^ 1);
+        mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u * (uint32_t)n);      // one barrier per chunk of tiles
+        for (int j = 0; j < n; ++j)
+            tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow);
     }
 }
-__device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb) {
+// swap == 0: D[128 batch rows x nc gate columns]   (A = streamed rows, B = resident weights)
+// swap == 1: D[128 gate columns x nrows16 batch rows] (A = resident weights, B = streamed rows):
+//            the MMA cost is max(M,128)*N/256 cycles per K=16, so the smaller of (nc, rows) goes to N.
+//            Weight regions hold nc < 128 rows; the rows the M=128 operand reads past them are other
+//            resident data whose products land in accumulator lanes nobody reads.
+__device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
+                                       int swap, int nrows16, int box_rows, int ckb, int nst) {
+    const int tile = rt_tile_bytes(box_rows);
     mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
     tc_fence_after();
-    const uint32_t idesc = idesc_bf16(128, nc, 0, 0);
+    const uint32_t idesc = swap ? idesc_bf16(128, nrows16, 0, 0) : idesc_bf16(128, nc, 0, 0);
     const uint32_t w0 = smem_u32(wbase);
-    for (int kb = 0; kb < nkb; ++kb, ++p.ring_i) {
-        const int st = p.ring_i % RT_STAGES;
-        mbar_wait(&s.a_full[st], (p.ring_i / RT_STAGES) & 1);
+    for (int kb0 = 0; kb0 < nkb; kb0 += ckb, ++p.ring_i) {
+        const int st = p.ring_i % nst;
+        mbar_wait(&s.a_full[st], (p.ring_i / nst) & 1);
         tc_fence_after();
-        const uint32_t sa = smem_u32(s.ring + st * RT_ASTAGE);
-        const uint32_t sb = w0 + (uint32_t)kb * (uint32_t)nc * 128u;
+        const int n = min(ckb, nkb - kb0);
+        for (int j = 0; j < n; ++j) {
+            const int kb = kb0 + j;
+            const uint32_t sa = smem_u32(s.ring + (st * ckb + j) * tile);
+            const uint32_t sb = w0 + (uint32_t)kb * (uint32_t)nc * 128u;
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-            mma_bf16(tmem, desc_kmajor(sa + k * 32), desc_kmajor(sb + k * 32), idesc, (kb | k) != 0);
+            for (int k = 0; k < 4; ++k) {
+                if (swap) mma_bf16(tmem, desc_kmajor(sb + k * 32), desc_kmajor(sa + k * 32), idesc, (kb | k) != 0);
+                else      mma_bf16(tmem, desc_kmajor(sa + k * 32), desc_kmajor(sb + k * 32), idesc, (kb | k) != 0);
+            }
+        }
         mma_commit(&s.a_empty[st]);
     }
     mma_commit(s.z_full);
@@ -125,30 +170,46 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
 // Grid barrier, split: epilogue threads publish, the TMA producer waits before touching
 // rows written by other CTAs (generic-proxy writes -> async-proxy reads need the proxy fence).
 __device__ __forceinline__ void rt_publish(unsigned* counter, int epi_tid) {
-    __threadfence();
-    epi_bar_sync();
-    if (epi_tid == 0) {
-        __threadfence();
+    epi_bar_sync();                                  // every epilogue thread's stores happen-before ...
+    if (epi_tid == 0)                                // ... this release, which is cumulative over them
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
-    }
 }
 __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned target) {
-    while (ld_acquire_u32(counter) < target) { }
+    unsigned v;
+    do {   // relaxed polls (one L2 round trip each) ...
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    } while (v < target);
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");  // ... then one acquire, and hand over to the async proxy (TMA)
     asm volatile("fence.proxy.async;" ::: "memory");
 }
 
-// TMEM accumulator rows [0,nr) x columns [0,nc) -> shared Zs[r*ldz + c] (ldz odd: conflict-free).
-// A warp can only read its own TMEM lane quarter; quarters with no valid row skip the load.
-__device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int lane, int nr, int nc, float* __restrict__ Zs, int ldz) {
-    if (32 * q < nr) {
-        float v[32];
-        const int r = 32 * q + lane;
-        for (int c0 = 0; c0 < nc; c0 += 32) {
-            tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
-            if (r < nr) {
+// Accumulator -> shared Zs[r*ldz + c] for batch rows r < nr and gate columns c < nc (ldz odd).
+// A warp can only read its own TMEM lane quarter; quarters holding nothing useful skip the load.
+__device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int lane, int nr, int nc, float* __restrict__ Zs, int ldz,
+                                        int swap) {
+    float v[32];
+    if (!swap) {
+        if (32 * q < nr) {                           // lanes = batch rows
+            const int r = 32 * q + lane;
+            for (int c0 = 0; c0 < nc; c0 += 32) {
+                tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
+                if (r < nr) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (c0 + i < nc) Zs[r * ldz + c0 + i] = v[i];
+                    for (int i = 0; i < 32; ++i)
+                        if (c0 + i < nc) Zs[r * ldz + c0 + i] = v[i];
+                }
+            }
+        }
+    } else {
+        if (32 * q < nc) {                           // lanes = gate columns, TMEM columns = batch rows
+            const int c = 32 * q + lane;
+            for (int r0 = 0; r0 < nr; r0 += 32) {
+                tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)r0, v);
+                if (c < nc) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (r0 + i < nr) Zs[(r0 + i) * ldz + c] = v[i];
+                }
             }
         }
     }
@@ -183,7 +244,7 @@ __device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ld
     do {                                                                          \
         mbar_wait(s.z_full, p.z_i & 1);                                           \
         tc_fence_after();                                                         \
-        zs_dump(tmem, q, lane, nr_, nc_, Zs, ldz);                                \
+        zs_dump(tmem, q, lane, nr_, nc_, Zs, ldz, a.swap);                                \
         tc_fence_before();                                                        \
         mbar_arrive(s.z_empty);                                                   \
         ++p.z_i;                                                                  \
@@ -216,15 +277,15 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
-    while ((int)tcols < NCA) tcols <<= 1;
+    while ((int)tcols < (a.swap ? 128 : NCA)) tcols <<= 1;
 
     // zero the ring once: rows past the TMA box are never written and must not hold NaNs
-    for (int i = threadIdx.x; i < RT_STAGES * RT_ASTAGE / 16; i += RT_THREADS)
+    for (int i = threadIdx.x; i < RT_RING_BYTES / 16; i += RT_THREADS)
         reinterpret_cast<uint4*>(s.ring)[i] = make_uint4(0, 0, 0, 0);
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, 128); mbar_init(s.w_bar, 1);
         fence_barrier_init();
     }
@@ -250,9 +311,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
             }
             for (int t = 0; t < a.S; ++t) {
                 for (int ph = 0; ph < nphase; ++ph) {
+                    const int dbg_phase = (int)phases_done;
+                    RT_STAMP(0);
                     if (phases_done > 0) rt_await(a.barrier + tile, phases_done * a.nslices);
+                    RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst);
+                    RT_STAMP(2);
                     ++phases_done;
                 }
             }
@@ -261,9 +326,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         if (lane == 0) {
             mbar_wait(s.w_bar, 0);
             for (int t = 0; t < a.S; ++t)
-                for (int ph = 0; ph < nphase; ++ph)
+                for (int ph = 0; ph < nphase; ++ph) {
+                    const int dbg_phase = t * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb);
+                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
+                    RT_STAMP(3);
+                }
         }
     } else {
         const int q = warp & 3;
@@ -302,7 +370,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                 }
                             }
                         }
+                        const int dbg_phase = t * nphase + ph;
+                        if (epi_tid == 0) RT_STAMP(4);
                         if (base == 0) RT_TAKE_ACC(nr, ph == 0 ? NCA : HC);
+                        if (epi_tid == 0) RT_STAMP(5);
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
                             if (!e[u].ok) continue;
@@ -340,7 +411,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     }
                     epi_bar_sync();          // Zs is reused by the next pass / phase
                 }
+                const int dbg_phase = t * nphase + ph;
+                if (epi_tid == 0) RT_STAMP(6);
                 rt_publish(a.barrier + tile, epi_tid);
+                if (epi_tid == 0) RT_STAMP(7);
             }
         }
     }
@@ -376,14 +450,14 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, zw = (int64_t)GZ * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
-    while ((int)tcols < HC) tcols <<= 1;
+    while ((int)tcols < (a.swap ? 128 : HC)) tcols <<= 1;
 
-    for (int i = threadIdx.x; i < RT_STAGES * RT_ASTAGE / 16; i += RT_THREADS)
+    for (int i = threadIdx.x; i < RT_RING_BYTES / 16; i += RT_THREADS)
         reinterpret_cast<uint4*>(s.ring)[i] = make_uint4(0, 0, 0, 0);
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, 128); mbar_init(s.w_bar, 1);
         fence_barrier_init();
     }
@@ -408,13 +482,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (t + 1 < a.S) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst);
                     ++phases_done;
                 }
             }
@@ -424,9 +498,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.S - 1; t >= 0; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
             }
         }
     } else {

@@ -107,6 +107,10 @@ BF16_SHAPES = [
     ("lstm", 64, 1, 5, 150, 20, {"CRNN_TC_TILES": 1}),      # BT = 150 -> two 128-row passes
     ("gru", 128, 1, 4, 260, 20, {"CRNN_TC_TILES": 2}),      # BT = 130 -> two passes, ragged
     ("rnn", 96, 2, 5, 40, 30, {"CRNN_TC_HC": 16}),
+    # both MMA orientations forced (weights on M / batch rows on M)
+    ("lstm", 32, 2, 6, 20, 11, {"CRNN_TC_SWAP": 1}), ("gru", 64, 2, 5, 40, 17, {"CRNN_TC_SWAP": 1}),
+    ("rnn", 128, 1, 5, 24, 17, {"CRNN_TC_SWAP": 1}), ("gru", 64, 2, 5, 40, 17, {"CRNN_TC_SWAP": 0}),
+    ("lstm", 32, 1, 4, 150, 9, {"CRNN_TC_SWAP": 1, "CRNN_TC_TILES": 1}),
 ]
 
 
