@@ -37,6 +37,7 @@ SIGNATURES = {
     "crnn_workspace_bytes": (c_i64, [c_vp]),
     "crnn_forward_backward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "crnn_clip_adam": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_i64, c_f32, c_vp, c_vp, c_vp]),
+    "crnn_clip_adam_noalloc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_i64, c_f32, c_vp, c_vp]),
     "crnn_train_step": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_i64,
                                 c_vp, c_vp]),
     "crnn_forward": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -853,6 +853,58 @@ int crnn_clip_adam(crnn_handle* h, float* params, const float* grads, float* m, 
     return CRNN_OK;
 }
 
+// ---- optimiser step for callers that cannot hand us a workspace -------------------------------
+// The partial sums of the global norm normally live in the caller's workspace.  This variant keeps
+// them in a fixed array that is part of the library image, so the call needs no buffer from the
+// caller and performs no allocation of its own.  One partial per CRNN_NOALLOC_SPAN gradient floats.
+#define CRNN_NOALLOC_MAX_PARTIALS 8192
+#define CRNN_NOALLOC_SPAN 16384
+static __device__ __align__(256) double g_noalloc_partials[CRNN_NOALLOC_MAX_PARTIALS];   // 64 KB on every GPU that loads the library
+// In host code `g_noalloc_partials` is only a stand-in for the symbol, not a device address: the
+// address each device gave the array is looked up once (below) and cached per device ordinal.
+static double* g_noalloc_partials_addr[64] = {nullptr};
+
+int crnn_clip_adam_noalloc(crnn_handle* h, float* params, const float* grads, float* m, float* v, float lr, float clip,
+                           int64_t step, float mult, float* gnorm_out, void* stream) {
+    if (!h) return set_err(CRNN_ERR_ARG, "null handle");
+    if (!params || !grads || !m || !v) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (step < 1) return set_err(CRNN_ERR_ARG, "Adam step must be >= 1");
+    const int dev = h->cfg.device;
+    if (dev < 0 || dev >= 64) return set_err(CRNN_ERR_ARG, "crnn_clip_adam_noalloc: device ordinal %d outside [0,64)", dev);
+    const int64_t need = ceil_div64(h->P, CRNN_NOALLOC_SPAN);
+    if (need > CRNN_NOALLOC_MAX_PARTIALS)
+        return set_err(CRNN_ERR_ARG,
+                       "crnn_clip_adam_noalloc: %lld parameter floats need %lld partial sums, the built-in scratch holds %d "
+                       "(limit %lld floats); use crnn_clip_adam with a caller workspace",
+                       (long long)h->P, (long long)need, CRNN_NOALLOC_MAX_PARTIALS,
+                       (long long)CRNN_NOALLOC_MAX_PARTIALS * CRNN_NOALLOC_SPAN);
+    CRNN_CUDA(cudaSetDevice(dev));
+    if (!g_noalloc_partials_addr[dev]) {
+        // first call on this device: resolve the array's device address (a driver query, not an allocation)
+        double* addr = nullptr;
+        CRNN_CUDA(cudaGetSymbolAddress((void**)&addr, g_noalloc_partials));
+        if (!addr) return set_err(CRNN_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the built-in scratch");
+        g_noalloc_partials_addr[dev] = addr;
+    }
+    double* partials = g_noalloc_partials_addr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+    if (step < h->pow_step) { h->pow_step = 0; h->b1p = 1.0f; h->b2p = 1.0f; }
+    while (h->pow_step < step) { h->b1p *= kBeta1; h->b2p *= kBeta2; ++h->pow_step; }
+    const int64_t emb_end = h->emb_off + (int64_t)h->cfg.vocab_size * h->cfg.rnn_size;
+    // Every partial the update kernel reads is rewritten here first, so nothing left in the array by
+    // an earlier call (it is shared by all calls) needs clearing.
+    sqnorm_partials_kernel<<<(int)need, 256, 0, st>>>(grads, h->P, h->emb_off, emb_end, partials);
+    CRNN_LAUNCH_CHECK("sqnorm_partials_kernel");
+    AdamArgs a{};
+    a.p = params; a.g = grads; a.m = m; a.v = v; a.p_bf16 = nullptr; a.P = h->P;
+    a.partial = partials; a.npartial = (int)need;
+    a.lr_t = lr * sqrtf(1.0f - h->b2p) / (1.0f - h->b1p);
+    a.beta1 = kBeta1; a.beta2 = kBeta2; a.eps = kEps; a.clip = clip; a.mult = mult; a.gnorm_out = gnorm_out;
+    clip_adam_kernel<<<grid_for(h->P / 4, h->sm_count), 256, 0, st>>>(a);
+    CRNN_LAUNCH_CHECK("clip_adam_kernel");
+    return CRNN_OK;
+}
+
 int crnn_train_step(crnn_handle* h, const int32_t* x, const int32_t* y, int64_t ld, float* state, float* params,
                     float* grads, float* m, float* v, float lr, float clip, int64_t step, void* ws, void* stream) {
     int rc = crnn_forward_backward(h, x, y, ld, state, state, params, grads, ws, stream);

@@ -105,6 +105,27 @@ int crnn_clip_adam(crnn_handle* h, float* d_params, const float* d_grads, float*
                    float lr, float grad_clip, int64_t step, float grad_mult,
                    float* d_gnorm_out, void* d_workspace, void* stream);
 
+/* crnn_clip_adam for callers that have no device buffer to spare and must not allocate one.
+ * (No counterpart in the reference: TensorFlow owns all memory there.)  Who needs it: code that
+ * runs after the process has handed every free byte of HBM to some other pool (a framework's
+ * caching allocator, a memory-capped serving sandbox), and code on a path where a cudaMalloc is
+ * not acceptable because it serialises the whole device or may simply fail - an optimiser hook
+ * called from inside somebody else's training loop, a fault-recovery path that has to apply one
+ * last update while memory is exhausted.  Same arguments and arithmetic as crnn_clip_adam minus
+ * the workspace: the global-norm partial sums go to a fixed 64 KB array that is part of the
+ * library image on every GPU that loads it (until the process exits).
+ *   - limit: crnn_flat_size(h) <= 8192 * 16384 = 134,217,728 floats; larger models get an error
+ *     that says so, and should use crnn_clip_adam.
+ *   - the call makes no cudaMalloc / cudaFree and uses no allocating library routine.
+ *   - the first call on each GPU looks up the array's device address (cudaGetSymbolAddress) and
+ *     caches it; make that first call outside any stream capture.
+ *   - all calls share the one array.  Nothing in it has to be zero on entry (each call rewrites
+ *     every partial it later reads), but two calls whose kernels overlap on the GPU - different
+ *     streams, different handles, different threads - race on it: serialise them.            */
+int crnn_clip_adam_noalloc(crnn_handle* h, float* d_params, const float* d_grads, float* d_m, float* d_v,
+                           float lr, float grad_clip, int64_t step, float grad_mult,
+                           float* d_gnorm_out, void* stream);
+
 /* The whole train_op of train.py:199 for a single process: forward_backward + clip_adam. */
 int crnn_train_step(crnn_handle* h, const int32_t* d_x, const int32_t* d_y, int64_t ld_xy,
                     float* d_state, float* d_params, float* d_grads, float* d_m, float* d_v,
