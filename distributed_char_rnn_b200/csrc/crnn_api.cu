@@ -536,7 +536,8 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     }
     if (rc != CRNN_OK) return rc;
     void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
-        backward ? tc::rec_bwd_tc_kernel<MODEL> : tc::rec_fwd_tc_kernel<MODEL>;
+        h->fast_act ? (backward ? tc::rec_bwd_tc_kernel<MODEL, true> : tc::rec_fwd_tc_kernel<MODEL, true>)
+                    : (backward ? tc::rec_bwd_tc_kernel<MODEL, false> : tc::rec_fwd_tc_kernel<MODEL, false>);
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     void* args[] = {&t0, &t1, &w0, &w1, &a};

@@ -19,7 +19,9 @@
 namespace crnn {
 namespace tc {
 
-constexpr int RT_THREADS = 192;
+constexpr int RT_EPI_WARPS = 8;             // two per SM sub-partition: one hides the other's latencies
+constexpr int RT_EPI_THREADS = RT_EPI_WARPS * 32;
+constexpr int RT_THREADS = 64 + RT_EPI_THREADS;
 constexpr int RT_RING_BYTES = 64 * 1024;  // TMA ring for the streamed operand
 constexpr int RT_MAX_STAGES = 32;
 constexpr int RT_MROWS_BYTES = 128 * 128; // bytes an M=128 operand reads from a tile base (128 rows x 64 bf16)
@@ -73,10 +75,10 @@ __device__ __forceinline__ float tanh_mufu(float x) {
 }
 // `fast` (block-uniform): one MUFU.TANH per activation (|err| ~ 5e-4, well under bf16's 4e-3
 // operand rounding) instead of the accurate expf/tanhf sequences.
-#define fast_tanh(x) (a.fast_act ? tanh_mufu(x) : tanhf(x))
-#define fast_sigmoid(x) (a.fast_act ? fmaf(0.5f, tanh_mufu(0.5f * (x)), 0.5f) : 1.0f / (1.0f + expf(-(x))))
+#define fast_tanh(x) (FAST ? tanh_mufu(x) : tanhf(x))
+#define fast_sigmoid(x) (FAST ? fmaf(0.5f, tanh_mufu(0.5f * (x)), 0.5f) : 1.0f / (1.0f + expf(-(x))))
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(RT_EPI_THREADS) : "memory"); }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -85,7 +87,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 #define RT_STAMP(slot)                                                                     \
     do {                                                                                   \
-        if (a.dbg && blockIdx.x == 0 && dbg_phase < 120) a.dbg[dbg_phase * 8 + (slot)] = clock64(); \
+        if (a.dbg && blockIdx.x == 0 && dbg_phase < 60) a.dbg[dbg_phase * 16 + (slot)] = clock64(); \
     } while (0)
 
 struct RtSmem {
@@ -185,13 +187,14 @@ __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned targe
 
 // Accumulator -> shared Zs[r*ldz + c] for batch rows r < nr and gate columns c < nc (ldz odd).
 // A warp can only read its own TMEM lane quarter; quarters holding nothing useful skip the load.
-__device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int lane, int nr, int nc, float* __restrict__ Zs, int ldz,
-                                        int swap) {
+__device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane, int nr, int nc, float* __restrict__ Zs,
+                                        int ldz, int swap) {
     float v[32];
+    constexpr int NH = RT_EPI_WARPS / 4;             // warps per lane quarter
     if (!swap) {
         if (32 * q < nr) {                           // lanes = batch rows
             const int r = 32 * q + lane;
-            for (int c0 = 0; c0 < nc; c0 += 32) {
+            for (int c0 = 32 * half; c0 < nc; c0 += 32 * NH) {
                 tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
                 if (r < nr) {
 #pragma unroll
@@ -203,7 +206,7 @@ __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int lane, int nr, 
     } else {
         if (32 * q < nc) {                           // lanes = gate columns, TMEM columns = batch rows
             const int c = 32 * q + lane;
-            for (int r0 = 0; r0 < nr; r0 += 32) {
+            for (int r0 = 32 * half; r0 < nr; r0 += 32 * NH) {
                 tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)r0, v);
                 if (c < nc) {
 #pragma unroll
@@ -215,7 +218,7 @@ __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int lane, int nr, 
     }
 }
 
-constexpr int RT_UB = 8;     // (row, unit) elements per epilogue thread per batch
+constexpr int RT_UB = 4;     // (row, unit) elements per epilogue thread per batch
 
 // Element -> (row, unit) mapping shared by all epilogues: consecutive threads take consecutive
 // hidden units of one batch row, so every global access of a warp is one contiguous segment.
@@ -244,7 +247,7 @@ __device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ld
     do {                                                                          \
         mbar_wait(s.z_full, p.z_i & 1);                                           \
         tc_fence_after();                                                         \
-        zs_dump(tmem, q, lane, nr_, nc_, Zs, ldz, a.swap);                                \
+        zs_dump(tmem, q, ehalf, lane, nr_, nc_, Zs, ldz, a.swap);                                \
         tc_fence_before();                                                        \
         mbar_arrive(s.z_empty);                                                   \
         ++p.z_i;                                                                  \
@@ -256,7 +259,7 @@ __device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ld
 // of W_h this CTA's local column lc contracts with, K contiguous.  lc = jj*G1 + g for the first
 // contraction; GRU candidate rows follow at lc = 2*HC + jj.
 // ------------------------------------------------------------------------------------------
-template <int MODEL>
+template <int MODEL, bool FAST>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmH,
                                                                    const __grid_constant__ CUtensorMap tmRS,
                                                                    const __grid_constant__ CUtensorMap tmW0,
@@ -286,7 +289,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
         for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
-        mbar_init(s.z_full, 1); mbar_init(s.z_empty, 128); mbar_init(s.w_bar, 1);
+        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(s.tmem_slot, tcols);
@@ -334,7 +337,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 }
         }
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        const int ehalf = (warp - 2) >> 2;            // which of the quarter's warps this is
         const int epi_tid = (warp - 2) * 32 + lane;
         for (int t = 0; t < a.S; ++t) {
             const int64_t tB = (int64_t)t * B;
@@ -348,13 +352,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     const int nunits = nr * hcv;
                     const int b0row = b0 + ps * 128;
                     const int gstride = ph == 0 ? G1 : 1;
-                    for (int base = 0; base < nunits; base += 128 * RT_UB) {
+                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * RT_UB) {
                         // ---- issue every global load of this batch before touching the accumulator
                         EpiIdx e[RT_UB];
                         float x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], ax[RT_UB];
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
-                            e[u] = epi_index(base + u * 128 + epi_tid, nunits, hcv, ldz, gstride, b0row, j0, H, tB);
+                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, gstride, b0row, j0, H, tB);
                             x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = 0.f;
                             if (e[u].ok) {
                                 const float* g = gt + e[u].row * gw + e[u].j;
@@ -409,6 +413,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                             }
                         }
                     }
+                    { const int dbg_phase = t * nphase + ph; if (epi_tid == 0) RT_STAMP(8); if (epi_tid == RT_EPI_THREADS - 1) RT_STAMP(9); }
                     epi_bar_sync();          // Zs is reused by the next pass / phase
                 }
                 const int dbg_phase = t * nphase + ph;
@@ -429,7 +434,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
 // backward.  dh_t = dy_t + dz_{t+1} * W_h^T: the B operand is rows H+j0.. of the bf16 copy of
 // the cell kernel itself (K = gate columns, contiguous) - no packing needed.
 // ------------------------------------------------------------------------------------------
-template <int MODEL>
+template <int MODEL, bool FAST>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmZ0,   // dzb, first contraction
                                                                    const __grid_constant__ CUtensorMap tmZ1,   // gru: dzb candidate columns
                                                                    const __grid_constant__ CUtensorMap tmW0,
@@ -458,7 +463,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
         for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
-        mbar_init(s.z_full, 1); mbar_init(s.z_empty, 128); mbar_init(s.w_bar, 1);
+        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(s.tmem_slot, tcols);
@@ -504,11 +509,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             }
         }
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        const int ehalf = (warp - 2) >> 2;            // which of the quarter's warps this is
         const int epi_tid = (warp - 2) * 32 + lane;
         // zero the CTA-private carries
         if (MODEL != CRNN_MODEL_RNN) {
-            for (int idx = epi_tid; idx < bt * hcv; idx += 128) {
+            for (int idx = epi_tid; idx < bt * hcv; idx += RT_EPI_THREADS) {
                 const int r = idx / hcv, jj = idx - r * hcv;
                 a.carry0[(int64_t)(b0 + r) * H + j0 + jj] = 0.f;
             }
@@ -520,12 +526,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 const int nr = min(128, bt - ps * 128);
                 const int nunits = nr * hcv;
                 const int b0row = b0 + ps * 128;
-                for (int base = 0; base < nunits; base += 128 * RT_UB) {
+                for (int base = 0; base < nunits; base += RT_EPI_THREADS * RT_UB) {
                     EpiIdx e[RT_UB];
                     float dyv[RT_UB], x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], c0v[RT_UB], c1v[RT_UB], cr[RT_UB];
 #pragma unroll
                     for (int u = 0; u < RT_UB; ++u) {
-                        e[u] = epi_index(base + u * 128 + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
+                        e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
                         dyv[u] = x0[u] = x1[u] = x2[u] = x3[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
                         if (e[u].ok) {
                             const float* g = a.gates + e[u].row * gw + e[u].j;
@@ -586,12 +592,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     const int nr = min(128, bt - ps * 128);
                     const int nunits = nr * hcv;
                     const int b0row = b0 + ps * 128;
-                    for (int base = 0; base < nunits; base += 128 * RT_UB) {
+                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * RT_UB) {
                         EpiIdx e[RT_UB];
                         float x0[RT_UB], x1[RT_UB], hp[RT_UB], c1v[RT_UB];
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
-                            e[u] = epi_index(base + u * 128 + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
+                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
                             x0[u] = x1[u] = hp[u] = c1v[u] = 0.f;
                             if (e[u].ok) {
                                 const float* g = a.gates + e[u].row * gw + e[u].j;

@@ -8,10 +8,10 @@ rng=np.random.default_rng(0)
 x=rng.integers(0,96,(256,50)).astype(np.int32); y=rng.integers(0,96,(256,50)).astype(np.int32)
 for _ in range(3): m.step(x,y)
 torch.cuda.synchronize()
-d=m.workspace[24576:24576+8*8*100].view(torch.int64).cpu().numpy().reshape(100,8)
+d=m.workspace[24576:24576+8*16*60].view(torch.int64).cpu().numpy().reshape(60,16)
 # phases 20..39
 base=d[20,0]
-names=['prod_start','await_done','tma_issued','mma_done','epi_loaded','acc_taken','epi_computed','published']
+names=['prod_start','await_done','tma_issued','mma_done','epi_loaded','acc_taken','epi_synced','published','w0_computed','w3_computed']
 print(names)
 for p in range(20,32):
-    print(p, [int(v-d[p,0]) for v in d[p]], 'phase_len', int(d[p+1,0]-d[p,0]))
+    print(p, [int(v-d[p,0]) for v in d[p][:10]], 'phase_len', int(d[p+1,0]-d[p,0]))
