@@ -519,7 +519,9 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // sized for the shortest K extent, H
     a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64));
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb);
+    a.use3d = (H % 64 == 0 && env_int("CRNN_TC_3D", 1)) ? 1 : 0;
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
+        if (a.use3d) return tc::make_tmap_bf16_kblocks(m, base, rows, cols, ld, p.box_rows, a.ckb);
         return tc::make_tmap_bf16(m, base, rows, cols, ld, p.box_rows);
     };
     if (!backward) {

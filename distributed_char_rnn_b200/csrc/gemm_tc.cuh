@@ -108,12 +108,14 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + s * L::STAGE_BYTES);
                 const uint32_t sb = sa + L::A_BYTES;
-#pragma unroll
-                for (int k = 0; k < GT_BK / 16; ++k) {
-                    const uint64_t ad = g.a_mn ? desc_mnmajor(sa + k * 2048, 8192) : desc_kmajor(sa + k * 32);
-                    const uint64_t bd = g.b_mn ? desc_mnmajor(sb + k * 2048, 8192) : desc_kmajor(sb + k * 32);
-                    mma_bf16(tmem_base, ad, bd, idesc, (i | k) != 0);
-                }
+                // one descriptor per operand per stage, advanced by adds (K step: 32 B K-major, 2048 B MN-major)
+                const uint64_t ad = g.a_mn ? desc_mnmajor(sa, 8192) : desc_kmajor(sa);
+                const uint64_t bd = g.b_mn ? desc_mnmajor(sb, 8192) : desc_kmajor(sb);
+                const uint64_t as = g.a_mn ? 128u : 2u, bs = g.b_mn ? 128u : 2u;
+                mma_bf16(tmem_base, ad, bd, idesc, (uint32_t)(i != 0));
+                mma_bf16(tmem_base, ad + as, bd + bs, idesc, 1u);
+                mma_bf16(tmem_base, ad + 2 * as, bd + 2 * bs, idesc, 1u);
+                mma_bf16(tmem_base, ad + 3 * as, bd + 3 * bs, idesc, 1u);
                 mma_commit(&empty_bar[s]);          // frees the smem slot once these MMAs retire
             }
             mma_commit(tmem_full);                  // accumulator complete

@@ -51,6 +51,7 @@ struct RecTcArgs {
     int GS;                     // gate-stash row width / H
     int box_rows;               // rows per A-tile TMA box
     int ckb, nst;               // ring geometry, fixed per launch: K tiles per stage, number of stages
+    int use3d;                  // streamed operand maps are [kblock][row][64]: one TMA instruction per stage
     int fast_act;               // 1: MUFU.TANH activations
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
@@ -125,15 +126,20 @@ struct RtPipe {
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
-                                           int ckb, int nst) {
+                                           int ckb, int nst, int use3d) {
     const int tile = rt_tile_bytes(box_rows);
     for (int kb = 0; kb < nkb; kb += ckb, ++p.ring_i) {
         const int st = p.ring_i % nst;
         const int n = min(ckb, nkb - kb);
         mbar_wait(&s.a_empty[st], ((p.ring_i / nst) & 1) ^ 1);
-        mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u * (uint32_t)n);      // one barrier per chunk of tiles
-        for (int j = 0; j < n; ++j)
-            tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow);
+        if (use3d) {                                   // whole stage in one instruction (out-of-range k-blocks read zero)
+            mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u * (uint32_t)ckb);
+            tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb);
+        } else {
+            mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u * (uint32_t)n);  // one barrier per chunk of tiles
+            for (int j = 0; j < n; ++j)
+                tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow);
+        }
     }
 }
 // swap == 0: D[128 batch rows x nc gate columns]   (A = streamed rows, B = resident weights)
@@ -142,25 +148,38 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 //            Weight regions hold nc < 128 rows; the rows the M=128 operand reads past them are other
 //            resident data whose products land in accumulator lanes nobody reads.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
-                                       int swap, int nrows16, int box_rows, int ckb, int nst) {
+                                       int swap, int nrows16, int box_rows, int ckb, int nst, long long* stamps = nullptr) {
     const int tile = rt_tile_bytes(box_rows);
     mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
     tc_fence_after();
+    if (stamps) stamps[10] = clock64();
     const uint32_t idesc = swap ? idesc_bf16(128, nrows16, 0, 0) : idesc_bf16(128, nc, 0, 0);
     const uint32_t w0 = smem_u32(wbase);
     for (int kb0 = 0; kb0 < nkb; kb0 += ckb, ++p.ring_i) {
         const int st = p.ring_i % nst;
         mbar_wait(&s.a_full[st], (p.ring_i / nst) & 1);
         tc_fence_after();
+        if (stamps) stamps[kb0 == 0 ? 11 : 12] = clock64();
         const int n = min(ckb, nkb - kb0);
-        for (int j = 0; j < n; ++j) {
-            const int kb = kb0 + j;
-            const uint32_t sa = smem_u32(s.ring + (st * ckb + j) * tile);
-            const uint32_t sb = w0 + (uint32_t)kb * (uint32_t)nc * 128u;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                if (swap) mma_bf16(tmem, desc_kmajor(sb + k * 32), desc_kmajor(sa + k * 32), idesc, (kb | k) != 0);
-                else      mma_bf16(tmem, desc_kmajor(sa + k * 32), desc_kmajor(sb + k * 32), idesc, (kb | k) != 0);
+        // Descriptors are built once per stage and advanced by plain adds: the issuing thread is a
+        // single scalar instruction stream, and every instruction between two tcgen05.mma costs
+        // tensor-pipe idle time (K step of 16 bf16 = 32 B = +2 in the descriptor's address field).
+        uint64_t da = desc_kmajor(smem_u32(s.ring + st * ckb * tile));
+        uint64_t db = desc_kmajor(w0 + (uint32_t)kb0 * (uint32_t)nc * 128u);
+        const uint64_t da_step = (uint64_t)(tile >> 4), db_step = (uint64_t)((nc * 128) >> 4);
+        if (!swap) {
+            for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+                mma_bf16(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
+                mma_bf16(tmem, da + 2, db + 2, idesc, 1u);
+                mma_bf16(tmem, da + 4, db + 4, idesc, 1u);
+                mma_bf16(tmem, da + 6, db + 6, idesc, 1u);
+            }
+        } else {
+            for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+                mma_bf16(tmem, db, da, idesc, (uint32_t)((kb0 + j) != 0));
+                mma_bf16(tmem, db + 2, da + 2, idesc, 1u);
+                mma_bf16(tmem, db + 4, da + 4, idesc, 1u);
+                mma_bf16(tmem, db + 6, da + 6, idesc, 1u);
             }
         }
         mma_commit(&s.a_empty[st]);
@@ -319,7 +338,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     if (phases_done > 0) rt_await(a.barrier + tile, phases_done * a.nslices);
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d);
                     RT_STAMP(2);
                     ++phases_done;
                 }
@@ -332,7 +351,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = t * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
+                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst,
+                               (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
                     RT_STAMP(3);
                 }
         }
@@ -487,13 +507,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (t + 1 < a.S) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d);
                     ++phases_done;
                 }
             }

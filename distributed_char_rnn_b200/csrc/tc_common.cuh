@@ -53,6 +53,13 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
         ::"r"(smem_u32(smem_dst)), "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
 
+// 3-D tile load (inner, middle, outer coordinates).
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
 // ---- TMEM --------------------------------------------------------------------------------
 // One full warp allocates `ncols` (power of two >= 32) columns; the base address lands in *slot.
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {
@@ -145,6 +152,27 @@ inline int make_tmap_bf16(CUtensorMap* out, const void* base, int64_t rows, int6
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return CRNN_OK;
+}
+
+// The same row-major bf16 matrix seen as [kblock][row][64]: dims (64 k, rows, cols/64 k-blocks) with
+// strides (row pitch, 128 B).  One box {64, box_rows, box_kb} lands in shared memory as box_kb
+// consecutive K-major swizzled tiles of box_rows x 128 B - several K tiles per TMA instruction.
+// Requires cols % 64 == 0 (a partial last k-block would alias the next row instead of reading zero).
+inline int make_tmap_bf16_kblocks(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t ld,
+                                  int box_rows, int box_kb) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    if (cols % 64 != 0 || (ld * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0)
+        return set_err(CRNN_ERR_ARG, "k-block tensor map needs cols %% 64 == 0 and 16-byte aligned rows");
+    cuuint64_t gdim[3] = {64u, (cuuint64_t)rows, (cuuint64_t)(cols / 64)};
+    cuuint64_t gstr[2] = {(cuuint64_t)ld * 2, 128u};
+    cuuint32_t box[3] = {64u, (cuuint32_t)box_rows, (cuuint32_t)box_kb};
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed (%d)", (int)r);
     return CRNN_OK;
 }
 

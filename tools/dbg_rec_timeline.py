@@ -11,7 +11,7 @@ torch.cuda.synchronize()
 d=m.workspace[24576:24576+8*16*60].view(torch.int64).cpu().numpy().reshape(60,16)
 # phases 20..39
 base=d[20,0]
-names=['prod_start','await_done','tma_issued','mma_done','epi_loaded','acc_taken','epi_synced','published','w0_computed','w3_computed']
+names=['prod_start','await_done','tma_issued','mma_done','epi_loaded','acc_taken','epi_synced','published','w0_computed','w3_computed','mma_zempty','mma_full0','mma_full1']
 print(names)
 for p in range(20,32):
-    print(p, [int(v-d[p,0]) for v in d[p][:10]], 'phase_len', int(d[p+1,0]-d[p,0]))
+    print(p, [int(v-d[p,0]) for v in d[p][:13]], 'phase_len', int(d[p+1,0]-d[p,0]))
