@@ -341,6 +341,11 @@ def main():
         _lib.check(lib.crnn_profile_enable(model._h, 0))
         phases = {lib.crnn_profile_phase_name(i).decode(): arr[i] / nprof for i in range(_lib.NUM_PHASES)}
         fl, by = phase_flops(c), phase_bytes(c, model.P)
+        if phases.get("xproj_gemm", 0.0) < 1e-6 and c["num_layers"] > 1:
+            # layer wavefront: the recurrence phases are fork..join spans that contain the interleaved
+            # x-projection / input- and weight-gradient GEMMs, so they carry those FLOPs too
+            fl["rec_fwd"] += fl["xproj_gemm"]
+            fl["rec_bwd"] += fl["input_grads"] + fl["weight_grads"]
         dom = max((p for p in phases if p != "misc"), key=lambda p: phases[p])
         dms = phases[dom]
         if dom in fl:

@@ -45,8 +45,9 @@ struct WsPlan {
     std::vector<size_t> hx, cx, gates;
     size_t dz, dya, dyb, carry0, carry1, logits;
     // CRNN_PREC_BF16 only: bf16 MMA operands
-    size_t pbf, wsmb, x0b, dzb, dlb;
+    size_t pbf, wsmb, x0b, dlb, gx0;
     std::vector<size_t> wr, hxb, rsb;
+    std::vector<size_t> dzv, dzbv, gout, carry0v, carry1v;   // per layer: layers run concurrently (wavefront)
     size_t total;
 };
 
@@ -70,6 +71,10 @@ struct crnn_handle {
     int64_t emb_off;
     RecPlan fwd, bwd;
     RecPlanTc tcp;
+    // wavefront over layers (tensor path): wf_W layer streams, each sequence cut into wf_C chunks
+    int wf_W, wf_C;
+    std::vector<cudaStream_t> wf_streams;
+    std::vector<cudaEvent_t> wf_events;
     long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
     int fast_act;
@@ -109,9 +114,9 @@ static const float kBeta1 = 0.9f, kBeta2 = 0.999f, kEps = 1e-8f;
 
 // scratch layout (bytes): [0,256) barrier words; [256,512) doubles {loss_sum, sq_sum};
 // [1024, 1024 + 8*NORM_BLOCKS) norm partials.
-static const size_t kScratchBytes = 32768;
+static const size_t kScratchBytes = 32768 + 512 * 256;   // 512 barrier blocks after the first 32 KB
 // one 256-byte block of barrier counters per recurrence launch (2 per layer), after the first 8 KB
-static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>((char*)ws + 8192 + (size_t)i * 256); }
+static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>((char*)ws + 32768 + (size_t)i * 256); }
 static inline double* ws_loss(void* ws) { return reinterpret_cast<double*>((char*)ws + 256); }
 static inline double* ws_sq(void* ws) { return reinterpret_cast<double*>((char*)ws + 264); }
 static inline double* ws_partials(void* ws) { return reinterpret_cast<double*>((char*)ws + 1024); }
@@ -170,11 +175,10 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
 // Decomposition of the tensor-core recurrence kernels: HC hidden units (multiple of 16) per slice,
 // BT batch rows per tile.  The resident weight slice (2*GW*H*HC bytes) plus the 64 KB A ring must
 // fit in shared memory; one CTA per SM, all co-resident.
-static int plan_recurrence_tc(const crnn_handle* h, RecPlanTc* out) {
+static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out) {
     const int H = h->cfg.rnn_size, B = h->cfg.batch_size, model = h->cfg.model;
     if (H % 16 != 0) return set_err(CRNN_ERR_UNSUP, "CRNN_PREC_BF16 needs rnn_size %% 16 == 0 (got %d)", H);
     const int g1 = model == CRNN_MODEL_LSTM ? 4 : (model == CRNN_MODEL_GRU ? 2 : 1);
-    const int max_ctas = h->sm_count;
     const int nkb = ceil_div(H, 64);
     const int hc_env = env_int("CRNN_TC_HC", 0), nt_env = env_int("CRNN_TC_TILES", 0);
     auto fill = [&](int HC, RecPlanTc* o) -> bool {
@@ -261,11 +265,12 @@ static void build_workspace(crnn_handle* h) {
         w.cx.push_back(h->cfg.model == CRNN_MODEL_LSTM ? take((S + 1) * B * H) : 0);
         w.gates.push_back(take(S * B * h->GS * H));
     }
-    w.dz = take((S + 1) * B * h->GZ * H);
-    w.dya = take(S * B * H);
-    w.dyb = take(S * B * H);
-    w.carry0 = take(B * H);
-    w.carry1 = take(B * H);
+    const bool fp32_path = h->cfg.precision == CRNN_PREC_FP32;
+    w.dz = fp32_path ? take((S + 1) * B * h->GZ * H) : 0;
+    w.dya = fp32_path ? take(S * B * H) : 0;
+    w.dyb = fp32_path ? take(S * B * H) : 0;
+    w.carry0 = fp32_path ? take(B * H) : 0;
+    w.carry1 = fp32_path ? take(B * H) : 0;
     w.logits = take(S * B * V);
     if (h->cfg.precision == CRNN_PREC_BF16) {
         auto take2 = [&](int64_t halves) { return take((halves + 1) / 2); };
@@ -278,7 +283,14 @@ static void build_workspace(crnn_handle* h) {
             w.hxb.push_back(take2((S + 1) * B * H));
             w.rsb.push_back(h->cfg.model == CRNN_MODEL_GRU ? take2(S * B * H) : 0);
         }
-        w.dzb = take2((S + 1) * B * h->GZ * H);
+        for (int l = 0; l < L; ++l) {
+            w.dzv.push_back(take(S * B * h->GZ * H));
+            w.dzbv.push_back(take2((S + 1) * B * h->GZ * H));
+            w.gout.push_back(take(S * B * H));
+            w.carry0v.push_back(take(B * H));
+            w.carry1v.push_back(take(B * H));
+        }
+        w.gx0 = take(S * B * H);
         w.dlb = take2(S * B * h->Vp);
     }
     w.total = off;
@@ -309,6 +321,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     CRNN_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
     if (prop.major != 10)
         return set_err(CRNN_ERR_UNSUP, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
+    CRNN_CUDA(cudaSetDevice(cfg->device));
     crnn_handle* h = new crnn_handle();
     h->cfg = *cfg;
     h->G = cfg->model == CRNN_MODEL_LSTM ? 4 : (cfg->model == CRNN_MODEL_GRU ? 3 : 1);
@@ -325,8 +338,36 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     if (rc == CRNN_OK) rc = plan_recurrence(h, true, &h->bwd);
     h->Vp = (cfg->vocab_size + 7) & ~7;
     h->fast_act = env_int("CRNN_FAST_ACT", 1);
-    if (rc == CRNN_OK && cfg->precision == CRNN_PREC_BF16) rc = plan_recurrence_tc(h, &h->tcp);
-    if (rc != CRNN_OK) { delete h; return rc; }
+    h->wf_W = 1; h->wf_C = 1;
+    if (rc == CRNN_OK && cfg->precision == CRNN_PREC_BF16) {
+        // Layers are independent chains once their inputs exist: run up to W of them at once, each on
+        // 1/W of the SMs, the sequence cut into C chunks so layer l+1 starts when layer l has produced
+        // the first chunk.  W = 1 is the plain sequential schedule.
+        // Measured on B200: overlapping two layers pays while a layer's recurrence is latency-bound
+        // (config 1: 1.09 -> 0.85 ms/step, config 3: 6.03 -> 5.18 ms) and costs when it is bound by the
+        // L2 all-gather of h (config 4: 19.3 -> 21.5 ms), so it is on for recurrent weights <= 4 MB/layer.
+        const int64_t wbytes = 2LL * h->G * cfg->rnn_size * cfg->rnn_size;
+        int W = std::min(cfg->num_layers, env_int("CRNN_WAVEFRONT", wbytes <= (4LL << 20) ? 2 : 1));
+        if (W < 1) W = 1;
+        for (; W >= 1; --W) {
+            rc = plan_recurrence_tc(h, h->sm_count / W, &h->tcp);
+            if (rc == CRNN_OK) break;
+        }
+        if (rc == CRNN_OK) {
+            h->wf_W = W;
+            int C = W > 1 ? std::max(1, std::min(8, cfg->seq_length / 16)) : 1;
+            const int c_env = env_int("CRNN_WAVEFRONT_CHUNKS", 0);
+            if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 8);
+            if (W == 1) C = 1;
+            h->wf_C = C;
+            for (int i = 0; i < W && W > 1; ++i) {
+                cudaStream_t s;
+                if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { rc = set_err(CRNN_ERR_CUDA, "cudaStreamCreate failed"); break; }
+                h->wf_streams.push_back(s);
+            }
+        }
+    }
+    if (rc != CRNN_OK) { for (cudaStream_t s_ : h->wf_streams) cudaStreamDestroy(s_); delete h; return rc; }
     build_workspace(h);
     *out = h;
     return CRNN_OK;
@@ -335,6 +376,8 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
 void crnn_destroy(crnn_handle* h) {
     if (!h) return;
     for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->wf_events) if (e) cudaEventDestroy(e);
+    for (cudaStream_t s : h->wf_streams) cudaStreamDestroy(s);
     delete h;
 }
 
@@ -441,7 +484,7 @@ static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const floa
     embed_gather_kernel<<<grid_for(SB * H / 4 + 1, h->sm_count), 256, 0, st>>>(emb, V, H, x, ldx, B, S, x0, nullptr);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     prof_mark(h, st, CRNN_PHASE_MISC);
-    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 64 * 256, st));
+    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 512 * 256, st));
     for (int l = 0; l < L; ++l) {
         LayerParams lp = layer_params(h, params, l);
         float* hx = wsf(ws, h->ws.hx[l]);
@@ -578,15 +621,53 @@ static int refresh_bf16_params(crnn_handle* h, const float* params, void* ws, cu
     return CRNN_OK;
 }
 
+// ---- wavefront helpers ---------------------------------------------------------------------
+// Stream of layer l: the caller's stream when layers run one after another, else one of the W
+// internal streams.  Events are created on first use and reused by every later step.
+static cudaStream_t wf_stream(crnn_handle* h, cudaStream_t st, int l) {
+    return h->wf_W > 1 ? h->wf_streams[l % h->wf_W] : st;
+}
+static int wf_event(crnn_handle* h, int idx, cudaEvent_t* out) {
+    if ((int)h->wf_events.size() <= idx) h->wf_events.resize(idx + 1, nullptr);
+    if (!h->wf_events[idx]) CRNN_CUDA(cudaEventCreateWithFlags(&h->wf_events[idx], cudaEventDisableTiming));
+    *out = h->wf_events[idx];
+    return CRNN_OK;
+}
+// event ids: forward (l,c) -> l*C+c ; backward (l,c) -> L*C + l*C+c ; fork/join after those
+static int wf_fork(crnn_handle* h, cudaStream_t st, int slot) {
+    if (h->wf_W <= 1) return CRNN_OK;
+    cudaEvent_t e;
+    int rc = wf_event(h, 2 * h->cfg.num_layers * h->wf_C + slot, &e);
+    if (rc != CRNN_OK) return rc;
+    CRNN_CUDA(cudaEventRecord(e, st));
+    for (cudaStream_t s : h->wf_streams) CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
+    return CRNN_OK;
+}
+static int wf_join(crnn_handle* h, cudaStream_t st, int slot) {
+    if (h->wf_W <= 1) return CRNN_OK;
+    for (int i = 0; i < h->wf_W; ++i) {
+        cudaEvent_t e;
+        int rc = wf_event(h, 2 * h->cfg.num_layers * h->wf_C + slot + i, &e);
+        if (rc != CRNN_OK) return rc;
+        CRNN_CUDA(cudaEventRecord(e, h->wf_streams[i]));
+        CRNN_CUDA(cudaStreamWaitEvent(st, e, 0));
+    }
+    return CRNN_OK;
+}
+static inline int wf_t0(const crnn_handle* h, int c) { return (int)((int64_t)h->cfg.seq_length * c / h->wf_C); }
+
 static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
                             const float* params, void* ws, cudaStream_t st) {
     const crnn_config& c = h->cfg;
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
-    const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
+    const int64_t BH = (int64_t)B * H;
+    const int64_t SB = (int64_t)S * B;
     const int gw = h->GS * H;
     const int sc = h->sm_count;
+    const int C = h->wf_C;
+    const bool wf = h->wf_W > 1;
     prof_mark(h, st, CRNN_PHASE_MISC);
-    h->dbg_ptr = reinterpret_cast<long long*>((char*)ws + 24576);      // 8 KB after the barrier blocks
+    h->dbg_ptr = reinterpret_cast<long long*>((char*)ws + 24576);      // 8 KB before the barrier blocks
     int rc = refresh_bf16_params(h, params, ws, st);
     if (rc != CRNN_OK) return rc;
     const bf16_t* pbf = wsb(ws, h->ws.pbf);
@@ -596,8 +677,14 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     embed_gather_kernel<<<grid_for(SB * H / 4 + 1, sc), 256, 0, st>>>(params + h->emb_off, V, H, x, ldx, B, S, x0, x0b);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     prof_mark(h, st, CRNN_PHASE_MISC);
-    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 64 * 256, st));
+    CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 512 * 256, st));
+    // In wavefront mode the "rec_fwd" phase is the whole fork..join span: the recurrences of all layers
+    // plus their chunked x-projections, which run interleaved with them.
+    if (wf) prof_mark(h, st, CRNN_PHASE_REC_FWD);
+    rc = wf_fork(h, st, 0);
+    if (rc != CRNN_OK) return rc;
     for (int l = 0; l < L; ++l) {
+        cudaStream_t s = wf_stream(h, st, l);
         LayerParams lp = layer_params(h, params, l);
         float* hx = wsf(ws, h->ws.hx[l]);
         float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
@@ -606,37 +693,57 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         const bf16_t* inb = l == 0 ? x0b : wsb(ws, h->ws.hxb[l - 1]) + BH;
         const float* sin = state_in + (int64_t)l * h->nstate * BH;
         const float* hin = c.model == CRNN_MODEL_LSTM ? sin + BH : sin;
-        if (c.model == CRNN_MODEL_LSTM) CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, st));
-        CRNN_CUDA(cudaMemcpyAsync(hx, hin, BH * 4, cudaMemcpyDeviceToDevice, st));
-        tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, st>>>(hin, H, B, H, hxb, H);
+        if (c.model == CRNN_MODEL_LSTM) CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, s));
+        CRNN_CUDA(cudaMemcpyAsync(hx, hin, BH * 4, cudaMemcpyDeviceToDevice, s));
+        tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, s>>>(hin, H, B, H, hxb, H);
         CRNN_LAUNCH_CHECK("cast_bf16_kernel");
-        prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
-        // x half of [x,h]*W for all S steps: A = inputs (K-major), B = kernel rows 0..H stored [K,N]
-        if (c.model == CRNN_MODEL_GRU) {
-            rc = tc::gemm_bf16_tc((int)SB, 2 * H, H, inb, H, 0, pbf + lp.oW, 2 * H, 1, gates, gw, lp.b, 0, st, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, H, inb, H, 0, pbf + lp.oWc, H, 1, gates + 2 * H, gw, lp.bc, 0, st, sc);
-        } else {
-            const int GH = h->G * H;
-            rc = tc::gemm_bf16_tc((int)SB, GH, H, inb, H, 0, pbf + lp.oW, GH, 1, gates, gw, lp.b, 0, st, sc);
+        for (int ck = 0; ck < C; ++ck) {
+            const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
+            const int rows = (t1 - t0) * B;
+            if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
+                cudaEvent_t e;
+                rc = wf_event(h, (l - 1) * C + ck, &e);
+                if (rc != CRNN_OK) return rc;
+                CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
+            }
+            if (!wf) prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
+            // x half of [x,h]*W for the chunk's steps: A = inputs (K-major), B = kernel rows 0..H stored [K,N]
+            const bf16_t* ain = inb + (int64_t)t0 * BH;
+            float* gch = gates + (int64_t)t0 * B * gw;
+            if (c.model == CRNN_MODEL_GRU) {
+                rc = tc::gemm_bf16_tc(rows, 2 * H, H, ain, H, 0, pbf + lp.oW, 2 * H, 1, gch, gw, lp.b, 0, s, sc);
+                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, ain, H, 0, pbf + lp.oWc, H, 1, gch + 2 * H, gw, lp.bc, 0, s, sc);
+            } else {
+                const int GH = h->G * H;
+                rc = tc::gemm_bf16_tc(rows, GH, H, ain, H, 0, pbf + lp.oW, GH, 1, gch, gw, lp.b, 0, s, sc);
+            }
+            if (rc != CRNN_OK) return rc;
+            tc::RecTcArgs a{};
+            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
+            a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
+            a.rsb = c.model == CRNN_MODEL_GRU ? wsb(ws, h->ws.rsb[l]) : nullptr;
+            a.barrier = ws_barrier(ws, l * C + ck);
+            if (!wf) prof_mark(h, st, CRNN_PHASE_REC_FWD);
+            rc = launch_rec_tc_model(h, false, a, nullptr, nullptr, wsb(ws, h->ws.wr[l]), s);
+            if (rc != CRNN_OK) return rc;
+            if (!wf) prof_mark(h, st, CRNN_PHASE_MISC);
+            if (wf) {
+                cudaEvent_t e;
+                rc = wf_event(h, l * C + ck, &e);
+                if (rc != CRNN_OK) return rc;
+                CRNN_CUDA(cudaEventRecord(e, s));
+            }
         }
-        if (rc != CRNN_OK) return rc;
-        tc::RecTcArgs a{};
-        a.B = B; a.H = H; a.S = S; a.GS = h->GS;
-        a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
-        a.rsb = c.model == CRNN_MODEL_GRU ? wsb(ws, h->ws.rsb[l]) : nullptr;
-        a.barrier = ws_barrier(ws, 2 * l);
-        prof_mark(h, st, CRNN_PHASE_REC_FWD);
-        rc = launch_rec_tc_model(h, false, a, nullptr, nullptr, wsb(ws, h->ws.wr[l]), st);
-        if (rc != CRNN_OK) return rc;
-        prof_mark(h, st, CRNN_PHASE_MISC);
         float* sout = state_out + (int64_t)l * h->nstate * BH;
         if (c.model == CRNN_MODEL_LSTM) {
-            CRNN_CUDA(cudaMemcpyAsync(sout, cx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
-            CRNN_CUDA(cudaMemcpyAsync(sout + BH, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+            CRNN_CUDA(cudaMemcpyAsync(sout, cx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, s));
+            CRNN_CUDA(cudaMemcpyAsync(sout + BH, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, s));
         } else {
-            CRNN_CUDA(cudaMemcpyAsync(sout, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, st));
+            CRNN_CUDA(cudaMemcpyAsync(sout, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, s));
         }
     }
+    rc = wf_join(h, st, 1);
+    if (rc != CRNN_OK) return rc;
     const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
     prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
     rc = tc::gemm_bf16_tc((int)SB, V, H, topb, H, 0, wsb(ws, h->ws.wsmb), h->Vp, 1, wsf(ws, h->ws.logits), V,
@@ -652,6 +759,8 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H, zw = h->GZ * H, Vp = h->Vp;
     const int sc = h->sm_count;
+    const int C = h->wf_C;
+    const bool wf = h->wf_W > 1;
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
@@ -664,63 +773,92 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     softmax_xent_kernel<<<grid_for(SB * 32, sc), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp);
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
     const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
-    float* dya = wsf(ws, h->ws.dya);
-    float* dyb = wsf(ws, h->ws.dyb);
     prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
     // d softmax_w [H,V] = out^T * dlogits ; d softmax_b = colsum ; d out = dlogits * softmax_w^T
     rc = tc::gemm_bf16_tc(H, V, (int)SB, topb, H, 1, dlb, Vp, 1, grads + h->tensors[0].offset, V, nullptr, 1, st, sc);
     if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
-    if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, V, dlb, Vp, 0, wsb(ws, h->ws.wsmb), Vp, 0, dya, H, nullptr, 0, st, sc);
+    if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, V, dlb, Vp, 0, wsb(ws, h->ws.wsmb), Vp, 0, wsf(ws, h->ws.gout[L - 1]), H, nullptr, 0, st, sc);
     if (rc != CRNN_OK) return rc;
 
-    float* dz = wsf(ws, h->ws.dz);
-    bf16_t* dzb = wsb(ws, h->ws.dzb);
-    float* dcur = dya;
-    float* dnext = dyb;
+    // BPTT, top layer first.  Wavefront: layer l works on chunk c (late steps first) as soon as layer
+    // l+1 has turned that chunk's dz into input gradients; "rec_bwd" then times the whole fork..join
+    // span (recurrences + interleaved input-gradient GEMMs), weight gradients included at its tail.
+    if (wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
+    rc = wf_fork(h, st, 1 + h->wf_W);
+    if (rc != CRNN_OK) return rc;
     for (int l = L - 1; l >= 0; --l) {
+        cudaStream_t s = wf_stream(h, st, l);
         LayerParams lp = layer_params(h, params, l);
         float* hx = wsf(ws, h->ws.hx[l]);
         float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
         float* gates = wsf(ws, h->ws.gates[l]);
         const bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
         const bf16_t* inb = l == 0 ? wsb(ws, h->ws.x0b) : wsb(ws, h->ws.hxb[l - 1]) + BH;
-        tc::RecTcArgs a{};
-        a.B = B; a.H = H; a.S = S; a.GS = h->GS;
-        a.gates = gates; a.hx = hx; a.cx = cx;
-        a.dy = dcur; a.dz = dz; a.dzb = dzb; a.carry0 = wsf(ws, h->ws.carry0); a.carry1 = wsf(ws, h->ws.carry1);
-        a.barrier = ws_barrier(ws, 2 * l + 1);
-        prof_mark(h, st, CRNN_PHASE_REC_BWD);
-        rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, st);
-        if (rc != CRNN_OK) return rc;
-        prof_mark(h, st, CRNN_PHASE_WEIGHT_GRADS);
+        float* dz = wsf(ws, h->ws.dzv[l]);
+        bf16_t* dzb = wsb(ws, h->ws.dzbv[l]);
+        float* dnext = l > 0 ? wsf(ws, h->ws.gout[l - 1]) : wsf(ws, h->ws.gx0);
+        for (int ck = C - 1; ck >= 0; --ck) {
+            const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
+            const int rows = (t1 - t0) * B;
+            if (wf && l < L - 1) {                   // layer l+1 has produced this chunk's output gradients
+                cudaEvent_t e;
+                rc = wf_event(h, L * C + (l + 1) * C + ck, &e);
+                if (rc != CRNN_OK) return rc;
+                CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
+            }
+            tc::RecTcArgs a{};
+            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
+            a.gates = gates; a.hx = hx; a.cx = cx;
+            a.dy = wsf(ws, h->ws.gout[l]); a.dz = dz; a.dzb = dzb;
+            a.carry0 = wsf(ws, h->ws.carry0v[l]); a.carry1 = wsf(ws, h->ws.carry1v[l]);
+            a.barrier = ws_barrier(ws, L * C + l * C + ck);
+            if (!wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
+            rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, s);
+            if (rc != CRNN_OK) return rc;
+            // input gradients of the chunk: dIn = dz * Wx^T (A = dz K-major, B = kernel rows 0..H as [N,K])
+            if (!wf) prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
+            const bf16_t* dzc = dzb + (int64_t)t0 * B * zw;
+            float* dn = dnext + (int64_t)t0 * BH;
+            if (c.model == CRNN_MODEL_GRU) {
+                rc = tc::gemm_bf16_tc(rows, H, 2 * H, dzc, zw, 0, pbf + lp.oW, 2 * H, 0, dn, H, nullptr, 0, s, sc);
+                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, dzc + 2 * H, zw, 0, pbf + lp.oWc, H, 0, dn, H, nullptr, 1, s, sc);
+            } else {
+                const int GH = h->G * H;
+                rc = tc::gemm_bf16_tc(rows, H, GH, dzc, zw, 0, pbf + lp.oW, GH, 0, dn, H, nullptr, 0, s, sc);
+            }
+            if (rc != CRNN_OK) return rc;
+            if (wf) {
+                cudaEvent_t e;
+                rc = wf_event(h, L * C + l * C + ck, &e);
+                if (rc != CRNN_OK) return rc;
+                CRNN_CUDA(cudaEventRecord(e, s));
+            }
+        }
+        if (!wf) prof_mark(h, st, CRNN_PHASE_WEIGHT_GRADS);
         float* gW = grads + lp.oW;
         float* gb = grads + lp.ob;
         if (c.model == CRNN_MODEL_GRU) {
             float* gWc = grads + lp.oWc;
             float* gbc = grads + lp.obc;
             const bf16_t* rsb = wsb(ws, h->ws.rsb[l]);
-            rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, inb, H, 1, dzb, zw, 1, gW, 2 * H, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, st);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, inb, H, 1, dzb + 2 * H, zw, 1, gWc, H, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, rsb, H, 1, dzb + 2 * H, zw, 1, gWc + (int64_t)H * H, H, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, st);
-            prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, 2 * H, dzb, zw, 0, pbf + lp.oW, 2 * H, 0, dnext, H, nullptr, 0, st, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, H, dzb + 2 * H, zw, 0, pbf + lp.oWc, H, 0, dnext, H, nullptr, 1, st, sc);
+            rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, inb, H, 1, dzb, zw, 1, gW, 2 * H, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, s);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, inb, H, 1, dzb + 2 * H, zw, 1, gWc, H, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, rsb, H, 1, dzb + 2 * H, zw, 1, gWc + (int64_t)H * H, H, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, s);
         } else {
             const int GH = h->G * H;
-            rc = tc::gemm_bf16_tc(H, GH, (int)SB, inb, H, 1, dzb, zw, 1, gW, GH, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, GH, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * GH, GH, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, st);
-            prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, GH, dzb, zw, 0, pbf + lp.oW, GH, 0, dnext, H, nullptr, 0, st, sc);
+            rc = tc::gemm_bf16_tc(H, GH, (int)SB, inb, H, 1, dzb, zw, 1, gW, GH, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, GH, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * GH, GH, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, s);
         }
         if (rc != CRNN_OK) return rc;
-        std::swap(dcur, dnext);
     }
+    rc = wf_join(h, st, 1 + 2 * h->wf_W);
+    if (rc != CRNN_OK) return rc;
     prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
-    embed_scatter_kernel<<<grid_for(SB * H, sc), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, dcur, ws_sq(ws));
+    embed_scatter_kernel<<<grid_for(SB * H, sc), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, wsf(ws, h->ws.gx0), ws_sq(ws));
     CRNN_LAUNCH_CHECK("embed_scatter_kernel");
     finalize_scalars_kernel<<<1, 32, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P);
     CRNN_LAUNCH_CHECK("finalize_scalars_kernel");

@@ -47,6 +47,7 @@ __host__ __device__ inline int rt_num_stages(int box_rows, int chunk_kb) {
 
 struct RecTcArgs {
     int B, H, S;
+    int t_begin, t_end;         // steps this launch covers (absolute; chunks of one sequence run as separate launches)
     int HC, BT, nslices, ntiles, npass;
     int GS;                     // gate-stash row width / H
     int box_rows;               // rows per A-tile TMA box
@@ -331,7 +332,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 if (MODEL == CRNN_MODEL_GRU)
                     tma_load_2d(s.wsb + (size_t)kb * HC * 128, &tmW1, s.w_bar, kb * 64, slice * GW * HC + NCA);
             }
-            for (int t = 0; t < a.S; ++t) {
+            for (int t = a.t_begin; t < a.t_end; ++t) {
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (int)phases_done;
                     RT_STAMP(0);
@@ -347,9 +348,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     } else if (warp == 1) {
         if (lane == 0) {
             mbar_wait(s.w_bar, 0);
-            for (int t = 0; t < a.S; ++t)
+            for (int t = a.t_begin; t < a.t_end; ++t)
                 for (int ph = 0; ph < nphase; ++ph) {
-                    const int dbg_phase = t * nphase + ph;
+                    const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst,
                                (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
@@ -360,7 +361,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         const int ehalf = (warp - 2) >> 2;            // which of the quarter's warps this is
         const int epi_tid = (warp - 2) * 32 + lane;
-        for (int t = 0; t < a.S; ++t) {
+        for (int t = a.t_begin; t < a.t_end; ++t) {
             const int64_t tB = (int64_t)t * B;
             float* gt = a.gates;
             const float* hprev = a.hx + (int64_t)t * BH;
@@ -394,7 +395,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                 }
                             }
                         }
-                        const int dbg_phase = t * nphase + ph;
+                        const int dbg_phase = (t - a.t_begin) * nphase + ph;
                         if (epi_tid == 0) RT_STAMP(4);
                         if (base == 0) RT_TAKE_ACC(nr, ph == 0 ? NCA : HC);
                         if (epi_tid == 0) RT_STAMP(5);
@@ -433,10 +434,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                             }
                         }
                     }
-                    { const int dbg_phase = t * nphase + ph; if (epi_tid == 0) RT_STAMP(8); if (epi_tid == RT_EPI_THREADS - 1) RT_STAMP(9); }
+                    { const int dbg_phase = (t - a.t_begin) * nphase + ph; if (epi_tid == 0) RT_STAMP(8); if (epi_tid == RT_EPI_THREADS - 1) RT_STAMP(9); }
                     epi_bar_sync();          // Zs is reused by the next pass / phase
                 }
-                const int dbg_phase = t * nphase + ph;
+                const int dbg_phase = (t - a.t_begin) * nphase + ph;
                 if (epi_tid == 0) RT_STAMP(6);
                 rt_publish(a.barrier + tile, epi_tid);
                 if (epi_tid == 0) RT_STAMP(7);
@@ -502,8 +503,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             for (int kb = 0; kb < nkb0; ++kb) tma_load_2d(s.wsa + (size_t)kb * HC * 128, &tmW0, s.w_bar, kb * 64, H + j0);
             if (MODEL == CRNN_MODEL_GRU)
                 for (int kb = 0; kb < nkb1; ++kb) tma_load_2d(s.wsb + (size_t)kb * HC * 128, &tmW1, s.w_bar, kb * 64, H + j0);
-            for (int t = a.S - 1; t >= 0; --t) {
-                // contraction 0 reads dz_{t+1} (all CTAs, previous step)
+            for (int t = a.t_end - 1; t >= a.t_begin; --t) {
+                // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
                 if (t + 1 < a.S) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
@@ -521,7 +522,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     } else if (warp == 1) {
         if (lane == 0) {
             mbar_wait(s.w_bar, 0);
-            for (int t = a.S - 1; t >= 0; --t) {
+            for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
                     for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
                 if (MODEL == CRNN_MODEL_GRU)
@@ -532,14 +533,14 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         const int ehalf = (warp - 2) >> 2;            // which of the quarter's warps this is
         const int epi_tid = (warp - 2) * 32 + lane;
-        // zero the CTA-private carries
-        if (MODEL != CRNN_MODEL_RNN) {
+        // zero the CTA-private carries (they persist in global memory across the launches of one sequence)
+        if (MODEL != CRNN_MODEL_RNN && a.t_end == a.S) {
             for (int idx = epi_tid; idx < bt * hcv; idx += RT_EPI_THREADS) {
                 const int r = idx / hcv, jj = idx - r * hcv;
                 a.carry0[(int64_t)(b0 + r) * H + j0 + jj] = 0.f;
             }
         }
-        for (int t = a.S - 1; t >= 0; --t) {
+        for (int t = a.t_end - 1; t >= a.t_begin; --t) {
             const bool has_next = t + 1 < a.S;
             const int64_t tB = (int64_t)t * B;
             for (int ps = 0; ps < a.npass; ++ps) {

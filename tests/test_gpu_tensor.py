@@ -111,6 +111,12 @@ BF16_SHAPES = [
     ("lstm", 32, 2, 6, 20, 11, {"CRNN_TC_SWAP": 1}), ("gru", 64, 2, 5, 40, 17, {"CRNN_TC_SWAP": 1}),
     ("rnn", 128, 1, 5, 24, 17, {"CRNN_TC_SWAP": 1}), ("gru", 64, 2, 5, 40, 17, {"CRNN_TC_SWAP": 0}),
     ("lstm", 32, 1, 4, 150, 9, {"CRNN_TC_SWAP": 1, "CRNN_TC_TILES": 1}),
+    # layer wavefront: layers on concurrent streams, the sequence cut into chunks (uneven ones too)
+    ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3}),
+    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4}),
+    ("rnn", 48, 3, 6, 12, 13, {"CRNN_WAVEFRONT": 3, "CRNN_WAVEFRONT_CHUNKS": 2}),
+    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 1}),
+    ("lstm", 64, 2, 5, 8, 9, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 5}),
 ]
 
 
