@@ -332,10 +332,13 @@ def main():
     arr = (ctypes.c_double * _lib.NUM_PHASES)()
     if rank == 0:
         _lib.check(lib.crnn_profile_enable(model._h, 1))
+    kms = (ctypes.c_double * 2)()
+    kln = (ctypes.c_int64 * 2)()
     for k in range(nprof):                                    # every rank steps (the all-reduce is collective)
         model.step_async(*dev_batch(W + k))
         if rank == 0:
             _lib.check(lib.crnn_profile_read(model._h, arr, 0))
+            _lib.check(lib.crnn_profile_read_kernels(model._h, kms, kln, 0))
     barrier()
     if rank == 0:
         _lib.check(lib.crnn_profile_enable(model._h, 0))
@@ -348,7 +351,20 @@ def main():
             fl["rec_bwd"] += fl["input_grads"] + fl["weight_grads"]
         dom = max((p for p in phases if p != "misc"), key=lambda p: phases[p])
         dms = phases[dom]
-        if dom in fl:
+        if dom in ("rec_fwd", "rec_bwd") and kln[1 if dom == "rec_bwd" else 0] > 0:
+            # the persistent recurrence kernel itself: algorithmic FLOPs of all its launches in one step
+            # over the summed durations of those launches (events on each launch's own stream)
+            i = 1 if dom == "rec_bwd" else 0
+            per_step_ms = kms[i] / nprof
+            kflops = phase_flops(c)[dom]
+            ach = kflops / (per_step_ms * 1e-3) / 1e12
+            roofline = {"bound": "tensor", "kernel": "rec_%s_tc_kernel" % ("bwd" if i else "fwd"), "achieved": ach,
+                        "peak": pk["tf_sus"], "unit": "TFLOP/s", "frac": ach / pk["tf_sus"], "traffic": None,
+                        "peak_source": pk["src"] + " bf16 sustained", "launches_per_step": kln[i] / nprof,
+                        "ms": kms[i] / max(1, kln[i]), "ms_per_step_summed": per_step_ms,
+                        "algorithmic_flops_per_launch": kflops / (kln[i] / nprof),
+                        "phase_span_ms": dms}
+        elif dom in fl:
             ach = fl[dom] / (dms * 1e-3) / 1e12
             roofline = {"bound": "tensor", "kernel": dom, "achieved": ach, "peak": pk["tf_sus"], "unit": "TFLOP/s",
                         "frac": ach / pk["tf_sus"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
@@ -359,7 +375,7 @@ def main():
                         "frac": ach / pk["hbm"], "traffic": None, "peak_source": pk["src"], "ms": dms,
                         "algorithmic_bytes": by[dom]}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
+        if os.path.exists(tpath):      # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu capture
             roofline["traffic"] = json.load(open(tpath)).get(args.config, {}).get(dom)
         step_tf = value / world * train_flop_per_char(c) / 1e12
         roofline["step_tflops"] = step_tf

@@ -45,6 +45,7 @@ SIGNATURES = {
     "crnn_profile_enable": (c_i32, [c_vp, c_i32]),
     "crnn_profile_read": (c_i32, [c_vp, ctypes.POINTER(ctypes.c_double), c_i32]),
     "crnn_profile_phase_name": (ctypes.c_char_p, [c_i32]),
+    "crnn_profile_read_kernels": (c_i32, [c_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_i64), c_i32]),
     "crnn_embedding_gather": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "crnn_embedding_scatter_add": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "crnn_softmax_xent": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp]),

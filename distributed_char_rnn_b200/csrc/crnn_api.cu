@@ -90,7 +90,27 @@ struct crnn_handle {
     std::vector<int> prof_id;
     int prof_n;
     double prof_ms[CRNN_NUM_PHASES];
+    // per-launch timing of the recurrence kernels (events on the stream each launch goes to)
+    std::vector<cudaEvent_t> kev;
+    std::vector<int> kev_id;
+    int kev_n;
+    double kern_ms[2];
+    long long kern_launches[2];
 };
+
+// Bracket one kernel launch with events on ITS stream (which: 0 = rec_fwd, 1 = rec_bwd).
+static void prof_kernel_mark(crnn_handle* h, cudaStream_t s, int which) {
+    if (!h->prof_on) return;
+    if (h->kev_n >= (int)h->kev.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        h->kev.push_back(e);
+        h->kev_id.push_back(-1);
+    }
+    cudaEventRecord(h->kev[h->kev_n], s);
+    h->kev_id[h->kev_n] = which;
+    ++h->kev_n;
+}
 
 static const char* kPhaseNames[CRNN_NUM_PHASES] = {
     "embed_gather", "xproj_gemm", "rec_fwd", "logits_gemm", "softmax_xent", "proj_grads",
@@ -331,7 +351,8 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->sm_count = prop.multiProcessorCount;
     h->max_smem = (int)prop.sharedMemPerBlockOptin;
     h->pow_step = 0; h->b1p = 1.0f; h->b2p = 1.0f;
-    h->prof_on = false; h->prof_n = 0;
+    h->prof_on = false; h->prof_n = 0; h->kev_n = 0;
+    h->kern_ms[0] = h->kern_ms[1] = 0.0; h->kern_launches[0] = h->kern_launches[1] = 0;
     for (int i = 0; i < CRNN_NUM_PHASES; ++i) h->prof_ms[i] = 0.0;
     build_layout(h);
     int rc = plan_recurrence(h, false, &h->fwd);
@@ -376,6 +397,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
 void crnn_destroy(crnn_handle* h) {
     if (!h) return;
     for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->kev) cudaEventDestroy(e);
     for (cudaEvent_t e : h->wf_events) if (e) cudaEventDestroy(e);
     for (cudaStream_t s : h->wf_streams) cudaStreamDestroy(s);
     delete h;
@@ -387,6 +409,21 @@ int crnn_profile_enable(crnn_handle* h, int32_t on) {
     if (!h) return set_err(CRNN_ERR_ARG, "null handle");
     h->prof_on = on != 0;
     h->prof_n = 0;
+    h->kev_n = 0;
+    return CRNN_OK;
+}
+int crnn_profile_read_kernels(crnn_handle* h, double* ms_out, int64_t* launches_out, int32_t reset) {
+    if (!h || !ms_out || !launches_out) return set_err(CRNN_ERR_ARG, "null argument");
+    for (int i = 0; i + 1 < h->kev_n; i += 2) {          // (begin, end) pairs
+        CRNN_CUDA(cudaEventSynchronize(h->kev[i + 1]));
+        float ms = 0.f;
+        CRNN_CUDA(cudaEventElapsedTime(&ms, h->kev[i], h->kev[i + 1]));
+        const int id = h->kev_id[i];
+        if (id == 0 || id == 1) { h->kern_ms[id] += ms; ++h->kern_launches[id]; }
+    }
+    h->kev_n = 0;
+    for (int i = 0; i < 2; ++i) { ms_out[i] = h->kern_ms[i]; launches_out[i] = h->kern_launches[i]; }
+    if (reset) { h->kern_ms[0] = h->kern_ms[1] = 0.0; h->kern_launches[0] = h->kern_launches[1] = 0; }
     return CRNN_OK;
 }
 const char* crnn_profile_phase_name(int32_t i) { return (i >= 0 && i < CRNN_NUM_PHASES) ? kPhaseNames[i] : ""; }
@@ -586,7 +623,9 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     void* args[] = {&t0, &t1, &w0, &w1, &a};
+    prof_kernel_mark(h, st, backward ? 1 : 0);
     CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(tc::RT_THREADS), args, smem, st));
+    prof_kernel_mark(h, st, backward ? 1 : 0);
     ++g_launches;
     return CRNN_OK;
 }

@@ -148,6 +148,10 @@ long long   crnn_launch_count(void);
 int         crnn_profile_enable(crnn_handle* h, int32_t on);
 int         crnn_profile_read(crnn_handle* h, double* ms_out, int32_t reset);
 const char* crnn_profile_phase_name(int32_t phase);
+/* While profiling is enabled every launch of the persistent recurrence kernels is bracketed by
+ * events on the stream it is launched on (layers may run on concurrent internal streams).
+ * ms_out[2] / launches_out[2]: summed kernel durations and launch counts, [0] forward, [1] BPTT. */
+int         crnn_profile_read_kernels(crnn_handle* h, double* ms_out, int64_t* launches_out, int32_t reset);
 
 /* ---- single operators (each is one slice of the graph; used by the parity tests) ---- */
 
