@@ -371,17 +371,19 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         int W = std::min(cfg->num_layers, env_int("CRNN_WAVEFRONT", wbytes <= (4LL << 20) ? 2 : 1));
         if (W < 1) W = 1;
         for (; W >= 1; --W) {
-            rc = plan_recurrence_tc(h, h->sm_count / W, &h->tcp);
+            // W > 1: leave a few SMs to the batch GEMMs that run beside the persistent recurrence kernels
+            const int reserve = W > 1 ? env_int("CRNN_WF_RESERVE", 20) : 0;     // measured best on config 3 (0: 4.96, 20: 4.81, 36: 5.47 ms)
+            rc = plan_recurrence_tc(h, (h->sm_count - reserve) / W, &h->tcp);
             if (rc == CRNN_OK) break;
         }
         if (rc == CRNN_OK) {
             h->wf_W = W;
-            int C = W > 1 ? std::max(1, std::min(8, cfg->seq_length / 16)) : 1;
+            int C = W > 1 ? std::max(1, std::min(16, cfg->seq_length / 10)) : 1;
             const int c_env = env_int("CRNN_WAVEFRONT_CHUNKS", 0);
-            if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 8);
+            if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 16);
             if (W == 1) C = 1;
             h->wf_C = C;
-            for (int i = 0; i < W && W > 1; ++i) {
+            for (int i = 0; i < 2 * W && W > 1; ++i) {      // [0,W): recurrence streams, [W,2W): GEMM streams
                 cudaStream_t s;
                 if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { rc = set_err(CRNN_ERR_CUDA, "cudaStreamCreate failed"); break; }
                 h->wf_streams.push_back(s);
@@ -672,11 +674,34 @@ static int wf_event(crnn_handle* h, int idx, cudaEvent_t* out) {
     *out = h->wf_events[idx];
     return CRNN_OK;
 }
-// event ids: forward (l,c) -> l*C+c ; backward (l,c) -> L*C + l*C+c ; fork/join after those
+// The batch GEMMs that feed / drain a layer's recurrence go to a second stream per layer, so a
+// chunk's GEMM never sits between two recurrence launches of the same layer.
+static cudaStream_t wf_gstream(crnn_handle* h, cudaStream_t st, int l) {
+    return h->wf_W > 1 ? h->wf_streams[h->wf_W + l % h->wf_W] : st;
+}
+static int wf_record(crnn_handle* h, int idx, cudaStream_t s) {
+    cudaEvent_t e;
+    int rc = wf_event(h, idx, &e);
+    if (rc != CRNN_OK) return rc;
+    CRNN_CUDA(cudaEventRecord(e, s));
+    return CRNN_OK;
+}
+static int wf_wait(crnn_handle* h, int idx, cudaStream_t s) {
+    cudaEvent_t e;
+    int rc = wf_event(h, idx, &e);
+    if (rc != CRNN_OK) return rc;
+    CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
+    return CRNN_OK;
+}
+// event ids: family f in {0: fwd recurrence done, 1: fwd x-projection done, 2: bwd recurrence done,
+// 3: bwd input gradients done}: f*L*C + l*C + c ; fork/join events after those
+static inline int wf_id(const crnn_handle* h, int fam, int l, int c) {
+    return (fam * h->cfg.num_layers + l) * h->wf_C + c;
+}
 static int wf_fork(crnn_handle* h, cudaStream_t st, int slot) {
     if (h->wf_W <= 1) return CRNN_OK;
     cudaEvent_t e;
-    int rc = wf_event(h, 2 * h->cfg.num_layers * h->wf_C + slot, &e);
+    int rc = wf_event(h, 4 * h->cfg.num_layers * h->wf_C + slot, &e);
     if (rc != CRNN_OK) return rc;
     CRNN_CUDA(cudaEventRecord(e, st));
     for (cudaStream_t s : h->wf_streams) CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
@@ -684,9 +709,9 @@ static int wf_fork(crnn_handle* h, cudaStream_t st, int slot) {
 }
 static int wf_join(crnn_handle* h, cudaStream_t st, int slot) {
     if (h->wf_W <= 1) return CRNN_OK;
-    for (int i = 0; i < h->wf_W; ++i) {
+    for (int i = 0; i < 2 * h->wf_W; ++i) {
         cudaEvent_t e;
-        int rc = wf_event(h, 2 * h->cfg.num_layers * h->wf_C + slot + i, &e);
+        int rc = wf_event(h, 4 * h->cfg.num_layers * h->wf_C + slot + i, &e);
         if (rc != CRNN_OK) return rc;
         CRNN_CUDA(cudaEventRecord(e, h->wf_streams[i]));
         CRNN_CUDA(cudaStreamWaitEvent(st, e, 0));
@@ -736,27 +761,31 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         CRNN_CUDA(cudaMemcpyAsync(hx, hin, BH * 4, cudaMemcpyDeviceToDevice, s));
         tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, s>>>(hin, H, B, H, hxb, H);
         CRNN_LAUNCH_CHECK("cast_bf16_kernel");
+        cudaStream_t gs = wf_gstream(h, st, l);
         for (int ck = 0; ck < C; ++ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
             if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
-                cudaEvent_t e;
-                rc = wf_event(h, (l - 1) * C + ck, &e);
+                rc = wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
                 if (rc != CRNN_OK) return rc;
-                CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
             }
             if (!wf) prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
             // x half of [x,h]*W for the chunk's steps: A = inputs (K-major), B = kernel rows 0..H stored [K,N]
             const bf16_t* ain = inb + (int64_t)t0 * BH;
             float* gch = gates + (int64_t)t0 * B * gw;
             if (c.model == CRNN_MODEL_GRU) {
-                rc = tc::gemm_bf16_tc(rows, 2 * H, H, ain, H, 0, pbf + lp.oW, 2 * H, 1, gch, gw, lp.b, 0, s, sc);
-                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, ain, H, 0, pbf + lp.oWc, H, 1, gch + 2 * H, gw, lp.bc, 0, s, sc);
+                rc = tc::gemm_bf16_tc(rows, 2 * H, H, ain, H, 0, pbf + lp.oW, 2 * H, 1, gch, gw, lp.b, 0, gs, sc);
+                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, ain, H, 0, pbf + lp.oWc, H, 1, gch + 2 * H, gw, lp.bc, 0, gs, sc);
             } else {
                 const int GH = h->G * H;
-                rc = tc::gemm_bf16_tc(rows, GH, H, ain, H, 0, pbf + lp.oW, GH, 1, gch, gw, lp.b, 0, s, sc);
+                rc = tc::gemm_bf16_tc(rows, GH, H, ain, H, 0, pbf + lp.oW, GH, 1, gch, gw, lp.b, 0, gs, sc);
             }
             if (rc != CRNN_OK) return rc;
+            if (wf) {
+                rc = wf_record(h, wf_id(h, 1, l, ck), gs);
+                if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 1, l, ck), s);
+                if (rc != CRNN_OK) return rc;
+            }
             tc::RecTcArgs a{};
             a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
             a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
@@ -767,10 +796,8 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             if (rc != CRNN_OK) return rc;
             if (!wf) prof_mark(h, st, CRNN_PHASE_MISC);
             if (wf) {
-                cudaEvent_t e;
-                rc = wf_event(h, l * C + ck, &e);
+                rc = wf_record(h, wf_id(h, 0, l, ck), s);
                 if (rc != CRNN_OK) return rc;
-                CRNN_CUDA(cudaEventRecord(e, s));
             }
         }
         float* sout = state_out + (int64_t)l * h->nstate * BH;
@@ -781,7 +808,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             CRNN_CUDA(cudaMemcpyAsync(sout, hx + (int64_t)S * BH, BH * 4, cudaMemcpyDeviceToDevice, s));
         }
     }
-    rc = wf_join(h, st, 1);
+    rc = wf_join(h, st, 1);                      // slots 1 .. 2W
     if (rc != CRNN_OK) return rc;
     const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
     prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
@@ -823,7 +850,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     // l+1 has turned that chunk's dz into input gradients; "rec_bwd" then times the whole fork..join
     // span (recurrences + interleaved input-gradient GEMMs), weight gradients included at its tail.
     if (wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
-    rc = wf_fork(h, st, 1 + h->wf_W);
+    rc = wf_fork(h, st, 1 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
     for (int l = L - 1; l >= 0; --l) {
         cudaStream_t s = wf_stream(h, st, l);
@@ -836,14 +863,13 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         float* dz = wsf(ws, h->ws.dzv[l]);
         bf16_t* dzb = wsb(ws, h->ws.dzbv[l]);
         float* dnext = l > 0 ? wsf(ws, h->ws.gout[l - 1]) : wsf(ws, h->ws.gx0);
+        cudaStream_t gs = wf_gstream(h, st, l);
         for (int ck = C - 1; ck >= 0; --ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
             if (wf && l < L - 1) {                   // layer l+1 has produced this chunk's output gradients
-                cudaEvent_t e;
-                rc = wf_event(h, L * C + (l + 1) * C + ck, &e);
+                rc = wf_wait(h, wf_id(h, 3, l + 1, ck), s);
                 if (rc != CRNN_OK) return rc;
-                CRNN_CUDA(cudaStreamWaitEvent(s, e, 0));
             }
             tc::RecTcArgs a{};
             a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
@@ -854,25 +880,29 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             if (!wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
             rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, s);
             if (rc != CRNN_OK) return rc;
+            if (wf) {
+                rc = wf_record(h, wf_id(h, 2, l, ck), s);
+                if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 2, l, ck), gs);
+                if (rc != CRNN_OK) return rc;
+            }
             // input gradients of the chunk: dIn = dz * Wx^T (A = dz K-major, B = kernel rows 0..H as [N,K])
             if (!wf) prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
             const bf16_t* dzc = dzb + (int64_t)t0 * B * zw;
             float* dn = dnext + (int64_t)t0 * BH;
             if (c.model == CRNN_MODEL_GRU) {
-                rc = tc::gemm_bf16_tc(rows, H, 2 * H, dzc, zw, 0, pbf + lp.oW, 2 * H, 0, dn, H, nullptr, 0, s, sc);
-                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, dzc + 2 * H, zw, 0, pbf + lp.oWc, H, 0, dn, H, nullptr, 1, s, sc);
+                rc = tc::gemm_bf16_tc(rows, H, 2 * H, dzc, zw, 0, pbf + lp.oW, 2 * H, 0, dn, H, nullptr, 0, gs, sc);
+                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, dzc + 2 * H, zw, 0, pbf + lp.oWc, H, 0, dn, H, nullptr, 1, gs, sc);
             } else {
                 const int GH = h->G * H;
-                rc = tc::gemm_bf16_tc(rows, H, GH, dzc, zw, 0, pbf + lp.oW, GH, 0, dn, H, nullptr, 0, s, sc);
+                rc = tc::gemm_bf16_tc(rows, H, GH, dzc, zw, 0, pbf + lp.oW, GH, 0, dn, H, nullptr, 0, gs, sc);
             }
             if (rc != CRNN_OK) return rc;
             if (wf) {
-                cudaEvent_t e;
-                rc = wf_event(h, L * C + l * C + ck, &e);
+                rc = wf_record(h, wf_id(h, 3, l, ck), gs);
                 if (rc != CRNN_OK) return rc;
-                CRNN_CUDA(cudaEventRecord(e, s));
             }
         }
+        s = gs;                                      // weight gradients follow the layer's last input-gradient GEMM
         if (!wf) prof_mark(h, st, CRNN_PHASE_WEIGHT_GRADS);
         float* gW = grads + lp.oW;
         float* gb = grads + lp.ob;
@@ -894,7 +924,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         }
         if (rc != CRNN_OK) return rc;
     }
-    rc = wf_join(h, st, 1 + 2 * h->wf_W);
+    rc = wf_join(h, st, 2 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
     prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
     embed_scatter_kernel<<<grid_for(SB * H, sc), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, wsf(ws, h->ws.gx0), ws_sq(ws));
