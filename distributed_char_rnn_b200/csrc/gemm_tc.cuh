@@ -29,6 +29,8 @@ struct GemmTcArgs {
     int M, N, K;
     int kblocks_per_split;   // BLOCK_K blocks per blockIdx.z
     int mode;                // 0 store, 1 C += (no atomics), 2 atomicAdd (split-K)
+    int tma_out;             // 1: epilogue stages 128x32 slabs in shared memory and writes them with TMA
+                             //    (store, or reduce-add for modes 1 and 2) instead of per-thread stores
     int a_mn, b_mn;          // 1: operand is MN-major in global memory
 };
 
@@ -44,6 +46,7 @@ struct GemmTcSmem {
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
+                                                                  const __grid_constant__ CUtensorMap tmC,
                                                                   GemmTcArgs g) {
     using L = GemmTcSmem<BN, STAGES>;
     extern __shared__ uint8_t smem_raw[];
@@ -127,6 +130,51 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
         mbar_wait(tmem_full, 0);
         tc_fence_after();
         float v[32];
+        if (g.tma_out) {
+            // All TMA loads have been consumed and all MMAs have retired (tmem_full): the pipeline stages
+            // are free, two of them become 128x32 fp32 staging slabs (128-byte swizzled rows).  A thread owns
+            // one accumulator row; it writes eight 16-byte pieces XOR-swizzled by (row & 7) - the layout
+            // the output tensor map expects - then ONE thread hands the slab to the TMA unit, which clips
+            // at the matrix edges and either stores or adds in L2.
+            const int r = 32 * q + lane;
+            const int epi_tid = (warp - 2) * 32 + lane;
+            const bool add_bias = g.bias != nullptr && blockIdx.z == 0;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int nb = n0 + c * 32;
+                if (nb >= g.N) break;               // warp-uniform
+                uint8_t* slab = smem + (c & 1) * (128 * 128);
+                if (c >= 2) {                       // the store issued from this slab two rounds ago has read it
+                    if (epi_tid == 0) bulk_wait_read<1>();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+                tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(c * 32), v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    if (add_bias) {
+                        const int n = nb + 4 * j;
+                        if (n + 3 < g.N) {
+                            float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+                            o.x += b4.x; o.y += b4.y; o.z += b4.z; o.w += b4.w;
+                        } else {
+                            if (n < g.N) o.x += __ldg(g.bias + n);
+                            if (n + 1 < g.N) o.y += __ldg(g.bias + n + 1);
+                            if (n + 2 < g.N) o.z += __ldg(g.bias + n + 2);
+                        }
+                    }
+                    *reinterpret_cast<float4*>(slab + r * 128 + ((j ^ (r & 7)) << 4)) = o;
+                }
+                fence_proxy_async();                // generic writes -> visible to the async proxy
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (epi_tid == 0 && nkb > 0) {
+                    if (g.mode == 0) tma_store_2d(&tmC, slab, nb, m0);
+                    else             tma_reduce_add_2d(&tmC, slab, nb, m0);
+                    bulk_commit();
+                }
+            }
+            if (epi_tid == 0) bulk_wait<0>();
+        } else {
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
             const int nb = n0 + c * 32;
@@ -162,6 +210,7 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
                 }
             }
         }
+        }
         tc_fence_before();
     }
     __syncthreads();
@@ -186,7 +235,14 @@ inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda
     if (rc != CRNN_OK) return rc;
     rc = b_mn ? make_tmap_bf16(&tmB, B, K, N, ldb, 64) : make_tmap_bf16(&tmB, B, N, K, ldb, BN);
     if (rc != CRNN_OK) return rc;
+    CUtensorMap tmC = tmA;                               // placeholder when the TMA epilogue is not usable
+    const int tma_out = ((ldc & 3) == 0 && ((uintptr_t)C & 15) == 0 && ((uintptr_t)bias & 15) == 0) ? 1 : 0;
+    if (tma_out) {
+        rc = make_tmap_f32(&tmC, C, M, N, ldc, GT_BM);
+        if (rc != CRNN_OK) return rc;
+    }
     GemmTcArgs g;
+    g.tma_out = tma_out;
     g.C = C; g.ldc = ldc; g.bias = bias; g.M = M; g.N = N; g.K = K; g.a_mn = a_mn; g.b_mn = b_mn;
     dim3 grid(ceil_div(N, BN), ceil_div(M, GT_BM), 1);
     const int total_kb = ceil_div(K, GT_BK);
@@ -203,7 +259,7 @@ inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda
         CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
         attr_set = true;
     }
-    gemm_bf16_tc_kernel<BN, STAGES><<<grid, GT_THREADS, L::TOTAL, st>>>(tmA, tmB, g);
+    gemm_bf16_tc_kernel<BN, STAGES><<<grid, GT_THREADS, L::TOTAL, st>>>(tmA, tmB, tmC, g);
     CRNN_LAUNCH_CHECK("gemm_bf16_tc_kernel");
     return CRNN_OK;
 }
