@@ -594,6 +594,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.fast_act = h->fast_act;
     a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
     a.swap = backward ? p.swap_bwd : p.swap_fwd;
+    a.m64 = (!a.swap && p.npass == 1 && p.BT <= 64 && env_int("CRNN_TC_M64", 1)) ? 1 : 0;
     a.dbg = (!backward && env_int("CRNN_TC_DEBUG", 0)) ? h->dbg_ptr : nullptr;
     CUtensorMap t0, t1, w0, w1;
     int rc;

@@ -55,6 +55,7 @@ struct RecTcArgs {
     int use3d;                  // streamed operand maps are [kblock][row][64]: one TMA instruction per stage
     int fast_act;               // 1: MUFU.TANH activations
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
+    int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
     float* gates;               // [S,B,GS*H]  in: x-projection + bias, out: activations
     float* hx;                  // [(S+1),B,H]
@@ -149,12 +150,12 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 //            Weight regions hold nc < 128 rows; the rows the M=128 operand reads past them are other
 //            resident data whose products land in accumulator lanes nobody reads.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
-                                       int swap, int nrows16, int box_rows, int ckb, int nst, long long* stamps = nullptr) {
+                                       int swap, int nrows16, int box_rows, int ckb, int nst, int m64, long long* stamps = nullptr) {
     const int tile = rt_tile_bytes(box_rows);
     mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
     tc_fence_after();
     if (stamps) stamps[10] = clock64();
-    const uint32_t idesc = swap ? idesc_bf16(128, nrows16, 0, 0) : idesc_bf16(128, nc, 0, 0);
+    const uint32_t idesc = swap ? idesc_bf16(128, nrows16, 0, 0) : idesc_bf16(m64 ? 64 : 128, nc, 0, 0);
     const uint32_t w0 = smem_u32(wbase);
     for (int kb0 = 0; kb0 < nkb; kb0 += ckb, ++p.ring_i) {
         const int st = p.ring_i % nst;
@@ -208,10 +209,23 @@ __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned targe
 // Accumulator -> shared Zs[r*ldz + c] for batch rows r < nr and gate columns c < nc (ldz odd).
 // A warp can only read its own TMEM lane quarter; quarters holding nothing useful skip the load.
 __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane, int nr, int nc, float* __restrict__ Zs,
-                                        int ldz, int swap) {
+                                        int ldz, int swap, int m64) {
     float v[32];
     constexpr int NH = RT_EPI_WARPS / 4;             // warps per lane quarter
-    if (!swap) {
+    if (m64 && !swap) {
+        // M=64 accumulator: batch row 16*q + lane lives in lane (32*q + lane), lane < 16
+        if (16 * q < nr) {
+            const int r = 16 * q + lane;
+            for (int c0 = 32 * half; c0 < nc; c0 += 32 * NH) {
+                tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
+                if (lane < 16 && r < nr) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c0 + i < nc) Zs[r * ldz + c0 + i] = v[i];
+                }
+            }
+        }
+    } else if (!swap) {
         if (32 * q < nr) {                           // lanes = batch rows
             const int r = 32 * q + lane;
             for (int c0 = 32 * half; c0 < nc; c0 += 32 * NH) {
@@ -267,7 +281,7 @@ __device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ld
     do {                                                                          \
         mbar_wait(s.z_full, p.z_i & 1);                                           \
         tc_fence_after();                                                         \
-        zs_dump(tmem, q, ehalf, lane, nr_, nc_, Zs, ldz, a.swap);                                \
+        zs_dump(tmem, q, ehalf, lane, nr_, nc_, Zs, ldz, a.swap, a.m64);                                \
         tc_fence_before();                                                        \
         mbar_arrive(s.z_empty);                                                   \
         ++p.z_i;                                                                  \
@@ -352,7 +366,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst,
+                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
                                (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
                     RT_STAMP(3);
                 }
@@ -524,9 +538,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64);
             }
         }
     } else {
