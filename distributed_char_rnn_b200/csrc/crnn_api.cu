@@ -625,9 +625,34 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
                     : (backward ? tc::rec_bwd_tc_kernel<MODEL, false> : tc::rec_fwd_tc_kernel<MODEL, false>);
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // Optional clusters along the slice index (CRNN_TC_CLUSTER=2|4|8): the CTAs of a cluster work on the
+    // same batch tile, so the streamed rows are fetched from L2 once per cluster and multicast.  Measured
+    // on B200 it does not pay: config 4 is unchanged at 2 and 4 (its BPTT is bound by the number of small
+    // MMAs, N = 16, not by L2), a 16 x 8 cluster grid with ~200 KB of shared memory per CTA does not get
+    // co-scheduled at all, and config 3 loses 60 % at 8 - so it is off unless asked for.
+    int csize = 1;
+    const int cmax = env_int("CRNN_TC_CLUSTER", 1);
+    for (int cs = 8; cs >= 2; cs >>= 1)
+        if (cs <= cmax && p.nslices % cs == 0) { csize = cs; break; }
+    a.csize = csize;
     void* args[] = {&t0, &t1, &w0, &w1, &a};
     prof_kernel_mark(h, st, backward ? 1 : 0);
-    CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(tc::RT_THREADS), args, smem, st));
+    if (csize == 1) {
+        CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(tc::RT_THREADS), args, smem, st));
+    } else {
+        cudaLaunchConfig_t cfgl{};
+        cfgl.gridDim = dim3(p.nslices * p.ntiles);
+        cfgl.blockDim = dim3(tc::RT_THREADS);
+        cfgl.dynamicSmemBytes = smem;
+        cfgl.stream = st;
+        cudaLaunchAttribute attrs[2];
+        attrs[0].id = cudaLaunchAttributeClusterDimension;
+        attrs[0].val.clusterDim.x = (unsigned)csize; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+        attrs[1].id = cudaLaunchAttributeCooperative;           // all clusters co-resident: tiles span several clusters
+        attrs[1].val.cooperative = 1;
+        cfgl.attrs = attrs; cfgl.numAttrs = 2;
+        CRNN_CUDA(cudaLaunchKernelExC(&cfgl, (const void*)fn, args));
+    }
     prof_kernel_mark(h, st, backward ? 1 : 0);
     ++g_launches;
     return CRNN_OK;

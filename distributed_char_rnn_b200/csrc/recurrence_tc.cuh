@@ -55,6 +55,7 @@ struct RecTcArgs {
     int use3d;                  // streamed operand maps are [kblock][row][64]: one TMA instruction per stage
     int fast_act;               // 1: MUFU.TANH activations
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
+    int csize;                  // CTAs per cluster along the slice index (1: no cluster); they share one batch tile's rows via TMA multicast
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
     float* gates;               // [S,B,GS*H]  in: x-projection + bias, out: activations
@@ -128,17 +129,30 @@ struct RtPipe {
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
-                                           int ckb, int nst, int use3d) {
+                                           int ckb, int nst, int use3d, int csize, int crank) {
     const int tile = rt_tile_bytes(box_rows);
+    const uint16_t mask = (uint16_t)((1u << csize) - 1u);
     for (int kb = 0; kb < nkb; kb += ckb, ++p.ring_i) {
         const int st = p.ring_i % nst;
         const int n = min(ckb, nkb - kb);
+        // (cluster: the empty barrier collects the MMA commits of EVERY CTA of the cluster, because the
+        //  CTA whose turn it is overwrites this stage in all of them)
         mbar_wait(&s.a_empty[st], ((p.ring_i / nst) & 1) ^ 1);
-        if (use3d) {                                   // whole stage in one instruction (out-of-range k-blocks read zero)
-            mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u * (uint32_t)ckb);
+        const uint32_t bytes = (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n);
+        mbar_expect_tx(&s.a_full[st], bytes);
+        if (csize > 1) {
+            // every CTA arms its own barrier; the stages are issued round-robin by the cluster's CTAs and
+            // each issue is multicast to all of them
+            if ((int)(p.ring_i % (uint32_t)csize) != crank) continue;
+            if (use3d) {
+                tma_load_3d_mc(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb, mask);
+            } else {
+                for (int j = 0; j < n; ++j)
+                    tma_load_2d_mc(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow, mask);
+            }
+        } else if (use3d) {                            // whole stage in one instruction (out-of-range k-blocks read zero)
             tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb);
         } else {
-            mbar_expect_tx(&s.a_full[st], (uint32_t)box_rows * 128u * (uint32_t)n);  // one barrier per chunk of tiles
             for (int j = 0; j < n; ++j)
                 tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow);
         }
@@ -150,7 +164,8 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 //            Weight regions hold nc < 128 rows; the rows the M=128 operand reads past them are other
 //            resident data whose products land in accumulator lanes nobody reads.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
-                                       int swap, int nrows16, int box_rows, int ckb, int nst, int m64, long long* stamps = nullptr) {
+                                       int swap, int nrows16, int box_rows, int ckb, int nst, int m64, int csize,
+                                       long long* stamps = nullptr) {
     const int tile = rt_tile_bytes(box_rows);
     mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
     tc_fence_after();
@@ -184,7 +199,8 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
                 mma_bf16(tmem, db + 6, da + 6, idesc, 1u);
             }
         }
-        mma_commit(&s.a_empty[st]);
+        if (csize > 1) mma_commit_mc(&s.a_empty[st], (uint16_t)((1u << csize) - 1u));
+        else           mma_commit(&s.a_empty[st]);
     }
     mma_commit(s.z_full);
     ++p.z_i;
@@ -322,7 +338,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)a.csize); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1);
         fence_barrier_init();
     }
@@ -331,6 +347,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s.tmem_slot;
+    const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
+    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
 
     RtPipe p{0, 0};
     unsigned phases_done = 0;
@@ -353,7 +371,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     if (phases_done > 0) rt_await(a.barrier + tile, phases_done * a.nslices);
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank);
                     RT_STAMP(2);
                     ++phases_done;
                 }
@@ -366,7 +384,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
+                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.csize,
                                (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
                     RT_STAMP(3);
                 }
@@ -459,6 +477,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         }
     }
     __syncthreads();
+    if (a.csize > 1) cluster_sync_all();             // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem, tcols);
@@ -497,7 +516,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)a.csize); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1);
         fence_barrier_init();
     }
@@ -506,6 +525,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s.tmem_slot;
+    const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
+    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
 
     RtPipe p{0, 0};
     unsigned phases_done = 0;
@@ -522,13 +543,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (t + 1 < a.S) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank);
                     ++phases_done;
                 }
             }
@@ -538,9 +559,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.csize);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.csize);
             }
         }
     } else {
@@ -660,6 +681,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         }
     }
     __syncthreads();
+    if (a.csize > 1) cluster_sync_all();             // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem, tcols);
