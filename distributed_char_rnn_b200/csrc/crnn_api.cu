@@ -632,8 +632,22 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // co-scheduled at all, and config 3 loses 60 % at 8 - so it is off unless asked for.
     int csize = 1;
     const int cmax = env_int("CRNN_TC_CLUSTER", 1);
-    for (int cs = 8; cs >= 2; cs >>= 1)
+    for (int cs = 16; cs >= 2; cs >>= 1)
         if (cs <= cmax && p.nslices % cs == 0) { csize = cs; break; }
+    a.mcast = csize > 1 ? 1 : 0;
+    a.cbar = 0;
+    // Cluster barrier: when ALL slices of a batch tile fit in one cluster, the steps are ordered by remote
+    // mbarrier arrives inside the cluster instead of a global counter polled through L2, and nothing ties
+    // different clusters together any more (no cooperative launch needed).  On by default for portable
+    // cluster sizes (config 1: 4 slices, -2 %); 16-CTA clusters (CRNN_TC_CBAR=16) gain 4 % per kernel on
+    // config 3 but eight of them with ~190 KB of shared memory per CTA are not co-scheduled, which costs
+    // the layer wavefront far more than that.
+    const int cbar_max = env_int("CRNN_TC_CBAR", 8);
+    if (!a.mcast && p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
+        csize = p.nslices;
+        a.cbar = 1;
+    }
+    if (csize > 8) CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     a.csize = csize;
     void* args[] = {&t0, &t1, &w0, &w1, &a};
     prof_kernel_mark(h, st, backward ? 1 : 0);
@@ -650,7 +664,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         attrs[0].val.clusterDim.x = (unsigned)csize; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
         attrs[1].id = cudaLaunchAttributeCooperative;           // all clusters co-resident: tiles span several clusters
         attrs[1].val.cooperative = 1;
-        cfgl.attrs = attrs; cfgl.numAttrs = 2;
+        cfgl.attrs = attrs; cfgl.numAttrs = a.cbar ? 1 : 2;     // cluster barrier: clusters are independent
         CRNN_CUDA(cudaLaunchKernelExC(&cfgl, (const void*)fn, args));
     }
     prof_kernel_mark(h, st, backward ? 1 : 0);

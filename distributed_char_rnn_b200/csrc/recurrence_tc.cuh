@@ -55,6 +55,8 @@ struct RecTcArgs {
     int use3d;                  // streamed operand maps are [kblock][row][64]: one TMA instruction per stage
     int fast_act;               // 1: MUFU.TANH activations
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
+    int mcast;                  // 1: the streamed rows are TMA-multicast inside the cluster (ring barriers become cluster-wide)
+    int cbar;                   // 1: the cluster holds ALL slices of a batch tile: steps are ordered by remote mbarrier arrives, no global counter
     int csize;                  // CTAs per cluster along the slice index (1: no cluster); they share one batch tile's rows via TMA multicast
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
@@ -96,7 +98,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 struct RtSmem {
     uint8_t* wsa; uint8_t* wsb; uint8_t* ring; float* zs;
-    uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar;
+    uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar, *step_bar;
     uint32_t* tmem_slot;
 };
 
@@ -112,7 +114,8 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     s.z_full = s.a_empty + RT_MAX_STAGES;
     s.z_empty = s.z_full + 1;
     s.w_bar = s.z_empty + 1;
-    s.tmem_slot = reinterpret_cast<uint32_t*>(s.w_bar + 1);
+    s.step_bar = s.w_bar + 1;
+    s.tmem_slot = reinterpret_cast<uint32_t*>(s.step_bar + 1);
     return s;
 }
 
@@ -129,7 +132,8 @@ struct RtPipe {
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
-                                           int ckb, int nst, int use3d, int csize, int crank) {
+                                           int ckb, int nst, int use3d, int csize_in, int crank, int mcast) {
+    const int csize = mcast ? csize_in : 1;
     const int tile = rt_tile_bytes(box_rows);
     const uint16_t mask = (uint16_t)((1u << csize) - 1u);
     for (int kb = 0; kb < nkb; kb += ckb, ++p.ring_i) {
@@ -212,6 +216,21 @@ __device__ __forceinline__ void rt_publish(unsigned* counter, int epi_tid) {
     epi_bar_sync();                                  // every epilogue thread's stores happen-before ...
     if (epi_tid == 0)                                // ... this release, which is cumulative over them
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
+}
+// Cluster form of the same hand-shake (the cluster = all slices of this batch tile): every slice
+// arrives on every slice's step barrier; the waiting producer sleeps on its own shared-memory barrier
+// instead of polling L2.  The data itself still travels through L2 (generic stores -> TMA loads), so
+// the arriving threads fence at gpu scope first.
+__device__ __forceinline__ void rt_publish_cluster(uint64_t* step_bar, int epi_tid, int csize) {
+    epi_bar_sync();
+    if (epi_tid < csize) {
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        mbar_arrive_remote(step_bar, (uint32_t)epi_tid);
+    }
+}
+__device__ __forceinline__ void rt_await_cluster(uint64_t* step_bar, unsigned phases_done) {
+    mbar_wait_cluster(step_bar, (phases_done - 1u) & 1u);
+    asm volatile("fence.proxy.async;" ::: "memory");
 }
 __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned target) {
     unsigned v;
@@ -338,8 +357,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)a.csize); }
-        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1);
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)(a.mcast ? a.csize : 1)); }
+        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(s.tmem_slot, tcols);
@@ -368,10 +387,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (int)phases_done;
                     RT_STAMP(0);
-                    if (phases_done > 0) rt_await(a.barrier + tile, phases_done * a.nslices);
+                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast);
                     RT_STAMP(2);
                     ++phases_done;
                 }
@@ -384,7 +403,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.csize,
+                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
                                (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
                     RT_STAMP(3);
                 }
@@ -471,7 +490,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 }
                 const int dbg_phase = (t - a.t_begin) * nphase + ph;
                 if (epi_tid == 0) RT_STAMP(6);
-                rt_publish(a.barrier + tile, epi_tid);
+                if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
                 if (epi_tid == 0) RT_STAMP(7);
             }
         }
@@ -516,8 +535,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)a.csize); }
-        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1);
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)(a.mcast ? a.csize : 1)); }
+        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(s.tmem_slot, tcols);
@@ -541,15 +560,15 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
                 if (t + 1 < a.S) {
-                    rt_await(a.barrier + tile, phases_done * a.nslices);
+                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
-                    rt_await(a.barrier + tile, phases_done * a.nslices);
+                    if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast);
                     ++phases_done;
                 }
             }
@@ -559,9 +578,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.csize);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.csize);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
             }
         }
     } else {
@@ -642,7 +661,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 }
                 epi_bar_sync();
             }
-            rt_publish(a.barrier + tile, epi_tid);
+            if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
             if (MODEL == CRNN_MODEL_GRU) {
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(128, bt - ps * 128);
@@ -676,7 +695,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     }
                     epi_bar_sync();
                 }
-                rt_publish(a.barrier + tile, epi_tid);
+                if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
             }
         }
     }
