@@ -601,6 +601,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // ring geometry is per launch (every contraction of the kernel shares the ring and its barriers):
     // sized for the shortest K extent, H
     a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64));
+    { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) a.ckb = std::min(ck_env, ceil_div(H, 64)); }
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb);
     a.use3d = (H % 64 == 0 && env_int("CRNN_TC_3D", 1)) ? 1 : 0;
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {

@@ -32,7 +32,10 @@ constexpr int RT_MROWS_BYTES = 128 * 128; // bytes an M=128 operand reads from a
 // reads.  Small batch tiles get a whole phase's K extent in one or two instructions.
 __host__ __device__ inline int rt_tile_bytes(int box_rows) { return ((box_rows + 7) & ~7) * 128; }
 __host__ __device__ inline int rt_chunk_kb(int box_rows, int nkb) {
-    int c = (24 * 1024) / rt_tile_bytes(box_rows);
+    // ~32 KB per stage: both the producer and the MMA thread pay a few hundred cycles of barrier
+    // hand-shake per stage, which is what bounds the large configurations (measured, config 4:
+    // 1/2/3/4 tiles of 8 KB per stage -> 28.6 / 21.9 / 19.7 / 18.5 ms per step)
+    int c = (32 * 1024) / rt_tile_bytes(box_rows);
     if (c < 1) c = 1;
     if (c > nkb) c = nkb;
     if (c > 256) c = 256;
@@ -125,8 +128,14 @@ inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats) {
 
 // Role-private pipeline state.
 struct RtPipe {
-    uint32_t ring_i;      // A-ring blocks issued / consumed so far
+    uint32_t ring_i;      // ring stages issued / consumed so far
     uint32_t z_i;         // accumulator hand-offs so far
+    uint32_t st;          // current ring stage  (= ring_i % nst, kept incrementally)
+    uint32_t ph;          // current ring phase bit (= (ring_i / nst) & 1)
+    __device__ __forceinline__ void advance(int nst) {
+        ++ring_i;
+        if (++st == (uint32_t)nst) { st = 0; ph ^= 1u; }
+    }
 };
 
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
@@ -136,12 +145,12 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
     const int csize = mcast ? csize_in : 1;
     const int tile = rt_tile_bytes(box_rows);
     const uint16_t mask = (uint16_t)((1u << csize) - 1u);
-    for (int kb = 0; kb < nkb; kb += ckb, ++p.ring_i) {
-        const int st = p.ring_i % nst;
+    for (int kb = 0; kb < nkb; kb += ckb, p.advance(nst)) {
+        const int st = (int)p.st;
         const int n = min(ckb, nkb - kb);
         // (cluster: the empty barrier collects the MMA commits of EVERY CTA of the cluster, because the
         //  CTA whose turn it is overwrites this stage in all of them)
-        mbar_wait(&s.a_empty[st], ((p.ring_i / nst) & 1) ^ 1);
+        mbar_wait(&s.a_empty[st], p.ph ^ 1u);
         const uint32_t bytes = (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n);
         mbar_expect_tx(&s.a_full[st], bytes);
         if (csize > 1) {
@@ -176,9 +185,9 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
     if (stamps) stamps[10] = clock64();
     const uint32_t idesc = swap ? idesc_bf16(128, nrows16, 0, 0) : idesc_bf16(m64 ? 64 : 128, nc, 0, 0);
     const uint32_t w0 = smem_u32(wbase);
-    for (int kb0 = 0; kb0 < nkb; kb0 += ckb, ++p.ring_i) {
-        const int st = p.ring_i % nst;
-        mbar_wait(&s.a_full[st], (p.ring_i / nst) & 1);
+    for (int kb0 = 0; kb0 < nkb; kb0 += ckb, p.advance(nst)) {
+        const int st = (int)p.st;
+        mbar_wait(&s.a_full[st], p.ph);
         tc_fence_after();
         if (stamps) stamps[kb0 == 0 ? 11 : 12] = clock64();
         const int n = min(ckb, nkb - kb0);
@@ -369,7 +378,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
     if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
 
-    RtPipe p{0, 0};
+    RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
     const int nphase = MODEL == CRNN_MODEL_GRU ? 2 : 1;
 
@@ -547,7 +556,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
     if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
 
-    RtPipe p{0, 0};
+    RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
 
     if (warp == 0) {
