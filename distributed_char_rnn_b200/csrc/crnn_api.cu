@@ -53,6 +53,7 @@ struct WsPlan {
 
 struct RecPlanTc {
     int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
+    int q_fwd, q_bwd;       // K parts per unit group (cluster size) of the forward / backward kernel
     size_t smem_fwd, smem_bwd;
 };
 
@@ -221,10 +222,33 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         o->swap_fwd = o->swap_bwd = 0;
         (void)rows16;
         if (sw_env == 1) { o->swap_fwd = g1 * HC <= 128; o->swap_bwd = HC <= 128; }
-        o->zs_fwd = rows * (g1 * HC + 1);
-        o->zs_bwd = rows * (HC + 1);
-        o->smem_fwd = tc::rt_smem_bytes((size_t)nkb * g1 * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, o->zs_fwd);
-        o->smem_bwd = tc::rt_smem_bytes((size_t)ceil_div(g1 * H, 64) * HC * 128, model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, o->zs_bwd);
+        // Split K over Q CTAs of a cluster when the per-CTA MMAs would otherwise be many and narrow
+        // (large H: the issue rate of small-N MMAs, not the tensor pipe, bounds the step).  Same resident
+        // bytes per CTA; N grows Q-fold, the K extent and the streamed rows shrink Q-fold; the partial sums
+        // are exchanged through distributed shared memory, whose staging area grows with N.
+        const size_t wbytes = (size_t)nkb * g1 * HC * 128 + (model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
+        auto pick_q = [&](int ncols_per_unit, int env) -> int {
+            for (int Qc = 4; Qc >= 2; Qc >>= 1) {
+                if (env > 0 && Qc != env) continue;
+                if (env == 0 && (nkb < 16 || ncols_per_unit * HC * Qc > 128)) continue;      // only long K, keep N <= 128
+                // measured (B200): Q = 4 pays (config 4 BPTT 9.9 -> 5.9 ms); Q = 2 pays only when one column per
+                // unit is exchanged (config 5: 26.3 -> 23.9 ms per direction) and loses for the LSTM forward
+                // pass, which gathers four (config 4: 4.6 -> 6.0 ms)
+                if (env == 0 && Qc == 2 && ncols_per_unit > 1) continue;
+                if (H % (64 * Qc) != 0 || H % (HC * Qc) != 0 || nslices % Qc != 0) continue;
+                if (ncols_per_unit * HC * Qc > 256) continue;
+                if ((int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1)) > h->max_smem) continue;
+                return Qc;
+            }
+            return 1;
+        };
+        const int q_env = env_int("CRNN_TC_KSPLIT", -1);       // -1 auto, 0/1 off, 2/4 forced
+        o->q_fwd = q_env == 0 || q_env == 1 ? 1 : pick_q(g1, std::max(q_env, 0));
+        o->q_bwd = q_env == 0 || q_env == 1 ? 1 : pick_q(1, std::max(q_env, 0));
+        o->zs_fwd = rows * (g1 * HC * o->q_fwd + 1);
+        o->zs_bwd = rows * (HC * o->q_bwd + 1);
+        o->smem_fwd = tc::rt_smem_bytes(wbytes, 0, o->zs_fwd);
+        o->smem_bwd = tc::rt_smem_bytes(wbytes, 0, o->zs_bwd);
         return (int)std::max(o->smem_fwd, o->smem_bwd) <= h->max_smem;
     };
     // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
@@ -590,6 +614,9 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const int H = h->cfg.rnn_size, S = h->cfg.seq_length, B = h->cfg.batch_size;
     const int g1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
     const int GW = h->G, GZ = h->GZ;
+    const int Q = backward ? p.q_bwd : p.q_fwd;
+    const int HCG = p.HC * Q;                        // units per group (the columns one CTA contracts)
+    a.ksplit = Q;
     a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles; a.npass = p.npass; a.box_rows = p.box_rows;
     a.fast_act = h->fast_act;
     a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
@@ -611,14 +638,14 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     if (!backward) {
         rc = amap(&t0, a.hxb, (int64_t)(S + 1) * B, H, H);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1, a.rsb, (int64_t)S * B, H, H) : (t1 = t0, CRNN_OK);
-        if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, wr, (int64_t)p.nslices * GW * p.HC, H, H, g1 * p.HC);
-        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, wr, (int64_t)p.nslices * GW * p.HC, H, H, p.HC) : (w1 = w0, CRNN_OK);
+        if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, wr, (int64_t)p.nslices * GW * p.HC, H, H, g1 * HCG);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, wr, (int64_t)p.nslices * GW * p.HC, H, H, HCG) : (w1 = w0, CRNN_OK);
     } else {
         const int64_t zw = (int64_t)GZ * H;
         rc = amap(&t0, a.dzb, (int64_t)(S + 1) * B, (int64_t)g1 * H, zw);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1, a.dzb + 2 * H, (int64_t)(S + 1) * B, H, zw) : (t1 = t0, CRNN_OK);
-        if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, pbf_W, 2 * H, (int64_t)g1 * H, (int64_t)g1 * H, p.HC);
-        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, pbf_Wc, 2 * H, H, H, p.HC) : (w1 = w0, CRNN_OK);
+        if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, pbf_W, 2 * H, (int64_t)g1 * H, (int64_t)g1 * H, HCG);
+        if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, pbf_Wc, 2 * H, H, H, HCG) : (w1 = w0, CRNN_OK);
     }
     if (rc != CRNN_OK) return rc;
     void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
@@ -648,6 +675,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         csize = p.nslices;
         a.cbar = 1;
     }
+    if (Q > 1) { csize = Q; a.mcast = 0; a.cbar = 0; }     // the cluster is the K-split group
     if (csize > 8) CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     a.csize = csize;
     void* args[] = {&t0, &t1, &w0, &w1, &a};
@@ -697,7 +725,9 @@ static int refresh_bf16_params(crnn_handle* h, const float* params, void* ws, cu
         const float* W = params + h->tensors[3 + l * per].offset;
         const float* Wc = per == 4 ? params + h->tensors[3 + l * per + 2].offset : nullptr;
         const int64_t n = (int64_t)h->tcp.nslices * h->G * h->tcp.HC * H;
-        tc::pack_rec_weights_kernel<<<grid_for(n, h->sm_count), 256, 0, st>>>(W, Wc, H, h->tcp.HC, h->tcp.nslices, g1, h->G, H, wsb(ws, h->ws.wr[l]));
+        // one packed group per K-split cluster: q_fwd * HC units, nslices / q_fwd groups (same total size)
+        tc::pack_rec_weights_kernel<<<grid_for(n, h->sm_count), 256, 0, st>>>(W, Wc, H, h->tcp.HC * h->tcp.q_fwd, h->tcp.nslices / h->tcp.q_fwd,
+                                                                              g1, h->G, H, wsb(ws, h->ws.wr[l]));
         CRNN_LAUNCH_CHECK("pack_rec_weights_kernel");
     }
     return CRNN_OK;

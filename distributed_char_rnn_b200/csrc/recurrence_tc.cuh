@@ -58,6 +58,8 @@ struct RecTcArgs {
     int use3d;                  // streamed operand maps are [kblock][row][64]: one TMA instruction per stage
     int fast_act;               // 1: MUFU.TANH activations
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
+    int ksplit;                 // Q: the contraction index is split over Q CTAs of a cluster; each contracts the columns of Q*HC
+                                // units over 1/Q of K and the partial sums are exchanged through distributed shared memory
     int mcast;                  // 1: the streamed rows are TMA-multicast inside the cluster (ring barriers become cluster-wide)
     int cbar;                   // 1: the cluster holds ALL slices of a batch tile: steps are ordered by remote mbarrier arrives, no global counter
     int csize;                  // CTAs per cluster along the slice index (1: no cluster); they share one batch tile's rows via TMA multicast
@@ -101,7 +103,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 struct RtSmem {
     uint8_t* wsa; uint8_t* wsb; uint8_t* ring; float* zs;
-    uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar, *step_bar;
+    uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar, *step_bar, *zs_ready, *zs_free;
     uint32_t* tmem_slot;
 };
 
@@ -118,7 +120,9 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     s.z_empty = s.z_full + 1;
     s.w_bar = s.z_empty + 1;
     s.step_bar = s.w_bar + 1;
-    s.tmem_slot = reinterpret_cast<uint32_t*>(s.step_bar + 1);
+    s.zs_ready = s.step_bar + 1;
+    s.zs_free = s.zs_ready + 1;
+    s.tmem_slot = reinterpret_cast<uint32_t*>(s.zs_free + 1);
     return s;
 }
 
@@ -141,7 +145,7 @@ struct RtPipe {
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
-                                           int ckb, int nst, int use3d, int csize_in, int crank, int mcast) {
+                                           int ckb, int nst, int use3d, int csize_in, int crank, int mcast, int kb_ofs = 0) {
     const int csize = mcast ? csize_in : 1;
     const int tile = rt_tile_bytes(box_rows);
     const uint16_t mask = (uint16_t)((1u << csize) - 1u);
@@ -158,16 +162,16 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
             // each issue is multicast to all of them
             if ((int)(p.ring_i % (uint32_t)csize) != crank) continue;
             if (use3d) {
-                tma_load_3d_mc(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb, mask);
+                tma_load_3d_mc(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kb, mask);
             } else {
                 for (int j = 0; j < n; ++j)
-                    tma_load_2d_mc(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow, mask);
+                    tma_load_2d_mc(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow, mask);
             }
         } else if (use3d) {                            // whole stage in one instruction (out-of-range k-blocks read zero)
-            tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb);
+            tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kb);
         } else {
             for (int j = 0; j < n; ++j)
-                tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb + j) * 64, arow);
+                tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow);
         }
     }
 }
@@ -308,28 +312,69 @@ struct EpiIdx {
     int j;
 };
 __device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ldz, int gstride, int b0row, int j0,
-                                            int H, int64_t tB) {
+                                            int H, int64_t tB, int jcol0 = 0) {
     EpiIdx e;
     e.ok = idx < nunits;
     const int r = e.ok ? idx / hcv : 0;
     const int jj = e.ok ? idx - r * hcv : 0;
-    e.zi = r * ldz + jj * gstride;
+    e.zi = r * ldz + (jcol0 + jj) * gstride;
     e.j = j0 + jj;
     e.o = (int64_t)(b0row + r) * H + e.j;
     e.row = tB + b0row + r;
     return e;
 }
 
+// Accumulator values of a batch of elements: NV consecutive columns per element, summed over the K
+// parts (cluster ranks, always in rank order).  All remote loads are issued before any is consumed,
+// so their distributed-shared-memory latencies overlap instead of adding up.
+template <int NV>
+__device__ __forceinline__ void rt_zgather(float (&zv)[RT_UB][4], const EpiIdx (&e)[RT_UB], const float* __restrict__ Zs,
+                                           const uint32_t* zpeer, int Q, int kq) {
+    if (Q == 1) {
+#pragma unroll
+        for (int u = 0; u < RT_UB; ++u)
+#pragma unroll
+            for (int k = 0; k < NV; ++k) zv[u][k] = e[u].ok ? Zs[e[u].zi + k] : 0.f;
+        return;
+    }
+    float part[RT_UB][NV][4];
+#pragma unroll
+    for (int u = 0; u < RT_UB; ++u)
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                float v = 0.f;
+                if (r < Q && e[u].ok) v = (r == kq) ? Zs[e[u].zi + k] : ld_dsmem_f32(zpeer[r] + 4u * (uint32_t)(e[u].zi + k));
+                part[u][k][r] = v;
+            }
+#pragma unroll
+    for (int u = 0; u < RT_UB; ++u)
+#pragma unroll
+        for (int k = 0; k < NV; ++k) zv[u][k] = ((part[u][k][0] + part[u][k][1]) + part[u][k][2]) + part[u][k][3];
+}
+
 // Wait for the accumulator, move it to shared memory, release TMEM to the MMA thread.
 #define RT_TAKE_ACC(nr_, nc_)                                                     \
     do {                                                                          \
+        if (Q > 1) mbar_wait_cluster(s.zs_free, (p.z_i & 1) ^ 1);  /* peers have read the previous partials */ \
         mbar_wait(s.z_full, p.z_i & 1);                                           \
         tc_fence_after();                                                         \
         zs_dump(tmem, q, ehalf, lane, nr_, nc_, Zs, ldz, a.swap, a.m64);                                \
         tc_fence_before();                                                        \
         mbar_arrive(s.z_empty);                                                   \
-        ++p.z_i;                                                                  \
         epi_bar_sync();                                                           \
+        if (Q > 1) {   /* partial sums of all K parts are in place once every peer has arrived */ \
+            if (epi_tid < Q) mbar_arrive_remote(s.zs_ready, (uint32_t)epi_tid);   \
+            mbar_wait_cluster(s.zs_ready, p.z_i & 1);                             \
+        }                                                                         \
+        ++p.z_i;                                                                  \
+    } while (0)
+
+// All epilogue threads are done with the peers' partial sums of this pass.
+#define RT_RELEASE_PARTIALS()                                                     \
+    do {                                                                          \
+        if (Q > 1 && epi_tid < Q) mbar_arrive_remote(s.zs_free, (uint32_t)epi_tid); \
     } while (0)
 
 // ------------------------------------------------------------------------------------------
@@ -347,14 +392,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     constexpr int G1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
     constexpr int GW = MODEL == CRNN_MODEL_GRU ? 3 : G1;
     const int B = a.B, H = a.H, HC = a.HC;
-    const int NCA = G1 * HC;
-    const int nkb = ceil_div(H, 64);
-    const RtSmem s = rt_carve(smem_raw, (size_t)nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0, a.zs_floats);
+    const int Q = a.ksplit;                           // K parts per unit group (= cluster size when > 1)
+    const int HCG = HC * Q;                           // units whose gate columns this CTA contracts
+    const int NCA = G1 * HCG;
+    const int nkb = ceil_div(H, 64) / Q;              // K blocks of this CTA's part (host: H % (64 Q) == 0 when Q > 1)
+    const RtSmem s = rt_carve(smem_raw, (size_t)nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb * HCG * 128 : 0, a.zs_floats);
     float* Zs = s.zs;
-    const int ldz = NCA + 1;
+    const int ldz = NCA + 1;                          // (GRU candidate pass uses the first HCG columns)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
-    const int j0 = slice * HC, hcv = min(HC, H - j0);
+    const int grp = slice / Q, kq = slice % Q;        // unit group, K part (== rank in the cluster)
+    const int j0 = grp * HCG + kq * HC, hcv = min(HC, H - j0);   // the units this CTA finishes in its epilogue
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
@@ -367,7 +415,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
         for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)(a.mcast ? a.csize : 1)); }
-        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices);
+        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(s.tmem_slot, tcols);
@@ -385,12 +433,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     if (warp == 0) {
         if (lane == 0) {
             // resident weights: once
-            uint32_t wbytes = (uint32_t)nkb * NCA * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb * HC * 128u : 0u);
+            uint32_t wbytes = (uint32_t)nkb * NCA * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb * HCG * 128u : 0u);
             mbar_expect_tx(s.w_bar, wbytes);
             for (int kb = 0; kb < nkb; ++kb) {
-                tma_load_2d(s.wsa + (size_t)kb * NCA * 128, &tmW0, s.w_bar, kb * 64, slice * GW * HC);
+                tma_load_2d(s.wsa + (size_t)kb * NCA * 128, &tmW0, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG);
                 if (MODEL == CRNN_MODEL_GRU)
-                    tma_load_2d(s.wsb + (size_t)kb * HC * 128, &tmW1, s.w_bar, kb * 64, slice * GW * HC + NCA);
+                    tma_load_2d(s.wsb + (size_t)kb * HCG * 128, &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
             }
             for (int t = a.t_begin; t < a.t_end; ++t) {
                 for (int ph = 0; ph < nphase; ++ph) {
@@ -399,7 +447,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb);
                     RT_STAMP(2);
                     ++phases_done;
                 }
@@ -412,7 +460,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HC, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
+                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
                                (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
                     RT_STAMP(3);
                 }
@@ -421,6 +469,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         const int ehalf = (warp - 2) >> 2;            // which of the quarter's warps this is
         const int epi_tid = (warp - 2) * 32 + lane;
+        uint32_t zpeer[4] = {0, 0, 0, 0};            // the peers' accumulator staging areas (distributed shared memory)
+        if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
         for (int t = a.t_begin; t < a.t_end; ++t) {
             const int64_t tB = (int64_t)t * B;
             float* gt = a.gates;
@@ -439,7 +489,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         float x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], ax[RT_UB];
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
-                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, gstride, b0row, j0, H, tB);
+                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, gstride, b0row, j0, H, tB, kq * HC);
                             x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = 0.f;
                             if (e[u].ok) {
                                 const float* g = gt + e[u].row * gw + e[u].j;
@@ -457,18 +507,20 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         }
                         const int dbg_phase = (t - a.t_begin) * nphase + ph;
                         if (epi_tid == 0) RT_STAMP(4);
-                        if (base == 0) RT_TAKE_ACC(nr, ph == 0 ? NCA : HC);
+                        if (base == 0) RT_TAKE_ACC(nr, ph == 0 ? NCA : HCG);
                         if (epi_tid == 0) RT_STAMP(5);
+                        float zv[RT_UB][4];
+                        if (ph == 0) rt_zgather<G1>(zv, e, Zs, zpeer, Q, kq);
+                        else         rt_zgather<1>(zv, e, Zs, zpeer, Q, kq);
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
                             if (!e[u].ok) continue;
                             float* g = gt + e[u].row * gw + e[u].j;
-                            const float* z = Zs + e[u].zi;
                             if (MODEL == CRNN_MODEL_LSTM) {
-                                float si = fast_sigmoid(z[0] + x0[u]);
-                                float tj = fast_tanh(z[1] + x1[u]);
-                                float sf = fast_sigmoid(z[2] + x2[u] + 1.0f);          // forget_bias
-                                float so = fast_sigmoid(z[3] + x3[u]);
+                                float si = fast_sigmoid(zv[u][0] + x0[u]);
+                                float tj = fast_tanh(zv[u][1] + x1[u]);
+                                float sf = fast_sigmoid(zv[u][2] + x2[u] + 1.0f);      // forget_bias
+                                float so = fast_sigmoid(zv[u][3] + x3[u]);
                                 float cn = fmaf(sf, ax[u], si * tj);
                                 float hn = so * fast_tanh(cn);
                                 hnext[e[u].o] = hn;
@@ -476,17 +528,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                 a.cx[(int64_t)(t + 1) * BH + e[u].o] = cn;
                                 g[0] = si; g[H] = tj; g[2 * H] = sf; g[3 * H] = so;
                             } else if (MODEL == CRNN_MODEL_RNN) {
-                                float hn = fast_tanh(z[0] + x0[u]);
+                                float hn = fast_tanh(zv[u][0] + x0[u]);
                                 hnext[e[u].o] = hn;
                                 hnb[e[u].o] = __float2bfloat16_rn(hn);
                             } else if (ph == 0) {
-                                float r_ = fast_sigmoid(z[0] + x0[u]);
-                                float u_ = fast_sigmoid(z[1] + x1[u]);
+                                float r_ = fast_sigmoid(zv[u][0] + x0[u]);
+                                float u_ = fast_sigmoid(zv[u][1] + x1[u]);
                                 float rs = r_ * ax[u];                                   // reset BEFORE the matmul
                                 a.rsb[e[u].row * H + e[u].j] = __float2bfloat16_rn(rs);
                                 g[0] = r_; g[H] = u_; g[3 * H] = rs;
                             } else {
-                                float cand = fast_tanh(z[0] + x0[u]);
+                                float cand = fast_tanh(zv[u][0] + x0[u]);
                                 float hn = fmaf(x1[u], ax[u] - cand, cand);              // u*h + (1-u)*cand
                                 hnext[e[u].o] = hn;
                                 hnb[e[u].o] = __float2bfloat16_rn(hn);
@@ -496,6 +548,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     }
                     { const int dbg_phase = (t - a.t_begin) * nphase + ph; if (epi_tid == 0) RT_STAMP(8); if (epi_tid == RT_EPI_THREADS - 1) RT_STAMP(9); }
                     epi_bar_sync();          // Zs is reused by the next pass / phase
+                    RT_RELEASE_PARTIALS();
                 }
                 const int dbg_phase = (t - a.t_begin) * nphase + ph;
                 if (epi_tid == 0) RT_STAMP(6);
@@ -526,18 +579,22 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     constexpr int G1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
     constexpr int GZ = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 3 : 1);
     const int B = a.B, H = a.H, HC = a.HC;
-    const int nkb0 = ceil_div(G1 * H, 64);
-    const int nkb1 = ceil_div(H, 64);
-    const RtSmem s = rt_carve(smem_raw, (size_t)nkb0 * HC * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb1 * HC * 128 : 0, a.zs_floats);
+    const int Q = a.ksplit;
+    const int HCG = HC * Q;
+    const int nkb0 = ceil_div(G1 * H, 64) / Q;        // this CTA's part of the gate-column contraction
+    const int nkb1 = ceil_div(H, 64) / Q;
+    const RtSmem s = rt_carve(smem_raw, (size_t)nkb0 * HCG * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb1 * HCG * 128 : 0, a.zs_floats);
     float* Zs = s.zs;
-    const int ldz = HC + 1;
+    const int ldz = HCG + 1;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
-    const int j0 = slice * HC, hcv = min(HC, H - j0);
+    const int grp = slice / Q, kq = slice % Q;
+    const int jg0 = grp * HCG;                        // first unit of the group whose dh this CTA contracts
+    const int j0 = jg0 + kq * HC, hcv = min(HC, H - j0);
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, zw = (int64_t)GZ * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
-    while ((int)tcols < (a.swap ? 128 : HC)) tcols <<= 1;
+    while ((int)tcols < (a.swap ? 128 : HCG)) tcols <<= 1;
 
     for (int i = threadIdx.x; i < RT_RING_BYTES / 16; i += RT_THREADS)
         reinterpret_cast<uint4*>(s.ring)[i] = make_uint4(0, 0, 0, 0);
@@ -545,7 +602,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
         for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)(a.mcast ? a.csize : 1)); }
-        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices);
+        mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(s.tmem_slot, tcols);
@@ -561,23 +618,23 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
 
     if (warp == 0) {
         if (lane == 0) {
-            uint32_t wbytes = (uint32_t)nkb0 * HC * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb1 * HC * 128u : 0u);
+            uint32_t wbytes = (uint32_t)nkb0 * HCG * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb1 * HCG * 128u : 0u);
             mbar_expect_tx(s.w_bar, wbytes);
-            for (int kb = 0; kb < nkb0; ++kb) tma_load_2d(s.wsa + (size_t)kb * HC * 128, &tmW0, s.w_bar, kb * 64, H + j0);
+            for (int kb = 0; kb < nkb0; ++kb) tma_load_2d(s.wsa + (size_t)kb * HCG * 128, &tmW0, s.w_bar, (kq * nkb0 + kb) * 64, H + jg0);
             if (MODEL == CRNN_MODEL_GRU)
-                for (int kb = 0; kb < nkb1; ++kb) tma_load_2d(s.wsb + (size_t)kb * HC * 128, &tmW1, s.w_bar, kb * 64, H + j0);
+                for (int kb = 0; kb < nkb1; ++kb) tma_load_2d(s.wsb + (size_t)kb * HCG * 128, &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
                 if (t + 1 < a.S) {
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb0);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb1);
                     ++phases_done;
                 }
             }
@@ -587,15 +644,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HC, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HC, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
             }
         }
     } else {
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         const int ehalf = (warp - 2) >> 2;            // which of the quarter's warps this is
         const int epi_tid = (warp - 2) * 32 + lane;
+        uint32_t zpeer[4] = {0, 0, 0, 0};
+        if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
         // zero the CTA-private carries (they persist in global memory across the launches of one sequence)
         if (MODEL != CRNN_MODEL_RNN && a.t_end == a.S) {
             for (int idx = epi_tid; idx < bt * hcv; idx += RT_EPI_THREADS) {
@@ -615,7 +674,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     float dyv[RT_UB], x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], c0v[RT_UB], c1v[RT_UB], cr[RT_UB];
 #pragma unroll
                     for (int u = 0; u < RT_UB; ++u) {
-                        e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
+                        e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB, kq * HC);
                         dyv[u] = x0[u] = x1[u] = x2[u] = x3[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
                         if (e[u].ok) {
                             const float* g = a.gates + e[u].row * gw + e[u].j;
@@ -634,11 +693,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                             }
                         }
                     }
-                    if (base == 0 && has_next) RT_TAKE_ACC(nr, HC);
+                    if (base == 0 && has_next) RT_TAKE_ACC(nr, HCG);
+                    float zv[RT_UB][4];
+                    if (has_next) rt_zgather<1>(zv, e, Zs, zpeer, Q, kq);
 #pragma unroll
                     for (int u = 0; u < RT_UB; ++u) {
                         if (!e[u].ok) continue;
-                        float dht = dyv[u] + (has_next ? Zs[e[u].zi] : 0.f);
+                        float dht = dyv[u] + (has_next ? zv[u][0] : 0.f);
                         float* dz = a.dz + e[u].row * zw + e[u].j;
                         __nv_bfloat16* dzb = a.dzb + e[u].row * zw + e[u].j;
                         if (MODEL == CRNN_MODEL_LSTM) {
@@ -669,6 +730,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     }
                 }
                 epi_bar_sync();
+                if (has_next) RT_RELEASE_PARTIALS();
             }
             if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
             if (MODEL == CRNN_MODEL_GRU) {
@@ -681,7 +743,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                         float x0[RT_UB], x1[RT_UB], hp[RT_UB], c1v[RT_UB];
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
-                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB);
+                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB, kq * HC);
                             x0[u] = x1[u] = hp[u] = c1v[u] = 0.f;
                             if (e[u].ok) {
                                 const float* g = a.gates + e[u].row * gw + e[u].j;
@@ -690,11 +752,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                                 c1v[u] = a.carry1[e[u].o];
                             }
                         }
-                        if (base == 0) RT_TAKE_ACC(nr, HC);
+                        if (base == 0) RT_TAKE_ACC(nr, HCG);
+                        float zv[RT_UB][4];
+                        rt_zgather<1>(zv, e, Zs, zpeer, Q, kq);
 #pragma unroll
                         for (int u = 0; u < RT_UB; ++u) {
                             if (!e[u].ok) continue;
-                            const float drs = Zs[e[u].zi];
+                            const float drs = zv[u][0];
                             const float r_ = x0[u], u_ = x1[u];
                             const float dr = drs * hp[u] * r_ * (1.0f - r_);
                             a.dz[e[u].row * zw + e[u].j] = dr;
@@ -703,6 +767,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                         }
                     }
                     epi_bar_sync();
+                    RT_RELEASE_PARTIALS();
                 }
                 if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
             }
@@ -717,6 +782,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
 }
 
 #undef RT_TAKE_ACC
+#undef RT_RELEASE_PARTIALS
 #undef fast_tanh
 #undef fast_sigmoid
 

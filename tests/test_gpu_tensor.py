@@ -123,6 +123,12 @@ BF16_SHAPES = [
     ("gru", 128, 1, 5, 300, 13, {"CRNN_TC_HC": 16, "CRNN_TC_TILES": 2, "CRNN_TC_CLUSTER": 8}),
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16}),
     ("gru", 128, 2, 7, 24, 13, {"CRNN_TC_HC": 16, "CRNN_WAVEFRONT": 1, "CRNN_TC_CLUSTER": 4}),
+    # K split over a cluster of 2 / 4 CTAs, partial sums exchanged through distributed shared memory
+    ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 2}),
+    ("gru", 256, 1, 5, 20, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 4}),
+    ("rnn", 256, 2, 5, 70, 13, {"CRNN_TC_HC": 32, "CRNN_TC_KSPLIT": 2}),
+    ("lstm", 256, 1, 4, 150, 9, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 4, "CRNN_TC_TILES": 1}),
+    ("gru", 128, 2, 8, 24, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 2, "CRNN_WAVEFRONT_CHUNKS": 3}),
     # cluster step barrier (remote mbarrier arrives) at 16 slices, and switched off
     ("gru", 256, 1, 5, 20, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 16}), ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 0}),
 ]
