@@ -132,7 +132,7 @@ def best_cpu_threads(c):
     ncpu = os.cpu_count() or 1
     best, best_t = ncpu, None
     for th in sorted({ncpu, max(1, ncpu // 2), max(1, ncpu // 4), 1}, reverse=True):
-        r = cpu_restatement_rate(c, 2.0, 1, steps=1, batch=max(1, c["batch_size"] // 8), threads=th)
+        r = cpu_restatement_rate(c, 2.0, 1 if c["rnn_size"] <= 512 else 0, steps=1, batch=max(1, c["batch_size"] // 16), threads=th)
         if best_t is None or r["seconds"] < best_t:
             best, best_t = th, r["seconds"]
     return best
@@ -385,9 +385,18 @@ def main():
         dist.barrier()
     cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_restatement_rate(c, 12.0, 1, threads=best_cpu_threads(c))
+        th = best_cpu_threads(c)
+        # bound the sample: a CPU step of the large configs is tens of TFLOP; use fewer sequences per step
+        probe_b = max(1, B // 8)
+        probe = cpu_restatement_rate(c, 5.0, 0, steps=1, batch=probe_b, threads=th)
+        bs = B
+        while bs > 1 and probe["seconds"] / probe_b * bs > 6.0:
+            bs //= 2
+        r = cpu_restatement_rate(c, 12.0, 1, batch=bs, threads=th)
         cpu = {"value": r["value"], "unit": "chars/s", "cores": r["cores"], "kind": "port",
-               "sample": "1 warm-up + %d full steps (%d chars each) in %.1f s" % (r["steps"], B * S, r["seconds"])}
+               "sample": "1 warm-up + %d steps of [%d of %d sequences x S=%d] (%d chars each) in %.1f s"
+                         % (r["steps"], bs, B, S, bs * S, r["seconds"])}
+    if cpu is not None and bs == B:
         # loss parity: the same first steps (same seed-0 weights, same batches) on the GPU path
         m2 = Model(margs, device="cuda:%d" % local_rank, seed=0, precision=args.precision)
         m2.assign_lr(0.002)
