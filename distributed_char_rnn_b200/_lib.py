@@ -20,7 +20,8 @@ c_i32, c_i64, c_f32, c_vp = ctypes.c_int32, ctypes.c_int64, ctypes.c_float, ctyp
 
 class CrnnConfig(ctypes.Structure):
     _fields_ = [("model", c_i32), ("rnn_size", c_i32), ("num_layers", c_i32), ("seq_length", c_i32),
-                ("batch_size", c_i32), ("vocab_size", c_i32), ("precision", c_i32), ("device", c_i32)]
+                ("batch_size", c_i32), ("vocab_size", c_i32), ("precision", c_i32), ("device", c_i32),
+                ("input_keep_prob", c_f32), ("output_keep_prob", c_f32), ("dropout_seed", c_i32), ("reserved", c_i32)]
 
 
 # name -> (restype, argtypes); must list every symbol include/crnn.h declares
@@ -46,6 +47,7 @@ SIGNATURES = {
     "crnn_profile_read": (c_i32, [c_vp, ctypes.POINTER(ctypes.c_double), c_i32]),
     "crnn_profile_phase_name": (ctypes.c_char_p, [c_i32]),
     "crnn_profile_read_kernels": (c_i32, [c_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_i64), c_i32]),
+    "crnn_dropout_mask": (c_i32, [c_vp, c_i64, c_i32, c_vp, c_vp]),
     "crnn_embedding_gather": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "crnn_embedding_scatter_add": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "crnn_softmax_xent": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp]),

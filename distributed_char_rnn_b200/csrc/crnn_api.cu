@@ -45,6 +45,8 @@ struct WsPlan {
     std::vector<size_t> hx, cx, gates;
     size_t dz, dya, dyb, carry0, carry1, logits;
     // CRNN_PREC_BF16 only: bf16 MMA operands
+    std::vector<size_t> xin, xinb;   // dropout: masked copy of each layer's input (fp32 / bf16)
+    size_t topd, topdb;              // dropout: masked top-layer output as the projection sees it
     size_t pbf, wsmb, x0b, dlb, gx0;
     std::vector<size_t> wr, hxb, rsb;
     std::vector<size_t> dzv, dzbv, gout, carry0v, carry1v;   // per layer: layers run concurrently (wavefront)
@@ -76,6 +78,10 @@ struct crnn_handle {
     int wf_W, wf_C;
     std::vector<cudaStream_t> wf_streams;
     std::vector<cudaEvent_t> wf_events;
+    // dropout (training calls only): keep probabilities, seed, and the count of training calls so far
+    float ikp, okp;
+    bool drop_on;
+    long long fb_calls;
     long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
     int fast_act;
@@ -316,8 +322,18 @@ static void build_workspace(crnn_handle* h) {
     w.carry0 = fp32_path ? take(B * H) : 0;
     w.carry1 = fp32_path ? take(B * H) : 0;
     w.logits = take(S * B * V);
+    auto take2 = [&](int64_t halves) { return take((halves + 1) / 2); };
+    w.topd = w.topdb = 0;
+    if (h->drop_on) {
+        const bool bf = h->cfg.precision == CRNN_PREC_BF16;
+        for (int l = 0; l < L; ++l) {
+            w.xin.push_back(take(S * B * H));
+            w.xinb.push_back(bf ? take2(S * B * H) : 0);
+        }
+        w.topd = take(S * B * H);
+        w.topdb = bf ? take2(S * B * H) : 0;
+    }
     if (h->cfg.precision == CRNN_PREC_BF16) {
-        auto take2 = [&](int64_t halves) { return take((halves + 1) / 2); };
         const int64_t GW = h->G;
         w.pbf = take2(h->P);
         w.wsmb = take2(H * h->Vp);
@@ -352,6 +368,8 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         return set_err(CRNN_ERR_ARG, "model type not supported: %d", cfg->model);
     if (cfg->rnn_size < 1 || cfg->num_layers < 1 || cfg->seq_length < 1 || cfg->batch_size < 1 || cfg->vocab_size < 1)
         return set_err(CRNN_ERR_ARG, "rnn_size, num_layers, seq_length, batch_size and vocab_size must be >= 1");
+    if (cfg->input_keep_prob < 0.f || cfg->input_keep_prob > 1.f || cfg->output_keep_prob < 0.f || cfg->output_keep_prob > 1.f)
+        return set_err(CRNN_ERR_ARG, "keep probabilities must be in (0, 1] (0 = unset = 1.0)");
     if (cfg->precision != CRNN_PREC_FP32 && cfg->precision != CRNN_PREC_BF16)
         return set_err(CRNN_ERR_ARG, "unknown precision %d", cfg->precision);
     int ndev = 0;
@@ -383,6 +401,10 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     if (rc == CRNN_OK) rc = plan_recurrence(h, true, &h->bwd);
     h->Vp = (cfg->vocab_size + 7) & ~7;
     h->fast_act = env_int("CRNN_FAST_ACT", 1);
+    h->ikp = (cfg->input_keep_prob > 0.f && cfg->input_keep_prob < 1.f) ? cfg->input_keep_prob : 1.0f;
+    h->okp = (cfg->output_keep_prob > 0.f && cfg->output_keep_prob < 1.f) ? cfg->output_keep_prob : 1.0f;
+    h->drop_on = h->ikp < 1.0f || h->okp < 1.0f;
+    h->fb_calls = 0;
     h->wf_W = 1; h->wf_C = 1;
     if (rc == CRNN_OK && cfg->precision == CRNN_PREC_BF16) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
@@ -534,10 +556,34 @@ static int grid_for(int64_t n_threads_needed, int sm_count) {
     return (int)std::max<int64_t>(1, std::min<int64_t>(blocks, (int64_t)sm_count * 8));
 }
 
+// ---- dropout sites ---------------------------------------------------------------------------
+// site l < L: what cell l reads = (embedding mask | output mask of cell l-1) x input mask of cell l;
+// site L: the top cell's output as the projection reads it.
+static DropArgs drop_args(const crnn_handle* h, long long call, int site, int64_t idx0) {
+    const int L = h->cfg.num_layers;
+    DropArgs d;
+    d.seed = (uint64_t)(uint32_t)h->cfg.dropout_seed * 0x100000001B3ull + (uint64_t)call * 0x9E3779B97F4A7C15ull + 0x5851F42D4C957F2Dull;
+    d.idx0 = idx0;
+    if (site >= L) { d.stage_a = 2 + 2 * (L - 1); d.keep_a = h->okp; d.stage_b = 0; d.keep_b = 1.0f; }
+    else if (site == 0) { d.stage_a = 0; d.keep_a = h->okp; d.stage_b = 1; d.keep_b = h->ikp; }
+    else { d.stage_a = 2 + 2 * (site - 1); d.keep_a = h->okp; d.stage_b = 1 + 2 * site; d.keep_b = h->ikp; }
+    return d;
+}
+// dst(/dst_b) = src * masks of `site` for elements [idx0, idx0+n) of the [S,B,H] tensor.
+static int drop_apply(const crnn_handle* h, long long call, int site, const float* src, float* dst, __nv_bfloat16* dst_b,
+                      int64_t idx0, int64_t n, cudaStream_t st) {
+    if (n <= 0) return CRNN_OK;
+    const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n, 256), (int64_t)h->sm_count * 8));
+    dropout_apply_kernel<<<(int)blocks, 256, 0, st>>>(src, dst, dst_b, n, drop_args(h, call, site, idx0));
+    CRNN_LAUNCH_CHECK("dropout_apply_kernel");
+    return CRNN_OK;
+}
+
 // Forward pass over all layers; leaves hx/cx/gates stashes in the workspace.
 static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
-                       const float* params, void* ws, cudaStream_t st) {
+                       const float* params, void* ws, cudaStream_t st, long long drop_call = -1) {
     const crnn_config& c = h->cfg;
+    const bool drop = h->drop_on && drop_call >= 0;       // training calls only (model.py:31, training=True)
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H;
@@ -554,6 +600,11 @@ static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const floa
         float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
         float* gates = wsf(ws, h->ws.gates[l]);
         const float* in = l == 0 ? x0 : wsf(ws, h->ws.hx[l - 1]) + BH;
+        if (drop) {
+            int rcd = drop_apply(h, drop_call, l, in, wsf(ws, h->ws.xin[l]), nullptr, 0, SB * H, st);
+            if (rcd != CRNN_OK) return rcd;
+            in = wsf(ws, h->ws.xin[l]);
+        }
         const float* sin = state_in + (int64_t)l * h->nstate * BH;
         if (c.model == CRNN_MODEL_LSTM) {
             CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, st));
@@ -591,6 +642,11 @@ static int run_forward(crnn_handle* h, const int32_t* x, int64_t ldx, const floa
     }
     // logits (time-major rows t*B+b) = top outputs * softmax_w + softmax_b   (model.py:76)
     const float* top = wsf(ws, h->ws.hx[L - 1]) + BH;
+    if (drop) {
+        int rcd = drop_apply(h, drop_call, L, top, wsf(ws, h->ws.topd), nullptr, 0, SB * H, st);
+        if (rcd != CRNN_OK) return rcd;
+        top = wsf(ws, h->ws.topd);
+    }
     const float* Wsm = params + h->tensors[0].offset;
     const float* bsm = params + h->tensors[1].offset;
     prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
@@ -792,8 +848,9 @@ static int wf_join(crnn_handle* h, cudaStream_t st, int slot) {
 static inline int wf_t0(const crnn_handle* h, int c) { return (int)((int64_t)h->cfg.seq_length * c / h->wf_C); }
 
 static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
-                            const float* params, void* ws, cudaStream_t st) {
+                            const float* params, void* ws, cudaStream_t st, long long drop_call = -1) {
     const crnn_config& c = h->cfg;
+    const bool drop = h->drop_on && drop_call >= 0;
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
     const int64_t BH = (int64_t)B * H;
     const int64_t SB = (int64_t)S * B;
@@ -825,7 +882,8 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
         float* gates = wsf(ws, h->ws.gates[l]);
         bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
-        const bf16_t* inb = l == 0 ? x0b : wsb(ws, h->ws.hxb[l - 1]) + BH;
+        const bf16_t* inb = drop ? wsb(ws, h->ws.xinb[l]) : (l == 0 ? x0b : wsb(ws, h->ws.hxb[l - 1]) + BH);
+        const float* in32 = l == 0 ? x0 : wsf(ws, h->ws.hx[l - 1]) + BH;      // dropout masks the fp32 source
         const float* sin = state_in + (int64_t)l * h->nstate * BH;
         const float* hin = c.model == CRNN_MODEL_LSTM ? sin + BH : sin;
         if (c.model == CRNN_MODEL_LSTM) CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, s));
@@ -838,6 +896,11 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             const int rows = (t1 - t0) * B;
             if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
                 rc = wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
+                if (rc != CRNN_OK) return rc;
+            }
+            if (drop) {                              // masked bf16 copy of this chunk's inputs
+                rc = drop_apply(h, drop_call, l, in32 + (int64_t)t0 * BH, nullptr, wsb(ws, h->ws.xinb[l]) + (int64_t)t0 * BH,
+                                (int64_t)t0 * BH, (int64_t)rows * H, gs);
                 if (rc != CRNN_OK) return rc;
             }
             if (!wf) prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
@@ -882,6 +945,11 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     rc = wf_join(h, st, 1);                      // slots 1 .. 2W
     if (rc != CRNN_OK) return rc;
     const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
+    if (drop) {
+        rc = drop_apply(h, drop_call, L, wsf(ws, h->ws.hx[L - 1]) + BH, nullptr, wsb(ws, h->ws.topdb), 0, SB * H, st);
+        if (rc != CRNN_OK) return rc;
+        topb = wsb(ws, h->ws.topdb);
+    }
     prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
     rc = tc::gemm_bf16_tc((int)SB, V, H, topb, H, 0, wsb(ws, h->ws.wsmb), h->Vp, 1, wsf(ws, h->ws.logits), V,
                           params + h->tensors[1].offset, 0, st, sc);
@@ -890,8 +958,9 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
 }
 
 static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t* y, int64_t ld, const float* state_in,
-                                 float* state_out, const float* params, float* grads, void* ws, cudaStream_t st) {
+                                 float* state_out, const float* params, float* grads, void* ws, cudaStream_t st, long long call) {
     const crnn_config& c = h->cfg;
+    const bool drop = h->drop_on;
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H, zw = h->GZ * H, Vp = h->Vp;
@@ -901,7 +970,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
-    int rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st);
+    int rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st, call);
     if (rc != CRNN_OK) return rc;
     const bf16_t* pbf = wsb(ws, h->ws.pbf);
     float* logits = wsf(ws, h->ws.logits);
@@ -909,12 +978,13 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
     softmax_xent_kernel<<<grid_for(SB * 32, sc), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp);
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
-    const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
+    const bf16_t* topb = drop ? wsb(ws, h->ws.topdb) : wsb(ws, h->ws.hxb[L - 1]) + BH;
     prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
     // d softmax_w [H,V] = out^T * dlogits ; d softmax_b = colsum ; d out = dlogits * softmax_w^T
     rc = tc::gemm_bf16_tc(H, V, (int)SB, topb, H, 1, dlb, Vp, 1, grads + h->tensors[0].offset, V, nullptr, 1, st, sc);
     if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
     if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, V, dlb, Vp, 0, wsb(ws, h->ws.wsmb), Vp, 0, wsf(ws, h->ws.gout[L - 1]), H, nullptr, 0, st, sc);
+    if (rc == CRNN_OK && drop) rc = drop_apply(h, call, L, wsf(ws, h->ws.gout[L - 1]), wsf(ws, h->ws.gout[L - 1]), nullptr, 0, SB * H, st);
     if (rc != CRNN_OK) return rc;
 
     // BPTT, top layer first.  Wavefront: layer l works on chunk c (late steps first) as soon as layer
@@ -930,7 +1000,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
         float* gates = wsf(ws, h->ws.gates[l]);
         const bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
-        const bf16_t* inb = l == 0 ? wsb(ws, h->ws.x0b) : wsb(ws, h->ws.hxb[l - 1]) + BH;
+        const bf16_t* inb = drop ? wsb(ws, h->ws.xinb[l]) : (l == 0 ? wsb(ws, h->ws.x0b) : wsb(ws, h->ws.hxb[l - 1]) + BH);
         float* dz = wsf(ws, h->ws.dzv[l]);
         bf16_t* dzb = wsb(ws, h->ws.dzbv[l]);
         float* dnext = l > 0 ? wsf(ws, h->ws.gout[l - 1]) : wsf(ws, h->ws.gx0);
@@ -967,6 +1037,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
                 const int GH = h->G * H;
                 rc = tc::gemm_bf16_tc(rows, H, GH, dzc, zw, 0, pbf + lp.oW, GH, 0, dn, H, nullptr, 0, gs, sc);
             }
+            if (rc == CRNN_OK && drop) rc = drop_apply(h, call, l, dn, dn, nullptr, (int64_t)t0 * BH, (int64_t)rows * H, gs);
             if (rc != CRNN_OK) return rc;
             if (wf) {
                 rc = wf_record(h, wf_id(h, 3, l, ck), gs);
@@ -1026,7 +1097,9 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     const crnn_config& c = h->cfg;
     if (ld < c.seq_length) return set_err(CRNN_ERR_ARG, "ld_xy %lld < seq_length %d", (long long)ld, c.seq_length);
     cudaStream_t st = (cudaStream_t)stream;
-    if (c.precision == CRNN_PREC_BF16) return forward_backward_bf16(h, x, y, ld, state_in, state_out, params, grads, ws, st);
+    const long long call = h->fb_calls++;               // index of this training call (dropout masks)
+    const bool drop = h->drop_on;
+    if (c.precision == CRNN_PREC_BF16) return forward_backward_bf16(h, x, y, ld, state_in, state_out, params, grads, ws, st, call);
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H, zw = h->GZ * H;
@@ -1034,7 +1107,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
-    rc = run_forward(h, x, ld, state_in, state_out, params, ws, st);
+    rc = run_forward(h, x, ld, state_in, state_out, params, ws, st, call);
     if (rc != CRNN_OK) return rc;
     prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
 
@@ -1042,7 +1115,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     float* logits = wsf(ws, h->ws.logits);
     softmax_xent_kernel<<<grid_for(SB * 32, h->sm_count), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), nullptr, 0);
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
-    const float* top = wsf(ws, h->ws.hx[L - 1]) + BH;
+    const float* top = drop ? wsf(ws, h->ws.topd) : wsf(ws, h->ws.hx[L - 1]) + BH;
     const float* Wsm = params + h->tensors[0].offset;
     float* dya = wsf(ws, h->ws.dya);
     float* dyb = wsf(ws, h->ws.dyb);
@@ -1050,6 +1123,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     rc = gemm_f32(1, 0, H, V, (int)SB, top, H, logits, V, grads + h->tensors[0].offset, V, nullptr, 1, st, h->sm_count);
     if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
     if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, V, logits, V, Wsm, V, dya, H, nullptr, 0, st, h->sm_count);
+    if (rc == CRNN_OK && drop) rc = drop_apply(h, call, L, dya, dya, nullptr, 0, SB * H, st);   // back through the output mask
     if (rc != CRNN_OK) return rc;
 
     float* dz = wsf(ws, h->ws.dz);
@@ -1060,7 +1134,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
         float* hx = wsf(ws, h->ws.hx[l]);
         float* cx = c.model == CRNN_MODEL_LSTM ? wsf(ws, h->ws.cx[l]) : nullptr;
         float* gates = wsf(ws, h->ws.gates[l]);
-        const float* in = l == 0 ? wsf(ws, h->ws.x0) : wsf(ws, h->ws.hx[l - 1]) + BH;
+        const float* in = drop ? wsf(ws, h->ws.xin[l]) : (l == 0 ? wsf(ws, h->ws.x0) : wsf(ws, h->ws.hx[l - 1]) + BH);
         RecArgs a{};
         a.B = B; a.H = H; a.S = S; a.GS = h->GS;
         a.W = lp.W; a.Wc = lp.Wc; a.gates = gates; a.hx = hx; a.cx = cx;
@@ -1095,6 +1169,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
             prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
             if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, GH, dz, zw, lp.W, GH, dnext, H, nullptr, 0, st, sc);
         }
+        if (rc == CRNN_OK && drop) rc = drop_apply(h, call, l, dnext, dnext, nullptr, 0, SB * H, st);   // back through this cell's input masks
         if (rc != CRNN_OK) return rc;
         std::swap(dcur, dnext);
     }
@@ -1250,6 +1325,13 @@ int crnn_gemm_f32(int32_t ta, int32_t tb, int32_t M, int32_t N, int32_t K, const
     if (!A || !B || !C) return set_err(CRNN_ERR_ARG, "null device pointer");
     if (M < 0 || N < 0 || K < 0) return set_err(CRNN_ERR_ARG, "bad shape");
     return gemm_f32(ta, tb, M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, (cudaStream_t)stream);
+}
+
+int crnn_dropout_mask(const crnn_handle* h, int64_t call_index, int32_t site, float* out, void* stream) {
+    if (!h || !out) return set_err(CRNN_ERR_ARG, "null argument");
+    if (site < 0 || site > h->cfg.num_layers || call_index < 0) return set_err(CRNN_ERR_ARG, "site must be in [0, num_layers], call_index >= 0");
+    const int64_t n = (int64_t)h->cfg.seq_length * h->cfg.batch_size * h->cfg.rnn_size;
+    return drop_apply(h, call_index, site, nullptr, out, nullptr, 0, n, (cudaStream_t)stream);
 }
 
 int crnn_gemm_bf16(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K, const void* A, int64_t lda,

@@ -64,6 +64,37 @@ __global__ void __launch_bounds__(256) embed_scatter_kernel(float* __restrict__ 
     if (threadIdx.x == 0 && sqnorm) atomicAdd(sqnorm, tot);
 }
 
+// ---- dropout (model.py:31-34,58-59; train.py:58-61) ----------------------------------------
+// tf.nn.dropout: x * floor(keep + u) / keep, a fresh mask per element and per step.  Masks are not
+// stored: they are a pure function of (seed, training-call index, stage, element index), regenerated
+// in the backward pass.  Stages: 0 = embedding, 1+2l = input of cell l, 2+2l = output of cell l.
+// A layer input carries the product of two masks (what produced it, and the cell's input wrapper).
+__device__ __forceinline__ float dropout_mult(uint64_t seed, uint32_t stage, uint64_t idx, float keep) {
+    if (keep >= 1.0f) return 1.0f;
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (uint64_t)(stage + 1) + idx * 0xD1B54A32D192ED03ull;
+    z ^= z >> 33; z *= 0xFF51AFD7ED558CCDull; z ^= z >> 33; z *= 0xC4CEB9FE1A85EC53ull; z ^= z >> 33;
+    const float u = (float)(uint32_t)(z >> 40) * (1.0f / 16777216.0f);        // uniform [0,1)
+    return u < keep ? 1.0f / keep : 0.0f;
+}
+
+struct DropArgs {
+    uint64_t seed;
+    uint32_t stage_a, stage_b;
+    float keep_a, keep_b;
+    int64_t idx0;          // global element index of src[0] inside the [S,B,H] tensor (chunked calls)
+};
+
+// dst = src * mask_a * mask_b (dst may equal src); optional bf16 copy.
+__global__ void __launch_bounds__(256) dropout_apply_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                                            __nv_bfloat16* __restrict__ dst_bf16, int64_t n, DropArgs d) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint64_t gi = (uint64_t)(d.idx0 + i);
+        const float v = (src ? src[i] : 1.0f) * dropout_mult(d.seed, d.stage_a, gi, d.keep_a) * dropout_mult(d.seed, d.stage_b, gi, d.keep_b);
+        if (dst) dst[i] = v;
+        if (dst_bf16) dst_bf16[i] = __float2bfloat16_rn(v);
+    }
+}
+
 // ---- softmax + sequence cross-entropy (model.py:77,80-85) ---------------------------------
 // One warp per row of logits [N, V] (row i = t*B + b).  In place: logits -> (softmax-onehot)/N.
 __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ logits, int B, int S, int V,

@@ -43,8 +43,11 @@ class Model(object):
             raise Exception("model type not supported on this engine: nas (rnn.NASCell is out of scope)")
         if args.model not in MODEL_IDS:        # model.py:24-25
             raise Exception("model type not supported: {}".format(args.model))
-        if training and (getattr(args, "output_keep_prob", 1.0) < 1.0 or getattr(args, "input_keep_prob", 1.0) < 1.0):
-            raise Exception("dropout (keep_prob < 1.0) is not implemented on this engine")
+        # DropoutWrapper per cell + tf.nn.dropout on the embedded inputs, training graphs only (model.py:31-34,58-59)
+        ikp = float(getattr(args, "input_keep_prob", 1.0)) if training else 1.0
+        okp = float(getattr(args, "output_keep_prob", 1.0)) if training else 1.0
+        if not (0.0 < ikp <= 1.0 and 0.0 < okp <= 1.0):
+            raise Exception("keep probabilities must be in (0, 1]")
         if not torch.cuda.is_available():
             raise _lib.CrnnError("no CUDA device: distributed_char_rnn_b200 has no CPU path")
         self.training = training
@@ -54,8 +57,10 @@ class Model(object):
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
 
+        self.dropout_seed = int(np.random.SeedSequence(seed).generate_state(1)[0] & 0x7FFFFFFF) if (ikp < 1 or okp < 1) else 0
         cfg = CrnnConfig(MODEL_IDS[args.model], args.rnn_size, args.num_layers, args.seq_length, args.batch_size,
-                         args.vocab_size, PREC_IDS[precision], self.device.index or 0)
+                         args.vocab_size, PREC_IDS[precision], self.device.index or 0, ikp, okp, self.dropout_seed, 0)
+        self.training_calls = 0                 # crnn_forward_backward calls so far = index of the next dropout mask set
         h = ctypes.c_void_p()
         check(self._lib.crnn_create(ctypes.byref(cfg), ctypes.byref(h)))
         self._h = h
@@ -203,6 +208,7 @@ class Model(object):
             self._state.copy_(state)
         st = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         self.global_step += 1
+        self.training_calls += 1
         a = self.args
         if self.world == 1:
             check(self._lib.crnn_train_step(self._h, ptr(xd), ptr(yd), self._ld(xd), ptr(self._state),
@@ -235,8 +241,21 @@ class Model(object):
         st = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         check(self._lib.crnn_forward_backward(self._h, ptr(xd), ptr(yd), self._ld(xd), ptr(sin), ptr(sout),
                                               ptr(self.params), ptr(self.grads), ptr(self.workspace), st))
+        self.training_calls += 1
         torch.cuda.current_stream(self.device).synchronize()
         return float(self.grads[self.P + 1]), sout
+
+    def dropout_masks(self, call_index):
+        """The multipliers training call ``call_index`` applies: ``L`` cell-input sites + the top output,
+        each ``[S, B, H]`` (time-major).  Lets a run with dropout be replayed on the CPU oracle."""
+        a = self.args
+        out = []
+        for site in range(a.num_layers + 1):
+            m = torch.empty((a.seq_length, a.batch_size, a.rnn_size), dtype=torch.float32, device=self.device)
+            check(self._lib.crnn_dropout_mask(self._h, call_index, site, ptr(m), None))
+            out.append(m.cpu().numpy())
+        torch.cuda.synchronize()
+        return out
 
     def forward(self, x, state=None, want_logits=True, want_probs=True):
         """``sess.run([logits, probs, final_state], feed)``: rows ordered ``b*S+t`` (``model.py:73``)."""

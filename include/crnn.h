@@ -71,6 +71,12 @@ typedef struct crnn_config {
     int32_t vocab_size;   /* V  (loader.vocab_size)                        train.py:85 */
     int32_t precision;    /* CRNN_PREC_*                                              */
     int32_t device;       /* CUDA device ordinal                                      */
+    /* DropoutWrapper / tf.nn.dropout of the training graph (model.py:31-34,58-59).  0 means 1.0
+     * (no dropout), so a config zero-filled past `device` behaves like the reference's defaults. */
+    float   input_keep_prob;   /* --input_keep_prob   train.py:60                      */
+    float   output_keep_prob;  /* --output_keep_prob  train.py:58                      */
+    int32_t dropout_seed;      /* masks = f(seed, training-call index, stage, element)  */
+    int32_t reserved;
 } crnn_config;
 
 typedef struct crnn_handle crnn_handle;
@@ -152,6 +158,13 @@ const char* crnn_profile_phase_name(int32_t phase);
  * events on the stream it is launched on (layers may run on concurrent internal streams).
  * ms_out[2] / launches_out[2]: summed kernel durations and launch counts, [0] forward, [1] BPTT. */
 int         crnn_profile_read_kernels(crnn_handle* h, double* ms_out, int64_t* launches_out, int32_t reset);
+
+/* The dropout multipliers (0 or 1/keep products) that training call number `call_index`
+ * (0-based count of crnn_forward_backward calls on this handle) applies at `site`:
+ * site l in [0,L) = input of cell l (cell 0: embedding mask x input mask; cell l: output mask of
+ * cell l-1 x input mask of cell l), site L = output of the top cell as seen by the projection.
+ * d_out: [S,B,H] floats, time-major.  For tests and for reproducing a run on the CPU.          */
+int crnn_dropout_mask(const crnn_handle* h, int64_t call_index, int32_t site, float* d_out, void* stream);
 
 /* ---- single operators (each is one slice of the graph; used by the parity tests) ---- */
 

@@ -133,7 +133,7 @@ def _cell_names(cfg, l):
     return (p + "basic_rnn_cell/kernel", p + "basic_rnn_cell/bias")
 
 
-def forward(cfg, params, x, state, dtype=np.float32, bf16_gemm=False, keep=False):
+def forward(cfg, params, x, state, dtype=np.float32, bf16_gemm=False, keep=False, masks=None):
     """Embedding + unrolled cells + logits (``model.py:54-77``).
 
     ``x``: ``[B, S]`` ids.  Returns ``(logits [B*S, V] rows ordered b*S+t, final_state,
@@ -146,7 +146,11 @@ def forward(cfg, params, x, state, dtype=np.float32, bf16_gemm=False, keep=False
     inp = [emb[x[:, t]] for t in range(S)]                       # model.py:55,62-63
     state = [tuple(s.astype(dtype) for s in st) for st in state]
     tape = {"x": x, "layers": []}
+    # masks (dropout, model.py:31-34,58-59): L arrays [S,B,H] multiplying what each cell reads (embedding or
+    # previous cell's output mask x the cell's input mask) and one for the top output as the projection sees it
     for l in range(L):
+        if masks is not None:
+            inp = [inp[t] * masks[l][t].astype(dtype) for t in range(S)]
         names = _cell_names(cfg, l)
         P = [params[n].astype(dtype) for n in names]
         rec = {"in": inp, "hprev": [], "g": []}
@@ -191,6 +195,8 @@ def forward(cfg, params, x, state, dtype=np.float32, bf16_gemm=False, keep=False
         tape["layers"].append(rec)
         inp = outs
     # model.py:73: concat(outputs, 1) -> [B, S*H] -> reshape [-1, H]: row = b*S + t
+    if masks is not None:
+        inp = [inp[t] * masks[L][t].astype(dtype) for t in range(S)]
     out = np.stack(inp, axis=1).reshape(B * S, H)
     logits = mm(out, params["rnnlm/softmax_w"].astype(dtype)) + params["rnnlm/softmax_b"].astype(dtype)
     tape["out"] = out
@@ -215,7 +221,7 @@ def loss_from_logits(logits, y):
     return xent.sum() / logits.dtype.type(n), xent
 
 
-def forward_backward(cfg, params, x, y, state, dtype=np.float32, bf16_gemm=False):
+def forward_backward(cfg, params, x, y, state, dtype=np.float32, bf16_gemm=False, masks=None):
     """One ``tf.gradients(cost, tvars)`` evaluation (``model.py:80-91``).
 
     Returns a dict with ``loss``, ``grads`` (dense, keyed like ``params``; the
@@ -228,7 +234,7 @@ def forward_backward(cfg, params, x, y, state, dtype=np.float32, bf16_gemm=False
     B, S = x.shape
     H, L, V = cfg.rnn_size, cfg.num_layers, cfg.vocab_size
     one = dtype(1.0)
-    logits, final_state, tape = forward(cfg, params, x, state, dtype, bf16_gemm, keep=True)
+    logits, final_state, tape = forward(cfg, params, x, state, dtype, bf16_gemm, keep=True, masks=masks)
     loss, _ = loss_from_logits(logits, y)
     n = B * S
     dlogits = softmax(logits)
@@ -240,6 +246,8 @@ def forward_backward(cfg, params, x, y, state, dtype=np.float32, bf16_gemm=False
     grads["rnnlm/softmax_b"] = dlogits.sum(axis=0)
     dout = mm(dlogits, Wsm.T).reshape(B, S, H)
     dys = [dout[:, t, :] for t in range(S)]
+    if masks is not None:
+        dys = [dys[t] * masks[L][t].astype(dtype) for t in range(S)]
     for l in reversed(range(L)):
         rec = tape["layers"][l]
         names = _cell_names(cfg, l)
@@ -300,6 +308,8 @@ def forward_backward(cfg, params, x, y, state, dtype=np.float32, bf16_gemm=False
                 dxh = mm(dz, W.T)
                 dxs[t], dh = dxh[:, :H], dxh[:, H:]
             grads[names[0]], grads[names[1]] = dW, db
+        if masks is not None:
+            dxs = [dxs[t] * masks[l][t].astype(dtype) for t in range(S)]
         dys = dxs
     dX = np.stack(dys, axis=1)                                   # [B, S, H] = IndexedSlices.values
     dE = np.zeros((V, H), dtype)
@@ -373,13 +383,13 @@ class Trainer(object):
         self.lr = np.float32(self.learning_rate) * np.float32(self.decay_rate) ** np.float32(e)
         self.state = zero_state(self.cfg, self.dtype)
 
-    def step(self, x, y, world=None):
-        """One ``session.run([cost, final_state, train_op])``.
+    def step(self, x, y, world=None, masks=None):
+        """One ``session.run([cost, final_state, train_op])``.  ``masks``: this step's dropout multipliers.
 
         ``world``: optional list of ``(x_r, y_r, state_r)`` for the N-rank contract
          — not used for single-process runs.
         """
-        fb = forward_backward(self.cfg, self.params, x, y, self.state, self.dtype, self.bf16)
+        fb = forward_backward(self.cfg, self.params, x, y, self.state, self.dtype, self.bf16, masks=masks)
         gn = global_norm(self.cfg, fb)
         scale = clip_scale(gn, self.cfg.grad_clip, self.dtype)
         grads = {k: g * scale for k, g in fb["grads"].items()}

@@ -135,7 +135,7 @@ def test_init_from_asserts_match_reference_messages(tmp_path):
         train.check_init_from(a, argparse.Namespace(chars=("a",), vocab={"a": 0}))
 
 
-def test_nas_and_dropout_are_rejected_explicitly():
+def test_nas_and_bad_keep_prob_are_rejected_explicitly():
     torch = pytest.importorskip("torch")
     from distributed_char_rnn_b200.model import Model
     ns = argparse.Namespace(model="nas", rnn_size=8, num_layers=1, seq_length=2, batch_size=2, vocab_size=5, grad_clip=5.0)
@@ -145,6 +145,6 @@ def test_nas_and_dropout_are_rejected_explicitly():
     with pytest.raises(Exception, match="model type not supported: bogus"):       # model.py:25
         Model(ns)
     ns = argparse.Namespace(model="lstm", rnn_size=8, num_layers=1, seq_length=2, batch_size=2, vocab_size=5,
-                            grad_clip=5.0, output_keep_prob=0.5, input_keep_prob=1.0)
-    with pytest.raises(Exception, match="dropout"):
+                            grad_clip=5.0, output_keep_prob=0.0, input_keep_prob=1.0)
+    with pytest.raises(Exception, match="keep probabilities"):
         Model(ns)
