@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libcrnn.so")
 
 MODEL_IDS = {"rnn": 0, "gru": 1, "lstm": 2}
-PREC_IDS = {"fp32": 0, "bf16": 1}
+PREC_IDS = {"fp32": 0, "bf16": 1, "bf16x3": 2}
 GRAD_TAIL = 2
 NUM_PHASES = 12
 
@@ -53,6 +53,8 @@ SIGNATURES = {
     "crnn_softmax_xent": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp]),
     "crnn_gemm_bf16": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
                                c_i32, c_vp]),
+    "crnn_gemm_bf16x3": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp,
+                                 c_i32, c_vp]),
     "crnn_gemm_f32": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
                               c_i32, c_vp]),
 }

@@ -37,6 +37,16 @@ __host__ __device__ __forceinline__ int64_t ceil_div64(int64_t a, int64_t b) { r
 __host__ __device__ __forceinline__ int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ __forceinline__ int64_t round_up64(int64_t a, int64_t b) { return ceil_div64(a, b) * b; }
 
+// Split-bf16 operands (CRNN_PREC_BF16X3): a float is carried as hi = bf16(v) and lo = bf16(v - hi), 16
+// significand bits together; a product keeps hi*hi + lo*hi + hi*lo (the dropped lo*lo term is ~2^-18
+// relative), so tensor-core contractions land within ~1e-5 of fp32.  `lo_ofs` is the element offset of
+// the lo twin from the hi array (0: plain bf16, no twin).
+__device__ __forceinline__ void store_bf16_split(__nv_bfloat16* __restrict__ p, int64_t lo_ofs, float v) {
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    p[0] = hi;
+    if (lo_ofs) p[lo_ofs] = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
 // fp32-accurate activations for the parity mode (no fast-math approximations).
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 __device__ __forceinline__ float tanh_acc(float x) { return tanhf(x); }

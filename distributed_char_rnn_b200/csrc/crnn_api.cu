@@ -56,6 +56,7 @@ struct WsPlan {
 struct RecPlanTc {
     int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
     int q_fwd, q_bwd;       // K parts per unit group (cluster size) of the forward / backward kernel
+    int ring_fwd, ring_bwd; // TMA ring bytes
     size_t smem_fwd, smem_bwd;
 };
 
@@ -81,6 +82,8 @@ struct crnn_handle {
     // dropout (training calls only): keep probabilities, seed, and the count of training calls so far
     float ikp, okp;
     bool drop_on;
+    bool tc;              // tensor-core path (CRNN_PREC_BF16 or CRNN_PREC_BF16X3)
+    int split;            // 1: CRNN_PREC_BF16X3, every bf16 operand array is followed by its lo twin
     long long fb_calls;
     long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
@@ -204,7 +207,7 @@ static int plan_recurrence(const crnn_handle* h, bool backward, RecPlan* out) {
 // fit in shared memory; one CTA per SM, all co-resident.
 static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out) {
     const int H = h->cfg.rnn_size, B = h->cfg.batch_size, model = h->cfg.model;
-    if (H % 16 != 0) return set_err(CRNN_ERR_UNSUP, "CRNN_PREC_BF16 needs rnn_size %% 16 == 0 (got %d)", H);
+    if (H % 16 != 0) return set_err(CRNN_ERR_UNSUP, "the tensor-core precisions need rnn_size %% 16 == 0 (got %d)", H);
     const int g1 = model == CRNN_MODEL_LSTM ? 4 : (model == CRNN_MODEL_GRU ? 2 : 1);
     const int nkb = ceil_div(H, 64);
     const int hc_env = env_int("CRNN_TC_HC", 0), nt_env = env_int("CRNN_TC_TILES", 0);
@@ -232,11 +235,13 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         // (large H: the issue rate of small-N MMAs, not the tensor pipe, bounds the step).  Same resident
         // bytes per CTA; N grows Q-fold, the K extent and the streamed rows shrink Q-fold; the partial sums
         // are exchanged through distributed shared memory, whose staging area grows with N.
-        const size_t wbytes = (size_t)nkb * g1 * HC * 128 + (model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0);
+        const size_t wbytes = ((size_t)nkb * g1 * HC * 128 + (model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0)) * (size_t)(1 + h->split);
         auto pick_q = [&](int ncols_per_unit, int env) -> int {
             for (int Qc = 4; Qc >= 2; Qc >>= 1) {
                 if (env > 0 && Qc != env) continue;
-                if (env == 0 && (nkb < 16 || ncols_per_unit * HC * Qc > 128)) continue;      // only long K, keep N <= 128
+                // only long K, keep N <= 128.  Split operands stream twice the bytes per K block through a ring that
+                // holds two stages of them, so the K split pays from K = 512 on (config 3: 8.05 -> 6.70 ms per step)
+                if (env == 0 && (nkb < (h->split ? 8 : 16) || ncols_per_unit * HC * Qc > 128)) continue;
                 // measured (B200): Q = 4 pays (config 4 BPTT 9.9 -> 5.9 ms); Q = 2 pays only when one column per
                 // unit is exchanged (config 5: 26.3 -> 23.9 ms per direction) and loses for the LSTM forward
                 // pass, which gathers four (config 4: 4.6 -> 6.0 ms)
@@ -253,9 +258,22 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         o->q_bwd = q_env == 0 || q_env == 1 ? 1 : pick_q(1, std::max(q_env, 0));
         o->zs_fwd = rows * (g1 * HC * o->q_fwd + 1);
         o->zs_bwd = rows * (HC * o->q_bwd + 1);
+        o->ring_fwd = o->ring_bwd = tc::RT_RING_BYTES;
         o->smem_fwd = tc::rt_smem_bytes(wbytes, 0, o->zs_fwd);
         o->smem_bwd = tc::rt_smem_bytes(wbytes, 0, o->zs_bwd);
-        return (int)std::max(o->smem_fwd, o->smem_bwd) <= h->max_smem;
+        if ((int)std::max(o->smem_fwd, o->smem_bwd) > h->max_smem) return false;
+        // A larger ring (CRNN_TC_RING_KB) is possible where shared memory is left, but measured on B200 it buys
+        // nothing: config 3 at 64 / 96 / 128 KB: 4.20 / 4.22 / 4.22 ms (bf16), 6.69 / 6.85 / 6.86 ms (split) - the
+        // stream is bound by the rate L2 serves the same rows to every slice of a tile, not by stages in flight.
+        const int ring_cap = env_int("CRNN_TC_RING_KB", 64) * 1024;
+        auto grow = [&](size_t* smem, int* ring) {
+            const int spare = ((h->max_smem - (int)*smem) / 1024) * 1024;
+            const int add = std::max(0, std::min(spare, ring_cap - *ring));
+            *ring += add; *smem += (size_t)add;
+        };
+        grow(&o->smem_fwd, &o->ring_fwd);
+        grow(&o->smem_bwd, &o->ring_bwd);
+        return true;
     };
     // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
     // while that leaves SMs idle: every SM should hold a (slice, tile) pair.
@@ -268,7 +286,8 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         if (best == 0 || cand.nslices * cand.ntiles > out->nslices * out->ntiles) { best = HC; *out = cand; }
         if (hc_env >= 16 || cand.nslices * cand.ntiles >= (max_ctas * 3) / 4) break;
     }
-    if (best == 0) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory", H);
+    if (best == 0) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory%s", H,
+                                  h->split ? " with split operands (use CRNN_PREC_BF16 or CRNN_PREC_FP32)" : "");
     return CRNN_OK;
 }
 
@@ -322,10 +341,11 @@ static void build_workspace(crnn_handle* h) {
     w.carry0 = fp32_path ? take(B * H) : 0;
     w.carry1 = fp32_path ? take(B * H) : 0;
     w.logits = take(S * B * V);
-    auto take2 = [&](int64_t halves) { return take((halves + 1) / 2); };
+    const int64_t nsp = 1 + h->split;                 // bf16 operand arrays: hi (+ lo twin right behind it)
+    auto take2 = [&](int64_t halves) { return take((halves * nsp + 1) / 2); };
     w.topd = w.topdb = 0;
     if (h->drop_on) {
-        const bool bf = h->cfg.precision == CRNN_PREC_BF16;
+        const bool bf = h->tc;
         for (int l = 0; l < L; ++l) {
             w.xin.push_back(take(S * B * H));
             w.xinb.push_back(bf ? take2(S * B * H) : 0);
@@ -333,7 +353,7 @@ static void build_workspace(crnn_handle* h) {
         w.topd = take(S * B * H);
         w.topdb = bf ? take2(S * B * H) : 0;
     }
-    if (h->cfg.precision == CRNN_PREC_BF16) {
+    if (h->tc) {
         const int64_t GW = h->G;
         w.pbf = take2(h->P);
         w.wsmb = take2(H * h->Vp);
@@ -370,7 +390,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         return set_err(CRNN_ERR_ARG, "rnn_size, num_layers, seq_length, batch_size and vocab_size must be >= 1");
     if (cfg->input_keep_prob < 0.f || cfg->input_keep_prob > 1.f || cfg->output_keep_prob < 0.f || cfg->output_keep_prob > 1.f)
         return set_err(CRNN_ERR_ARG, "keep probabilities must be in (0, 1] (0 = unset = 1.0)");
-    if (cfg->precision != CRNN_PREC_FP32 && cfg->precision != CRNN_PREC_BF16)
+    if (cfg->precision != CRNN_PREC_FP32 && cfg->precision != CRNN_PREC_BF16 && cfg->precision != CRNN_PREC_BF16X3)
         return set_err(CRNN_ERR_ARG, "unknown precision %d", cfg->precision);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -390,6 +410,8 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->GS = cfg->model == CRNN_MODEL_RNN ? 1 : 4;     // lstm: i,j,f,o   gru: r,u,cand,r*h
     h->GZ = h->G;
     h->nstate = cfg->model == CRNN_MODEL_LSTM ? 2 : 1;
+    h->tc = cfg->precision != CRNN_PREC_FP32;
+    h->split = cfg->precision == CRNN_PREC_BF16X3 ? 1 : 0;
     h->sm_count = prop.multiProcessorCount;
     h->max_smem = (int)prop.sharedMemPerBlockOptin;
     h->pow_step = 0; h->b1p = 1.0f; h->b2p = 1.0f;
@@ -400,13 +422,13 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     int rc = plan_recurrence(h, false, &h->fwd);
     if (rc == CRNN_OK) rc = plan_recurrence(h, true, &h->bwd);
     h->Vp = (cfg->vocab_size + 7) & ~7;
-    h->fast_act = env_int("CRNN_FAST_ACT", 1);
+    h->fast_act = h->split ? 0 : env_int("CRNN_FAST_ACT", 1);   // MUFU.TANH (5e-4) has no place in the fp32-grade mode
     h->ikp = (cfg->input_keep_prob > 0.f && cfg->input_keep_prob < 1.f) ? cfg->input_keep_prob : 1.0f;
     h->okp = (cfg->output_keep_prob > 0.f && cfg->output_keep_prob < 1.f) ? cfg->output_keep_prob : 1.0f;
     h->drop_on = h->ikp < 1.0f || h->okp < 1.0f;
     h->fb_calls = 0;
     h->wf_W = 1; h->wf_C = 1;
-    if (rc == CRNN_OK && cfg->precision == CRNN_PREC_BF16) {
+    if (rc == CRNN_OK && h->tc) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
         // 1/W of the SMs, the sequence cut into C chunks so layer l+1 starts when layer l has produced
         // the first chunk.  W = 1 is the plain sequential schedule.
@@ -419,7 +441,9 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         for (; W >= 1; --W) {
             // W > 1: leave a few SMs to the batch GEMMs that run beside the persistent recurrence kernels
             const int reserve = W > 1 ? env_int("CRNN_WF_RESERVE", 20) : 0;     // measured best on config 3 (0: 4.96, 20: 4.81, 36: 5.47 ms)
-            rc = plan_recurrence_tc(h, (h->sm_count - reserve) / W, &h->tcp);
+            int ctas = (h->sm_count - reserve) / W;
+            { const int cap = env_int("CRNN_TC_MAXCTAS", 0); if (cap > 0) ctas = std::min(ctas, cap); }   // experiments only
+            rc = plan_recurrence_tc(h, ctas, &h->tcp);
             if (rc == CRNN_OK) break;
         }
         if (rc == CRNN_OK) {
@@ -571,10 +595,10 @@ static DropArgs drop_args(const crnn_handle* h, long long call, int site, int64_
 }
 // dst(/dst_b) = src * masks of `site` for elements [idx0, idx0+n) of the [S,B,H] tensor.
 static int drop_apply(const crnn_handle* h, long long call, int site, const float* src, float* dst, __nv_bfloat16* dst_b,
-                      int64_t idx0, int64_t n, cudaStream_t st) {
+                      int64_t idx0, int64_t n, cudaStream_t st, int64_t lo_ofs = 0) {
     if (n <= 0) return CRNN_OK;
     const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n, 256), (int64_t)h->sm_count * 8));
-    dropout_apply_kernel<<<(int)blocks, 256, 0, st>>>(src, dst, dst_b, n, drop_args(h, call, site, idx0));
+    dropout_apply_kernel<<<(int)blocks, 256, 0, st>>>(src, dst, dst_b, n, drop_args(h, call, site, idx0), lo_ofs);
     CRNN_LAUNCH_CHECK("dropout_apply_kernel");
     return CRNN_OK;
 }
@@ -679,13 +703,22 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.swap = backward ? p.swap_bwd : p.swap_fwd;
     a.m64 = (!a.swap && p.npass == 1 && p.BT <= 64 && env_int("CRNN_TC_M64", 1)) ? 1 : 0;
     a.dbg = (!backward && env_int("CRNN_TC_DEBUG", 0)) ? h->dbg_ptr : nullptr;
-    CUtensorMap t0, t1, w0, w1;
+    CUtensorMap t0, t1, w0, w1, t0l, t1l, w0l, w1l;
     int rc;
+    const int split = h->split;
+    a.split = split;
+    // lo twins sit right behind their hi arrays (build_workspace): element offsets
+    const int64_t lo_pbf = split ? h->P : 0;
+    const int64_t lo_wr = split ? (int64_t)p.nslices * GW * p.HC * H : 0;
+    a.hxb_lo = split ? (long long)(S + 1) * B * H : 0;
+    a.rsb_lo = split ? (long long)S * B * H : 0;
+    a.dzb_lo = split ? (long long)(S + 1) * B * GZ * H : 0;
     // ring geometry is per launch (every contraction of the kernel shares the ring and its barriers):
     // sized for the shortest K extent, H
-    a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64));
+    a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64), split);
     { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) a.ckb = std::min(ck_env, ceil_div(H, 64)); }
-    a.nst = tc::rt_num_stages(p.box_rows, a.ckb);
+    a.ring_bytes = backward ? p.ring_bwd : p.ring_fwd;
+    a.nst = tc::rt_num_stages(p.box_rows, a.ckb, split, a.ring_bytes);
     a.use3d = (H % 64 == 0 && env_int("CRNN_TC_3D", 1)) ? 1 : 0;
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
         if (a.use3d) return tc::make_tmap_bf16_kblocks(m, base, rows, cols, ld, p.box_rows, a.ckb);
@@ -696,15 +729,29 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1, a.rsb, (int64_t)S * B, H, H) : (t1 = t0, CRNN_OK);
         if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, wr, (int64_t)p.nslices * GW * p.HC, H, H, g1 * HCG);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, wr, (int64_t)p.nslices * GW * p.HC, H, H, HCG) : (w1 = w0, CRNN_OK);
+        t0l = t0; t1l = t1; w0l = w0; w1l = w1;
+        if (rc == CRNN_OK && split) {
+            rc = amap(&t0l, a.hxb + a.hxb_lo, (int64_t)(S + 1) * B, H, H);
+            if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1l, a.rsb + a.rsb_lo, (int64_t)S * B, H, H) : (t1l = t0l, CRNN_OK);
+            if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0l, wr + lo_wr, (int64_t)p.nslices * GW * p.HC, H, H, g1 * HCG);
+            if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1l, wr + lo_wr, (int64_t)p.nslices * GW * p.HC, H, H, HCG) : (w1l = w0l, CRNN_OK);
+        }
     } else {
         const int64_t zw = (int64_t)GZ * H;
         rc = amap(&t0, a.dzb, (int64_t)(S + 1) * B, (int64_t)g1 * H, zw);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1, a.dzb + 2 * H, (int64_t)(S + 1) * B, H, zw) : (t1 = t0, CRNN_OK);
         if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0, pbf_W, 2 * H, (int64_t)g1 * H, (int64_t)g1 * H, HCG);
         if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1, pbf_Wc, 2 * H, H, H, HCG) : (w1 = w0, CRNN_OK);
+        t0l = t0; t1l = t1; w0l = w0; w1l = w1;
+        if (rc == CRNN_OK && split) {
+            rc = amap(&t0l, a.dzb + a.dzb_lo, (int64_t)(S + 1) * B, (int64_t)g1 * H, zw);
+            if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? amap(&t1l, a.dzb + a.dzb_lo + 2 * H, (int64_t)(S + 1) * B, H, zw) : (t1l = t0l, CRNN_OK);
+            if (rc == CRNN_OK) rc = tc::make_tmap_bf16(&w0l, pbf_W + lo_pbf, 2 * H, (int64_t)g1 * H, (int64_t)g1 * H, HCG);
+            if (rc == CRNN_OK) rc = MODEL == CRNN_MODEL_GRU ? tc::make_tmap_bf16(&w1l, pbf_Wc + lo_pbf, 2 * H, H, H, HCG) : (w1l = w0l, CRNN_OK);
+        }
     }
     if (rc != CRNN_OK) return rc;
-    void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
+    void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
         h->fast_act ? (backward ? tc::rec_bwd_tc_kernel<MODEL, true> : tc::rec_fwd_tc_kernel<MODEL, true>)
                     : (backward ? tc::rec_bwd_tc_kernel<MODEL, false> : tc::rec_fwd_tc_kernel<MODEL, false>);
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
@@ -717,7 +764,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     int csize = 1;
     const int cmax = env_int("CRNN_TC_CLUSTER", 1);
     for (int cs = 16; cs >= 2; cs >>= 1)
-        if (cs <= cmax && p.nslices % cs == 0) { csize = cs; break; }
+        if (cs <= cmax && p.nslices % cs == 0 && !split) { csize = cs; break; }   // (multicast of split operands: not built)
     a.mcast = csize > 1 ? 1 : 0;
     a.cbar = 0;
     // Cluster barrier: when ALL slices of a batch tile fit in one cluster, the steps are ordered by remote
@@ -734,7 +781,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     if (Q > 1) { csize = Q; a.mcast = 0; a.cbar = 0; }     // the cluster is the K-split group
     if (csize > 8) CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     a.csize = csize;
-    void* args[] = {&t0, &t1, &w0, &w1, &a};
+    void* args[] = {&t0, &t1, &w0, &w1, &t0l, &t1l, &w0l, &w1l, &a};
     prof_kernel_mark(h, st, backward ? 1 : 0);
     if (csize == 1) {
         CRNN_CUDA(cudaLaunchCooperativeKernel((const void*)fn, dim3(p.nslices * p.ntiles), dim3(tc::RT_THREADS), args, smem, st));
@@ -771,9 +818,11 @@ static int launch_rec_tc_model(crnn_handle* h, bool backward, tc::RecTcArgs& a, 
 static int refresh_bf16_params(crnn_handle* h, const float* params, void* ws, cudaStream_t st) {
     const crnn_config& c = h->cfg;
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers;
-    tc::cast_bf16_kernel<<<grid_for(h->P, h->sm_count), 256, 0, st>>>(params, h->P, 1, (int)h->P, wsb(ws, h->ws.pbf), h->P);
+    const int64_t sp = h->split;                       // lo twins behind the hi arrays
+    tc::cast_bf16_kernel<<<grid_for(h->P, h->sm_count), 256, 0, st>>>(params, h->P, 1, (int)h->P, wsb(ws, h->ws.pbf), h->P, sp * h->P);
     CRNN_LAUNCH_CHECK("cast_bf16_kernel");
-    tc::cast_bf16_kernel<<<grid_for((int64_t)H * V, h->sm_count), 256, 0, st>>>(params + h->tensors[0].offset, V, H, V, wsb(ws, h->ws.wsmb), h->Vp);
+    tc::cast_bf16_kernel<<<grid_for((int64_t)H * V, h->sm_count), 256, 0, st>>>(params + h->tensors[0].offset, V, H, V, wsb(ws, h->ws.wsmb), h->Vp,
+                                                                                 sp * H * h->Vp);
     CRNN_LAUNCH_CHECK("cast_bf16_kernel");
     const int g1 = c.model == CRNN_MODEL_LSTM ? 4 : (c.model == CRNN_MODEL_GRU ? 2 : 1);
     for (int l = 0; l < L; ++l) {
@@ -783,7 +832,7 @@ static int refresh_bf16_params(crnn_handle* h, const float* params, void* ws, cu
         const int64_t n = (int64_t)h->tcp.nslices * h->G * h->tcp.HC * H;
         // one packed group per K-split cluster: q_fwd * HC units, nslices / q_fwd groups (same total size)
         tc::pack_rec_weights_kernel<<<grid_for(n, h->sm_count), 256, 0, st>>>(W, Wc, H, h->tcp.HC * h->tcp.q_fwd, h->tcp.nslices / h->tcp.q_fwd,
-                                                                              g1, h->G, H, wsb(ws, h->ws.wr[l]));
+                                                                              g1, h->G, H, wsb(ws, h->ws.wr[l]), sp * n);
         CRNN_LAUNCH_CHECK("pack_rec_weights_kernel");
     }
     return CRNN_OK;
@@ -847,6 +896,29 @@ static int wf_join(crnn_handle* h, cudaStream_t st, int slot) {
 }
 static inline int wf_t0(const crnn_handle* h, int c) { return (int)((int64_t)h->cfg.seq_length * c / h->wf_C); }
 
+// Element offsets of the lo twins (0 unless CRNN_PREC_BF16X3), and the GEMM call that passes them on.
+struct LoOfs {
+    int64_t act, hxb, pbf, wsm, dzb, dlb;
+};
+static LoOfs lo_offsets(const crnn_handle* h) {
+    const crnn_config& c = h->cfg;
+    const int64_t sp = h->split, S = c.seq_length, B = c.batch_size, H = c.rnn_size;
+    LoOfs o;
+    o.act = sp * S * B * H;
+    o.hxb = sp * (S + 1) * B * H;
+    o.pbf = sp * h->P;
+    o.wsm = sp * H * h->Vp;
+    o.dzb = sp * (S + 1) * B * h->GZ * H;
+    o.dlb = sp * S * B * h->Vp;
+    return o;
+}
+static int gemm_tc(const crnn_handle* h, int M, int N, int K, const bf16_t* A, int64_t lda, int a_mn, int64_t a_lo,
+                   const bf16_t* B, int64_t ldb, int b_mn, int64_t b_lo, float* C, int64_t ldc, const float* bias, int accumulate,
+                   cudaStream_t st) {
+    return tc::gemm_bf16_tc(M, N, K, A, lda, a_mn, B, ldb, b_mn, C, ldc, bias, accumulate, st, h->sm_count,
+                            h->split ? A + a_lo : nullptr, h->split ? B + b_lo : nullptr);
+}
+
 static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
                             const float* params, void* ws, cudaStream_t st, long long drop_call = -1) {
     const crnn_config& c = h->cfg;
@@ -866,7 +938,8 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     float* x0 = wsf(ws, h->ws.x0);
     bf16_t* x0b = wsb(ws, h->ws.x0b);
     prof_mark(h, st, CRNN_PHASE_EMBED_GATHER);
-    embed_gather_kernel<<<grid_for(SB * H / 4 + 1, sc), 256, 0, st>>>(params + h->emb_off, V, H, x, ldx, B, S, x0, x0b);
+    const LoOfs lo = lo_offsets(h);
+    embed_gather_kernel<<<grid_for(SB * H / 4 + 1, sc), 256, 0, st>>>(params + h->emb_off, V, H, x, ldx, B, S, x0, x0b, lo.act);
     CRNN_LAUNCH_CHECK("embed_gather_kernel");
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 512 * 256, st));
@@ -883,12 +956,13 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         float* gates = wsf(ws, h->ws.gates[l]);
         bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
         const bf16_t* inb = drop ? wsb(ws, h->ws.xinb[l]) : (l == 0 ? x0b : wsb(ws, h->ws.hxb[l - 1]) + BH);
+        const int64_t in_lo = (drop || l == 0) ? lo.act : lo.hxb;
         const float* in32 = l == 0 ? x0 : wsf(ws, h->ws.hx[l - 1]) + BH;      // dropout masks the fp32 source
         const float* sin = state_in + (int64_t)l * h->nstate * BH;
         const float* hin = c.model == CRNN_MODEL_LSTM ? sin + BH : sin;
         if (c.model == CRNN_MODEL_LSTM) CRNN_CUDA(cudaMemcpyAsync(cx, sin, BH * 4, cudaMemcpyDeviceToDevice, s));
         CRNN_CUDA(cudaMemcpyAsync(hx, hin, BH * 4, cudaMemcpyDeviceToDevice, s));
-        tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, s>>>(hin, H, B, H, hxb, H);
+        tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, s>>>(hin, H, B, H, hxb, H, lo.hxb);
         CRNN_LAUNCH_CHECK("cast_bf16_kernel");
         cudaStream_t gs = wf_gstream(h, st, l);
         for (int ck = 0; ck < C; ++ck) {
@@ -900,7 +974,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             }
             if (drop) {                              // masked bf16 copy of this chunk's inputs
                 rc = drop_apply(h, drop_call, l, in32 + (int64_t)t0 * BH, nullptr, wsb(ws, h->ws.xinb[l]) + (int64_t)t0 * BH,
-                                (int64_t)t0 * BH, (int64_t)rows * H, gs);
+                                (int64_t)t0 * BH, (int64_t)rows * H, gs, lo.act);
                 if (rc != CRNN_OK) return rc;
             }
             if (!wf) prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
@@ -908,11 +982,11 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             const bf16_t* ain = inb + (int64_t)t0 * BH;
             float* gch = gates + (int64_t)t0 * B * gw;
             if (c.model == CRNN_MODEL_GRU) {
-                rc = tc::gemm_bf16_tc(rows, 2 * H, H, ain, H, 0, pbf + lp.oW, 2 * H, 1, gch, gw, lp.b, 0, gs, sc);
-                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, ain, H, 0, pbf + lp.oWc, H, 1, gch + 2 * H, gw, lp.bc, 0, gs, sc);
+                rc = gemm_tc(h, rows, 2 * H, H, ain, H, 0, in_lo, pbf + lp.oW, 2 * H, 1, lo.pbf, gch, gw, lp.b, 0, gs);
+                if (rc == CRNN_OK) rc = gemm_tc(h, rows, H, H, ain, H, 0, in_lo, pbf + lp.oWc, H, 1, lo.pbf, gch + 2 * H, gw, lp.bc, 0, gs);
             } else {
                 const int GH = h->G * H;
-                rc = tc::gemm_bf16_tc(rows, GH, H, ain, H, 0, pbf + lp.oW, GH, 1, gch, gw, lp.b, 0, gs, sc);
+                rc = gemm_tc(h, rows, GH, H, ain, H, 0, in_lo, pbf + lp.oW, GH, 1, lo.pbf, gch, gw, lp.b, 0, gs);
             }
             if (rc != CRNN_OK) return rc;
             if (wf) {
@@ -946,13 +1020,13 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     if (rc != CRNN_OK) return rc;
     const bf16_t* topb = wsb(ws, h->ws.hxb[L - 1]) + BH;
     if (drop) {
-        rc = drop_apply(h, drop_call, L, wsf(ws, h->ws.hx[L - 1]) + BH, nullptr, wsb(ws, h->ws.topdb), 0, SB * H, st);
+        rc = drop_apply(h, drop_call, L, wsf(ws, h->ws.hx[L - 1]) + BH, nullptr, wsb(ws, h->ws.topdb), 0, SB * H, st, lo.act);
         if (rc != CRNN_OK) return rc;
         topb = wsb(ws, h->ws.topdb);
     }
     prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
-    rc = tc::gemm_bf16_tc((int)SB, V, H, topb, H, 0, wsb(ws, h->ws.wsmb), h->Vp, 1, wsf(ws, h->ws.logits), V,
-                          params + h->tensors[1].offset, 0, st, sc);
+    rc = gemm_tc(h, (int)SB, V, H, topb, H, 0, drop ? lo.act : lo.hxb, wsb(ws, h->ws.wsmb), h->Vp, 1, lo.wsm, wsf(ws, h->ws.logits), V,
+                 params + h->tensors[1].offset, 0, st);
     prof_mark(h, st, CRNN_PHASE_MISC);
     return rc;
 }
@@ -976,14 +1050,16 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     float* logits = wsf(ws, h->ws.logits);
     bf16_t* dlb = wsb(ws, h->ws.dlb);
     prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
-    softmax_xent_kernel<<<grid_for(SB * 32, sc), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp);
+    const LoOfs lo = lo_offsets(h);
+    const int64_t top_lo = drop ? lo.act : lo.hxb;
+    softmax_xent_kernel<<<grid_for(SB * 32, sc), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp, lo.dlb);
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
     const bf16_t* topb = drop ? wsb(ws, h->ws.topdb) : wsb(ws, h->ws.hxb[L - 1]) + BH;
     prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
     // d softmax_w [H,V] = out^T * dlogits ; d softmax_b = colsum ; d out = dlogits * softmax_w^T
-    rc = tc::gemm_bf16_tc(H, V, (int)SB, topb, H, 1, dlb, Vp, 1, grads + h->tensors[0].offset, V, nullptr, 1, st, sc);
+    rc = gemm_tc(h, H, V, (int)SB, topb, H, 1, top_lo, dlb, Vp, 1, lo.dlb, grads + h->tensors[0].offset, V, nullptr, 1, st);
     if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
-    if (rc == CRNN_OK) rc = tc::gemm_bf16_tc((int)SB, H, V, dlb, Vp, 0, wsb(ws, h->ws.wsmb), Vp, 0, wsf(ws, h->ws.gout[L - 1]), H, nullptr, 0, st, sc);
+    if (rc == CRNN_OK) rc = gemm_tc(h, (int)SB, H, V, dlb, Vp, 0, lo.dlb, wsb(ws, h->ws.wsmb), Vp, 0, lo.wsm, wsf(ws, h->ws.gout[L - 1]), H, nullptr, 0, st);
     if (rc == CRNN_OK && drop) rc = drop_apply(h, call, L, wsf(ws, h->ws.gout[L - 1]), wsf(ws, h->ws.gout[L - 1]), nullptr, 0, SB * H, st);
     if (rc != CRNN_OK) return rc;
 
@@ -1001,6 +1077,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         float* gates = wsf(ws, h->ws.gates[l]);
         const bf16_t* hxb = wsb(ws, h->ws.hxb[l]);
         const bf16_t* inb = drop ? wsb(ws, h->ws.xinb[l]) : (l == 0 ? wsb(ws, h->ws.x0b) : wsb(ws, h->ws.hxb[l - 1]) + BH);
+        const int64_t in_lo = (drop || l == 0) ? lo.act : lo.hxb;
         float* dz = wsf(ws, h->ws.dzv[l]);
         bf16_t* dzb = wsb(ws, h->ws.dzbv[l]);
         float* dnext = l > 0 ? wsf(ws, h->ws.gout[l - 1]) : wsf(ws, h->ws.gx0);
@@ -1031,11 +1108,11 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             const bf16_t* dzc = dzb + (int64_t)t0 * B * zw;
             float* dn = dnext + (int64_t)t0 * BH;
             if (c.model == CRNN_MODEL_GRU) {
-                rc = tc::gemm_bf16_tc(rows, H, 2 * H, dzc, zw, 0, pbf + lp.oW, 2 * H, 0, dn, H, nullptr, 0, gs, sc);
-                if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(rows, H, H, dzc + 2 * H, zw, 0, pbf + lp.oWc, H, 0, dn, H, nullptr, 1, gs, sc);
+                rc = gemm_tc(h, rows, H, 2 * H, dzc, zw, 0, lo.dzb, pbf + lp.oW, 2 * H, 0, lo.pbf, dn, H, nullptr, 0, gs);
+                if (rc == CRNN_OK) rc = gemm_tc(h, rows, H, H, dzc + 2 * H, zw, 0, lo.dzb, pbf + lp.oWc, H, 0, lo.pbf, dn, H, nullptr, 1, gs);
             } else {
                 const int GH = h->G * H;
-                rc = tc::gemm_bf16_tc(rows, H, GH, dzc, zw, 0, pbf + lp.oW, GH, 0, dn, H, nullptr, 0, gs, sc);
+                rc = gemm_tc(h, rows, H, GH, dzc, zw, 0, lo.dzb, pbf + lp.oW, GH, 0, lo.pbf, dn, H, nullptr, 0, gs);
             }
             if (rc == CRNN_OK && drop) rc = drop_apply(h, call, l, dn, dn, nullptr, (int64_t)t0 * BH, (int64_t)rows * H, gs);
             if (rc != CRNN_OK) return rc;
@@ -1052,16 +1129,16 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             float* gWc = grads + lp.oWc;
             float* gbc = grads + lp.obc;
             const bf16_t* rsb = wsb(ws, h->ws.rsb[l]);
-            rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, inb, H, 1, dzb, zw, 1, gW, 2 * H, nullptr, 1, s, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, 2 * H, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, s, sc);
+            rc = gemm_tc(h, H, 2 * H, (int)SB, inb, H, 1, in_lo, dzb, zw, 1, lo.dzb, gW, 2 * H, nullptr, 1, s);
+            if (rc == CRNN_OK) rc = gemm_tc(h, H, 2 * H, (int)SB, hxb, H, 1, lo.hxb, dzb, zw, 1, lo.dzb, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, s);
             if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, s);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, inb, H, 1, dzb + 2 * H, zw, 1, gWc, H, nullptr, 1, s, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, H, (int)SB, rsb, H, 1, dzb + 2 * H, zw, 1, gWc + (int64_t)H * H, H, nullptr, 1, s, sc);
+            if (rc == CRNN_OK) rc = gemm_tc(h, H, H, (int)SB, inb, H, 1, in_lo, dzb + 2 * H, zw, 1, lo.dzb, gWc, H, nullptr, 1, s);
+            if (rc == CRNN_OK) rc = gemm_tc(h, H, H, (int)SB, rsb, H, 1, lo.act, dzb + 2 * H, zw, 1, lo.dzb, gWc + (int64_t)H * H, H, nullptr, 1, s);
             if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, s);
         } else {
             const int GH = h->G * H;
-            rc = tc::gemm_bf16_tc(H, GH, (int)SB, inb, H, 1, dzb, zw, 1, gW, GH, nullptr, 1, s, sc);
-            if (rc == CRNN_OK) rc = tc::gemm_bf16_tc(H, GH, (int)SB, hxb, H, 1, dzb, zw, 1, gW + (int64_t)H * GH, GH, nullptr, 1, s, sc);
+            rc = gemm_tc(h, H, GH, (int)SB, inb, H, 1, in_lo, dzb, zw, 1, lo.dzb, gW, GH, nullptr, 1, s);
+            if (rc == CRNN_OK) rc = gemm_tc(h, H, GH, (int)SB, hxb, H, 1, lo.hxb, dzb, zw, 1, lo.dzb, gW + (int64_t)H * GH, GH, nullptr, 1, s);
             if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, s);
         }
         if (rc != CRNN_OK) return rc;
@@ -1099,7 +1176,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     cudaStream_t st = (cudaStream_t)stream;
     const long long call = h->fb_calls++;               // index of this training call (dropout masks)
     const bool drop = h->drop_on;
-    if (c.precision == CRNN_PREC_BF16) return forward_backward_bf16(h, x, y, ld, state_in, state_out, params, grads, ws, st, call);
+    if (h->tc) return forward_backward_bf16(h, x, y, ld, state_in, state_out, params, grads, ws, st, call);
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H, zw = h->GZ * H;
@@ -1277,7 +1354,7 @@ int crnn_forward(crnn_handle* h, const int32_t* x, int64_t ld, const float* stat
     if (ld < c.seq_length) return set_err(CRNN_ERR_ARG, "ld_x %lld < seq_length %d", (long long)ld, c.seq_length);
     cudaStream_t st = (cudaStream_t)stream;
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
-    rc = c.precision == CRNN_PREC_BF16 ? run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st)
+    rc = h->tc ? run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st)
                                        : run_forward(h, x, ld, state_in, state_out, params, ws, st);
     if (rc != CRNN_OK) return rc;
     if (logits_out || probs_out) {
@@ -1340,6 +1417,15 @@ int crnn_gemm_bf16(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K, 
     if (M < 0 || N < 0 || K < 1) return set_err(CRNN_ERR_ARG, "bad shape");
     return tc::gemm_bf16_tc(M, N, K, (const __nv_bfloat16*)A, lda, a_mn, (const __nv_bfloat16*)B, ldb, b_mn, C, ldc, bias,
                             accumulate, (cudaStream_t)stream);
+}
+
+int crnn_gemm_bf16x3(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K, const void* A_hi, const void* A_lo, int64_t lda,
+                     const void* B_hi, const void* B_lo, int64_t ldb, float* C, int64_t ldc, const float* bias, int32_t accumulate,
+                     void* stream) {
+    if (!A_hi || !A_lo || !B_hi || !B_lo || !C) return set_err(CRNN_ERR_ARG, "null device pointer");
+    if (M < 0 || N < 0 || K < 1) return set_err(CRNN_ERR_ARG, "bad shape");
+    return tc::gemm_bf16_tc(M, N, K, (const __nv_bfloat16*)A_hi, lda, a_mn, (const __nv_bfloat16*)B_hi, ldb, b_mn, C, ldc, bias,
+                            accumulate, (cudaStream_t)stream, 148, (const __nv_bfloat16*)A_lo, (const __nv_bfloat16*)B_lo);
 }
 
 }  // extern "C"

@@ -10,7 +10,7 @@ namespace crnn {
 __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restrict__ table, int V, int H,
                                                            const int32_t* __restrict__ x, int64_t ldx,
                                                            int B, int S, float* __restrict__ out,
-                                                           __nv_bfloat16* __restrict__ out_bf16) {
+                                                           __nv_bfloat16* __restrict__ out_bf16, int64_t lo_ofs = 0) {
     const int64_t n = (int64_t)S * B * H;
     const bool vec = (H & 3) == 0;
     if (vec) {
@@ -25,8 +25,14 @@ __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restri
             float4 v = __ldg(reinterpret_cast<const float4*>(table + (int64_t)id * H) + c);
             reinterpret_cast<float4*>(out)[i] = v;
             if (out_bf16) {
-                reinterpret_cast<__nv_bfloat162*>(out_bf16)[2 * i] = __floats2bfloat162_rn(v.x, v.y);
-                reinterpret_cast<__nv_bfloat162*>(out_bf16)[2 * i + 1] = __floats2bfloat162_rn(v.z, v.w);
+                const __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+                reinterpret_cast<__nv_bfloat162*>(out_bf16)[2 * i] = h0;
+                reinterpret_cast<__nv_bfloat162*>(out_bf16)[2 * i + 1] = h1;
+                if (lo_ofs) {                       // lo_ofs is a multiple of 4: the twin keeps the 8-byte alignment
+                    const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+                    reinterpret_cast<__nv_bfloat162*>(out_bf16 + lo_ofs)[2 * i] = __floats2bfloat162_rn(v.x - f0.x, v.y - f0.y);
+                    reinterpret_cast<__nv_bfloat162*>(out_bf16 + lo_ofs)[2 * i + 1] = __floats2bfloat162_rn(v.z - f1.x, v.w - f1.y);
+                }
             }
         }
     } else {
@@ -37,7 +43,7 @@ __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restri
             int id = __ldg(x + (int64_t)b * ldx + t);
             id = min(max(id, 0), V - 1);
             out[i] = __ldg(table + (int64_t)id * H + c);
-            if (out_bf16) out_bf16[i] = __float2bfloat16_rn(out[i]);
+            if (out_bf16) store_bf16_split(out_bf16 + i, lo_ofs, out[i]);
         }
     }
 }
@@ -86,12 +92,13 @@ struct DropArgs {
 
 // dst = src * mask_a * mask_b (dst may equal src); optional bf16 copy.
 __global__ void __launch_bounds__(256) dropout_apply_kernel(const float* __restrict__ src, float* __restrict__ dst,
-                                                            __nv_bfloat16* __restrict__ dst_bf16, int64_t n, DropArgs d) {
+                                                            __nv_bfloat16* __restrict__ dst_bf16, int64_t n, DropArgs d,
+                                                            int64_t lo_ofs = 0) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const uint64_t gi = (uint64_t)(d.idx0 + i);
         const float v = (src ? src[i] : 1.0f) * dropout_mult(d.seed, d.stage_a, gi, d.keep_a) * dropout_mult(d.seed, d.stage_b, gi, d.keep_b);
         if (dst) dst[i] = v;
-        if (dst_bf16) dst_bf16[i] = __float2bfloat16_rn(v);
+        if (dst_bf16) store_bf16_split(dst_bf16 + i, lo_ofs, v);
     }
 }
 
@@ -100,7 +107,8 @@ __global__ void __launch_bounds__(256) dropout_apply_kernel(const float* __restr
 __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ logits, int B, int S, int V,
                                                            const int32_t* __restrict__ y, int64_t ldy,
                                                            double* __restrict__ loss_sum,
-                                                           __nv_bfloat16* __restrict__ dl_bf16, int64_t ld_bf16) {
+                                                           __nv_bfloat16* __restrict__ dl_bf16, int64_t ld_bf16,
+                                                           int64_t lo_ofs = 0) {
     __shared__ double sh[32];
     const int lane = threadIdx.x & 31;
     const int64_t N = (int64_t)B * S;
@@ -125,7 +133,7 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ l
             float p = expf(v - m) * inv;
             const float d = (p - (c == label ? 1.0f : 0.0f)) * invN;
             z[c] = d;
-            if (dl_bf16) dl_bf16[row * ld_bf16 + c] = __float2bfloat16_rn(d);
+            if (dl_bf16) store_bf16_split(dl_bf16 + row * ld_bf16 + c, lo_ofs, d);
         }
         zl = warp_sum(zl);
         if (lane == 0) local += (double)(lse - zl);

@@ -34,21 +34,26 @@ struct GemmTcArgs {
     int a_mn, b_mn;          // 1: operand is MN-major in global memory
 };
 
-template <int BN, int STAGES>
+// SPLIT: both operands come as (hi, lo) bf16 pairs (see store_bf16_split); a stage then holds
+// A_hi, B_hi, A_lo, B_lo and every K step issues hi*hi + lo*hi + hi*lo into the same accumulator.
+template <int BN, int STAGES, bool SPLIT>
 struct GemmTcSmem {
     static constexpr int A_BYTES = GT_BM * GT_BK * 2;       // 16 KB
     static constexpr int B_BYTES = BN * GT_BK * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int HALF_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGE_BYTES = HALF_BYTES * (SPLIT ? 2 : 1);
     static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
     static constexpr int TOTAL = BAR_OFF + 256 + 1024;       // + barriers/slot + alignment slack
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool SPLIT>
 __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
+                                                                  const __grid_constant__ CUtensorMap tmAl,
+                                                                  const __grid_constant__ CUtensorMap tmBl,
                                                                   const __grid_constant__ CUtensorMap tmC,
                                                                   GemmTcArgs g) {
-    using L = GemmTcSmem<BN, STAGES>;
+    using L = GemmTcSmem<BN, STAGES, SPLIT>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
@@ -86,17 +91,24 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
                 uint8_t* sb = sa + L::A_BYTES;
                 mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
                 const int k0 = (kb0 + i) * GT_BK;
-                if (!g.a_mn) {
-                    tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
-                } else {
 #pragma unroll
-                    for (int j = 0; j < GT_BM / 64; ++j) tma_load_2d(sa + j * 8192, &tmA, &full_bar[s], m0 + 64 * j, k0);
-                }
-                if (!g.b_mn) {
-                    tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);
-                } else {
+                for (int half = 0; half < (SPLIT ? 2 : 1); ++half) {
+                    const CUtensorMap* ma = half ? &tmAl : &tmA;
+                    const CUtensorMap* mb = half ? &tmBl : &tmB;
+                    uint8_t* da = sa + half * L::HALF_BYTES;
+                    uint8_t* db = sb + half * L::HALF_BYTES;
+                    if (!g.a_mn) {
+                        tma_load_2d(da, ma, &full_bar[s], k0, m0);
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * 8192, &tmB, &full_bar[s], n0 + 64 * j, k0);
+                        for (int j = 0; j < GT_BM / 64; ++j) tma_load_2d(da + j * 8192, ma, &full_bar[s], m0 + 64 * j, k0);
+                    }
+                    if (!g.b_mn) {
+                        tma_load_2d(db, mb, &full_bar[s], k0, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) tma_load_2d(db + j * 8192, mb, &full_bar[s], n0 + 64 * j, k0);
+                    }
                 }
             }
         }
@@ -119,6 +131,13 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
                 mma_bf16(tmem_base, ad + as, bd + bs, idesc, 1u);
                 mma_bf16(tmem_base, ad + 2 * as, bd + 2 * bs, idesc, 1u);
                 mma_bf16(tmem_base, ad + 3 * as, bd + 3 * bs, idesc, 1u);
+                if (SPLIT) {                        // + lo(A)*hi(B) + hi(A)*lo(B); smallest terms could go first, fp32 adds make it moot
+                    const uint64_t lo = (uint64_t)(L::HALF_BYTES >> 4);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) mma_bf16(tmem_base, ad + lo + k * as, bd + k * bs, idesc, 1u);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) mma_bf16(tmem_base, ad + k * as, bd + lo + k * bs, idesc, 1u);
+                }
                 mma_commit(&empty_bar[s]);          // frees the smem slot once these MMAs retire
             }
             mma_commit(tmem_full);                  // accumulator complete
@@ -225,16 +244,25 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
 // stored [K,N] row-major.  accumulate = 1 adds into C (split-K with atomics when that fills the GPU).
 inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda, int a_mn,
                         const __nv_bfloat16* B, int64_t ldb, int b_mn, float* C, int64_t ldc,
-                        const float* bias, int accumulate, cudaStream_t st, int sm_count = 148) {
+                        const float* bias, int accumulate, cudaStream_t st, int sm_count = 148,
+                        const __nv_bfloat16* A_lo = nullptr, const __nv_bfloat16* B_lo = nullptr) {
     if (M <= 0 || N <= 0) return CRNN_OK;
     if (K <= 0) return set_err(CRNN_ERR_ARG, "gemm_bf16_tc: K must be positive");
+    if ((A_lo == nullptr) != (B_lo == nullptr)) return set_err(CRNN_ERR_ARG, "gemm_bf16_tc: both operands or neither must be split");
+    const bool split = A_lo != nullptr;
     constexpr int BN = 128, STAGES = 3;
-    using L = GemmTcSmem<BN, STAGES>;
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmAl, tmBl;
     int rc = a_mn ? make_tmap_bf16(&tmA, A, K, M, lda, 64) : make_tmap_bf16(&tmA, A, M, K, lda, GT_BM);
     if (rc != CRNN_OK) return rc;
     rc = b_mn ? make_tmap_bf16(&tmB, B, K, N, ldb, 64) : make_tmap_bf16(&tmB, B, N, K, ldb, BN);
     if (rc != CRNN_OK) return rc;
+    tmAl = tmA; tmBl = tmB;
+    if (split) {
+        rc = a_mn ? make_tmap_bf16(&tmAl, A_lo, K, M, lda, 64) : make_tmap_bf16(&tmAl, A_lo, M, K, lda, GT_BM);
+        if (rc != CRNN_OK) return rc;
+        rc = b_mn ? make_tmap_bf16(&tmBl, B_lo, K, N, ldb, 64) : make_tmap_bf16(&tmBl, B_lo, N, K, ldb, BN);
+        if (rc != CRNN_OK) return rc;
+    }
     CUtensorMap tmC = tmA;                               // placeholder when the TMA epilogue is not usable
     const int tma_out = ((ldc & 3) == 0 && ((uintptr_t)C & 15) == 0 && ((uintptr_t)bias & 15) == 0) ? 1 : 0;
     if (tma_out) {
@@ -256,22 +284,26 @@ inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda
     g.mode = accumulate ? (grid.z > 1 ? 2 : 1) : 0;
     static bool attr_set = false;
     if (!attr_set) {
-        CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+        CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       GemmTcSmem<BN, STAGES, false>::TOTAL));
+        CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       GemmTcSmem<BN, STAGES, true>::TOTAL));
         attr_set = true;
     }
-    gemm_bf16_tc_kernel<BN, STAGES><<<grid, GT_THREADS, L::TOTAL, st>>>(tmA, tmB, tmC, g);
+    if (split) gemm_bf16_tc_kernel<BN, STAGES, true><<<grid, GT_THREADS, GemmTcSmem<BN, STAGES, true>::TOTAL, st>>>(tmA, tmB, tmAl, tmBl, tmC, g);
+    else       gemm_bf16_tc_kernel<BN, STAGES, false><<<grid, GT_THREADS, GemmTcSmem<BN, STAGES, false>::TOTAL, st>>>(tmA, tmB, tmAl, tmBl, tmC, g);
     CRNN_LAUNCH_CHECK("gemm_bf16_tc_kernel");
     return CRNN_OK;
 }
 
 // fp32 -> bf16 cast of a row-major matrix (optionally re-pitched): the bf16 shadow copies.
 __global__ void __launch_bounds__(256) cast_bf16_kernel(const float* __restrict__ src, int64_t lds, int64_t rows, int cols,
-                                                        __nv_bfloat16* __restrict__ dst, int64_t ldd) {
+                                                        __nv_bfloat16* __restrict__ dst, int64_t ldd, int64_t lo_ofs = 0) {
     const int64_t n = rows * cols;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         int64_t r = i / cols;
         int c = (int)(i % cols);
-        dst[r * ldd + c] = __float2bfloat16_rn(src[r * lds + c]);
+        store_bf16_split(dst + r * ldd + c, lo_ofs, src[r * lds + c]);
     }
 }
 

@@ -22,7 +22,7 @@ namespace tc {
 constexpr int RT_EPI_WARPS = 8;             // two per SM sub-partition: one hides the other's latencies
 constexpr int RT_EPI_THREADS = RT_EPI_WARPS * 32;
 constexpr int RT_THREADS = 64 + RT_EPI_THREADS;
-constexpr int RT_RING_BYTES = 64 * 1024;  // TMA ring for the streamed operand
+constexpr int RT_RING_BYTES = 64 * 1024;  // TMA ring for the streamed operand (default; RecTcArgs::ring_bytes may be larger)
 constexpr int RT_MAX_STAGES = 32;
 constexpr int RT_MROWS_BYTES = 128 * 128; // bytes an M=128 operand reads from a tile base (128 rows x 64 bf16)
 // Ring geometry.  A tile is one K block (64 bf16 = 128 B per row) of `box_rows` rows; a STAGE is
@@ -31,19 +31,20 @@ constexpr int RT_MROWS_BYTES = 128 * 128; // bytes an M=128 operand reads from a
 // tile sees later tiles / the slack at the ring's end; those products fall in accumulator rows nobody
 // reads.  Small batch tiles get a whole phase's K extent in one or two instructions.
 __host__ __device__ inline int rt_tile_bytes(int box_rows) { return ((box_rows + 7) & ~7) * 128; }
-__host__ __device__ inline int rt_chunk_kb(int box_rows, int nkb) {
+// Split operands (RecTcArgs::split): a stage holds `chunk_kb` hi tiles followed by their `chunk_kb` lo tiles.
+__host__ __device__ inline int rt_chunk_kb(int box_rows, int nkb, int split = 0) {
     // ~32 KB per stage: both the producer and the MMA thread pay a few hundred cycles of barrier
     // hand-shake per stage, which is what bounds the large configurations (measured, config 4:
     // 1/2/3/4 tiles of 8 KB per stage -> 28.6 / 21.9 / 19.7 / 18.5 ms per step)
-    int c = (32 * 1024) / rt_tile_bytes(box_rows);
+    int c = (32 * 1024) / (rt_tile_bytes(box_rows) * (1 + split));
     if (c < 1) c = 1;
     if (c > nkb) c = nkb;
     if (c > 256) c = 256;
     if (c == nkb && nkb >= 4 && (nkb & 1) == 0) c = nkb / 2;     // two instructions: MMAs start on the first half
     return c;
 }
-__host__ __device__ inline int rt_num_stages(int box_rows, int chunk_kb) {
-    int n = (RT_RING_BYTES - RT_MROWS_BYTES + rt_tile_bytes(box_rows)) / (rt_tile_bytes(box_rows) * chunk_kb);
+__host__ __device__ inline int rt_num_stages(int box_rows, int chunk_kb, int split = 0, int ring_bytes = RT_RING_BYTES) {
+    int n = (ring_bytes - RT_MROWS_BYTES + rt_tile_bytes(box_rows)) / (rt_tile_bytes(box_rows) * chunk_kb * (1 + split));
     if (n < 2) n = 2;
     return n > RT_MAX_STAGES ? RT_MAX_STAGES : n;
 }
@@ -64,6 +65,9 @@ struct RecTcArgs {
     int cbar;                   // 1: the cluster holds ALL slices of a batch tile: steps are ordered by remote mbarrier arrives, no global counter
     int csize;                  // CTAs per cluster along the slice index (1: no cluster); they share one batch tile's rows via TMA multicast
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
+    int split;                  // 1: every bf16 operand is a (hi, lo) pair (CRNN_PREC_BF16X3): hi*hi + lo*hi + hi*lo per K step
+    long long hxb_lo, rsb_lo, dzb_lo;   // element offsets of the lo twins of hxb / rsb / dzb (0 when not split)
+    int ring_bytes;             // size of the TMA ring (>= RT_RING_BYTES, multiple of 1024)
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
     float* gates;               // [S,B,GS*H]  in: x-projection + bias, out: activations
     float* hx;                  // [(S+1),B,H]
@@ -86,8 +90,13 @@ __device__ __forceinline__ float tanh_mufu(float x) {
 }
 // `fast` (block-uniform): one MUFU.TANH per activation (|err| ~ 5e-4, well under bf16's 4e-3
 // operand rounding) instead of the accurate expf/tanhf sequences.
-#define fast_tanh(x) (FAST ? tanh_mufu(x) : tanhf(x))
-#define fast_sigmoid(x) (FAST ? fmaf(0.5f, tanh_mufu(0.5f * (x)), 0.5f) : 1.0f / (1.0f + expf(-(x))))
+// !FAST (the 1e-4 parity bar of CRNN_PREC_BF16X3): ex2.approx + rcp.approx forms, absolute error < 1e-6 -
+// a tenth of the split-operand contraction error - at a fifth of the instructions of expf / tanhf, which
+// sit on the serial chain of every step.  Saturate correctly: e^x -> inf gives 1/inf = 0.
+__device__ __forceinline__ float sigmoid_ex2(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_ex2(float x) { return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x)); }
+#define fast_tanh(x) (FAST ? tanh_mufu(x) : tanh_ex2(x))
+#define fast_sigmoid(x) (FAST ? fmaf(0.5f, tanh_mufu(0.5f * (x)), 0.5f) : sigmoid_ex2(x))
 
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(RT_EPI_THREADS) : "memory"); }
 
@@ -107,12 +116,12 @@ struct RtSmem {
     uint32_t* tmem_slot;
 };
 
-__device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, size_t wsb_bytes, int zs_floats) {
+__device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, size_t wsb_bytes, int zs_floats, int ring_bytes) {
     RtSmem s;
     uint8_t* p = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     s.wsa = p; p += wsa_bytes;
     s.wsb = p; p += wsb_bytes;
-    s.ring = p; p += RT_RING_BYTES;
+    s.ring = p; p += ring_bytes;
     s.zs = reinterpret_cast<float*>(p); p += (size_t)((zs_floats + 3) & ~3) * 4;
     s.a_full = reinterpret_cast<uint64_t*>(p);
     s.a_empty = s.a_full + RT_MAX_STAGES;
@@ -126,8 +135,8 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     return s;
 }
 
-inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats) {
-    return wsa_bytes + wsb_bytes + RT_RING_BYTES + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024;
+inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats, int ring_bytes = RT_RING_BYTES) {
+    return wsa_bytes + wsb_bytes + ring_bytes + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024;
 }
 
 // Role-private pipeline state.
@@ -145,9 +154,31 @@ struct RtPipe {
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
-                                           int ckb, int nst, int use3d, int csize_in, int crank, int mcast, int kb_ofs = 0) {
+                                           int ckb, int nst, int use3d, int csize_in, int crank, int mcast, int kb_ofs = 0,
+                                           const CUtensorMap* tmAlo = nullptr) {
     const int csize = mcast ? csize_in : 1;
     const int tile = rt_tile_bytes(box_rows);
+    if (tmAlo) {                                       // split operands: hi tiles then lo tiles, one barrier per stage
+        const int stage = 2 * ckb * tile;
+        for (int kb = 0; kb < nkb; kb += ckb, p.advance(nst)) {
+            const int st = (int)p.st;
+            const int n = min(ckb, nkb - kb);
+            mbar_wait(&s.a_empty[st], p.ph ^ 1u);
+            mbar_expect_tx(&s.a_full[st], 2u * (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n));
+            uint8_t* hi = s.ring + st * stage;
+            uint8_t* lo = hi + ckb * tile;
+            if (use3d) {
+                tma_load_3d(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kb);
+                tma_load_3d(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kb);
+            } else {
+                for (int j = 0; j < n; ++j) {
+                    tma_load_2d(hi + j * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow);
+                    tma_load_2d(lo + j * tile, tmAlo, &s.a_full[st], (kb_ofs + kb + j) * 64, arow);
+                }
+            }
+        }
+        return;
+    }
     const uint16_t mask = (uint16_t)((1u << csize) - 1u);
     for (int kb = 0; kb < nkb; kb += ckb, p.advance(nst)) {
         const int st = (int)p.st;
@@ -182,8 +213,10 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 //            resident data whose products land in accumulator lanes nobody reads.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
                                        int swap, int nrows16, int box_rows, int ckb, int nst, int m64, int csize,
-                                       long long* stamps = nullptr) {
+                                       long long* stamps = nullptr, int split = 0) {
     const int tile = rt_tile_bytes(box_rows);
+    // split: lo tiles sit ckb tiles after their hi tiles in the stage, the lo weight region right after the hi one
+    const uint64_t a_lo = (uint64_t)((ckb * tile) >> 4), w_lo = (uint64_t)(((uint32_t)nkb * (uint32_t)nc * 128u) >> 4);
     mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
     tc_fence_after();
     if (stamps) stamps[10] = clock64();
@@ -198,10 +231,28 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
         // Descriptors are built once per stage and advanced by plain adds: the issuing thread is a
         // single scalar instruction stream, and every instruction between two tcgen05.mma costs
         // tensor-pipe idle time (K step of 16 bf16 = 32 B = +2 in the descriptor's address field).
-        uint64_t da = desc_kmajor(smem_u32(s.ring + st * ckb * tile));
+        uint64_t da = desc_kmajor(smem_u32(s.ring + st * ckb * tile * (1 + split)));
         uint64_t db = desc_kmajor(w0 + (uint32_t)kb0 * (uint32_t)nc * 128u);
         const uint64_t da_step = (uint64_t)(tile >> 4), db_step = (uint64_t)((nc * 128) >> 4);
-        if (!swap) {
+        if (split) {
+            for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) {
+                    if (!swap) mma_bf16(tmem, da + k, db + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+                    else       mma_bf16(tmem, db + k, da + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) {
+                    if (!swap) mma_bf16(tmem, da + a_lo + k, db + k, idesc, 1u);
+                    else       mma_bf16(tmem, db + k, da + a_lo + k, idesc, 1u);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) {
+                    if (!swap) mma_bf16(tmem, da + k, db + w_lo + k, idesc, 1u);
+                    else       mma_bf16(tmem, db + w_lo + k, da + k, idesc, 1u);
+                }
+            }
+        } else if (!swap) {
             for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
                 mma_bf16(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
                 mma_bf16(tmem, da + 2, db + 2, idesc, 1u);
@@ -387,6 +438,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                                                    const __grid_constant__ CUtensorMap tmRS,
                                                                    const __grid_constant__ CUtensorMap tmW0,
                                                                    const __grid_constant__ CUtensorMap tmW1,
+                                                                   const __grid_constant__ CUtensorMap tmHl,    // lo twins (split operands)
+                                                                   const __grid_constant__ CUtensorMap tmRSl,
+                                                                   const __grid_constant__ CUtensorMap tmW0l,
+                                                                   const __grid_constant__ CUtensorMap tmW1l,
                                                                    RecTcArgs a) {
     extern __shared__ uint8_t smem_raw[];
     constexpr int G1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
@@ -396,7 +451,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const int HCG = HC * Q;                           // units whose gate columns this CTA contracts
     const int NCA = G1 * HCG;
     const int nkb = ceil_div(H, 64) / Q;              // K blocks of this CTA's part (host: H % (64 Q) == 0 when Q > 1)
-    const RtSmem s = rt_carve(smem_raw, (size_t)nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb * HCG * 128 : 0, a.zs_floats);
+    const int nsp = 1 + a.split;                      // operand copies resident / streamed
+    const RtSmem s = rt_carve(smem_raw, (size_t)nsp * nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nsp * nkb * HCG * 128 : 0, a.zs_floats, a.ring_bytes);
     float* Zs = s.zs;
     const int ldz = NCA + 1;                          // (GRU candidate pass uses the first HCG columns)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -409,7 +465,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     while ((int)tcols < (a.swap ? 128 : NCA)) tcols <<= 1;
 
     // zero the ring once: rows past the TMA box are never written and must not hold NaNs
-    for (int i = threadIdx.x; i < RT_RING_BYTES / 16; i += RT_THREADS)
+    for (int i = threadIdx.x; i < a.ring_bytes / 16; i += RT_THREADS)
         reinterpret_cast<uint4*>(s.ring)[i] = make_uint4(0, 0, 0, 0);
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
@@ -434,12 +490,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         if (lane == 0) {
             // resident weights: once
             uint32_t wbytes = (uint32_t)nkb * NCA * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb * HCG * 128u : 0u);
-            mbar_expect_tx(s.w_bar, wbytes);
-            for (int kb = 0; kb < nkb; ++kb) {
-                tma_load_2d(s.wsa + (size_t)kb * NCA * 128, &tmW0, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG);
-                if (MODEL == CRNN_MODEL_GRU)
-                    tma_load_2d(s.wsb + (size_t)kb * HCG * 128, &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
-            }
+            mbar_expect_tx(s.w_bar, wbytes * (uint32_t)nsp);
+            for (int half = 0; half < nsp; ++half)
+                for (int kb = 0; kb < nkb; ++kb) {
+                    tma_load_2d(s.wsa + (size_t)(half * nkb + kb) * NCA * 128, half ? &tmW0l : &tmW0, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG);
+                    if (MODEL == CRNN_MODEL_GRU)
+                        tma_load_2d(s.wsb + (size_t)(half * nkb + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
+                }
             for (int t = a.t_begin; t < a.t_end; ++t) {
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (int)phases_done;
@@ -447,7 +504,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb,
+                                   a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr);
                     RT_STAMP(2);
                     ++phases_done;
                 }
@@ -461,7 +519,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
-                               (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr);
+                               (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr, a.split);
                     RT_STAMP(3);
                 }
         }
@@ -524,24 +582,24 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                 float cn = fmaf(sf, ax[u], si * tj);
                                 float hn = so * fast_tanh(cn);
                                 hnext[e[u].o] = hn;
-                                hnb[e[u].o] = __float2bfloat16_rn(hn);
+                                store_bf16_split(hnb + e[u].o, a.hxb_lo, hn);
                                 a.cx[(int64_t)(t + 1) * BH + e[u].o] = cn;
                                 g[0] = si; g[H] = tj; g[2 * H] = sf; g[3 * H] = so;
                             } else if (MODEL == CRNN_MODEL_RNN) {
                                 float hn = fast_tanh(zv[u][0] + x0[u]);
                                 hnext[e[u].o] = hn;
-                                hnb[e[u].o] = __float2bfloat16_rn(hn);
+                                store_bf16_split(hnb + e[u].o, a.hxb_lo, hn);
                             } else if (ph == 0) {
                                 float r_ = fast_sigmoid(zv[u][0] + x0[u]);
                                 float u_ = fast_sigmoid(zv[u][1] + x1[u]);
                                 float rs = r_ * ax[u];                                   // reset BEFORE the matmul
-                                a.rsb[e[u].row * H + e[u].j] = __float2bfloat16_rn(rs);
+                                store_bf16_split(a.rsb + e[u].row * H + e[u].j, a.rsb_lo, rs);
                                 g[0] = r_; g[H] = u_; g[3 * H] = rs;
                             } else {
                                 float cand = fast_tanh(zv[u][0] + x0[u]);
                                 float hn = fmaf(x1[u], ax[u] - cand, cand);              // u*h + (1-u)*cand
                                 hnext[e[u].o] = hn;
-                                hnb[e[u].o] = __float2bfloat16_rn(hn);
+                                store_bf16_split(hnb + e[u].o, a.hxb_lo, hn);
                                 g[2 * H] = cand;
                             }
                         }
@@ -574,6 +632,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                                                                    const __grid_constant__ CUtensorMap tmZ1,   // gru: dzb candidate columns
                                                                    const __grid_constant__ CUtensorMap tmW0,
                                                                    const __grid_constant__ CUtensorMap tmW1,
+                                                                   const __grid_constant__ CUtensorMap tmZ0l,   // lo twins (split operands)
+                                                                   const __grid_constant__ CUtensorMap tmZ1l,
+                                                                   const __grid_constant__ CUtensorMap tmW0l,
+                                                                   const __grid_constant__ CUtensorMap tmW1l,
                                                                    RecTcArgs a) {
     extern __shared__ uint8_t smem_raw[];
     constexpr int G1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
@@ -583,7 +645,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     const int HCG = HC * Q;
     const int nkb0 = ceil_div(G1 * H, 64) / Q;        // this CTA's part of the gate-column contraction
     const int nkb1 = ceil_div(H, 64) / Q;
-    const RtSmem s = rt_carve(smem_raw, (size_t)nkb0 * HCG * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nkb1 * HCG * 128 : 0, a.zs_floats);
+    const int nsp = 1 + a.split;
+    const RtSmem s = rt_carve(smem_raw, (size_t)nsp * nkb0 * HCG * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nsp * nkb1 * HCG * 128 : 0, a.zs_floats, a.ring_bytes);
     float* Zs = s.zs;
     const int ldz = HCG + 1;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -596,7 +659,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     uint32_t tcols = 32;
     while ((int)tcols < (a.swap ? 128 : HCG)) tcols <<= 1;
 
-    for (int i = threadIdx.x; i < RT_RING_BYTES / 16; i += RT_THREADS)
+    for (int i = threadIdx.x; i < a.ring_bytes / 16; i += RT_THREADS)
         reinterpret_cast<uint4*>(s.ring)[i] = make_uint4(0, 0, 0, 0);
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
@@ -619,22 +682,28 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     if (warp == 0) {
         if (lane == 0) {
             uint32_t wbytes = (uint32_t)nkb0 * HCG * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb1 * HCG * 128u : 0u);
-            mbar_expect_tx(s.w_bar, wbytes);
-            for (int kb = 0; kb < nkb0; ++kb) tma_load_2d(s.wsa + (size_t)kb * HCG * 128, &tmW0, s.w_bar, (kq * nkb0 + kb) * 64, H + jg0);
-            if (MODEL == CRNN_MODEL_GRU)
-                for (int kb = 0; kb < nkb1; ++kb) tma_load_2d(s.wsb + (size_t)kb * HCG * 128, &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
+            mbar_expect_tx(s.w_bar, wbytes * (uint32_t)nsp);
+            for (int half = 0; half < nsp; ++half) {
+                for (int kb = 0; kb < nkb0; ++kb)
+                    tma_load_2d(s.wsa + (size_t)(half * nkb0 + kb) * HCG * 128, half ? &tmW0l : &tmW0, s.w_bar, (kq * nkb0 + kb) * 64, H + jg0);
+                if (MODEL == CRNN_MODEL_GRU)
+                    for (int kb = 0; kb < nkb1; ++kb)
+                        tma_load_2d(s.wsb + (size_t)(half * nkb1 + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
+            }
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
                 if (t + 1 < a.S) {
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb0);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb0,
+                                   a.split ? &tmZ0l : nullptr);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb1);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb1,
+                                   a.split ? &tmZ1l : nullptr);
                     ++phases_done;
                 }
             }
@@ -644,9 +713,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split);
             }
         }
     } else {
@@ -712,19 +781,19 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                             const float dO = dht * tcn * so * (1.0f - so);
                             a.carry0[e[u].o] = dct * sf;
                             dz[0] = di; dz[H] = dj; dz[2 * H] = df; dz[3 * H] = dO;
-                            dzb[0] = __float2bfloat16_rn(di); dzb[H] = __float2bfloat16_rn(dj);
-                            dzb[2 * H] = __float2bfloat16_rn(df); dzb[3 * H] = __float2bfloat16_rn(dO);
+                            store_bf16_split(dzb, a.dzb_lo, di); store_bf16_split(dzb + H, a.dzb_lo, dj);
+                            store_bf16_split(dzb + 2 * H, a.dzb_lo, df); store_bf16_split(dzb + 3 * H, a.dzb_lo, dO);
                         } else if (MODEL == CRNN_MODEL_RNN) {
                             const float d = dht * (1.0f - x0[u] * x0[u]);
                             dz[0] = d;
-                            dzb[0] = __float2bfloat16_rn(d);
+                            store_bf16_split(dzb, a.dzb_lo, d);
                         } else {
                             dht += cr[u];
                             const float u_ = x1[u], cand = x2[u], hp = c0v[u];
                             const float dc = dht * (1.0f - u_) * (1.0f - cand * cand);   // d candidate pre-activation
                             const float du = dht * (hp - cand) * u_ * (1.0f - u_);       // d update-gate pre-activation
                             dz[2 * H] = dc; dz[H] = du;
-                            dzb[2 * H] = __float2bfloat16_rn(dc); dzb[H] = __float2bfloat16_rn(du);
+                            store_bf16_split(dzb + 2 * H, a.dzb_lo, dc); store_bf16_split(dzb + H, a.dzb_lo, du);
                             a.carry1[e[u].o] = dht;
                         }
                     }
@@ -762,7 +831,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                             const float r_ = x0[u], u_ = x1[u];
                             const float dr = drs * hp[u] * r_ * (1.0f - r_);
                             a.dz[e[u].row * zw + e[u].j] = dr;
-                            a.dzb[e[u].row * zw + e[u].j] = __float2bfloat16_rn(dr);
+                            store_bf16_split(a.dzb + e[u].row * zw + e[u].j, a.dzb_lo, dr);
                             a.carry0[e[u].o] = fmaf(c1v[u], u_, drs * r_);
                         }
                     }
@@ -791,7 +860,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
 //   GRU: rows 2*HC + jj -> Wc[(H+k), j0+jj].  Rows of units past H and k >= H are zero.
 __global__ void __launch_bounds__(256) pack_rec_weights_kernel(const float* __restrict__ W, const float* __restrict__ Wc,
                                                                int H, int HC, int nslices, int G1, int GW, int Kp,
-                                                               __nv_bfloat16* __restrict__ out) {
+                                                               __nv_bfloat16* __restrict__ out, int64_t lo_ofs = 0) {
     const int64_t n = (int64_t)nslices * GW * HC * Kp;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const int k = (int)(i % Kp);
@@ -808,7 +877,7 @@ __global__ void __launch_bounds__(256) pack_rec_weights_kernel(const float* __re
                 if (j < H) v = Wc[(int64_t)(H + k) * H + j];
             }
         }
-        out[i] = __float2bfloat16_rn(v);
+        store_bf16_split(out + i, lo_ofs, v);
     }
 }
 

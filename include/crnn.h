@@ -44,6 +44,10 @@ extern "C" {
 
 #define CRNN_PREC_FP32  0   /* fp32 FFMA contractions: the 1e-4 parity mode                    */
 #define CRNN_PREC_BF16  1   /* bf16 tcgen05 contractions, fp32 accumulate / state / master weights */
+#define CRNN_PREC_BF16X3 2  /* fp32-grade tensor-core mode: every operand is a (hi, lo) bf16 pair and each
+                             * contraction issues hi*hi + lo*hi + hi*lo into the fp32 accumulator (error
+                             * ~2^-17 per product instead of bf16's 2^-9); accurate activations.  Meets the
+                             * same 1e-4 parity bar as CRNN_PREC_FP32 against the fp32 oracle.            */
 
 #define CRNN_GRAD_TAIL  2
 
@@ -194,6 +198,13 @@ int crnn_gemm_f32(int32_t ta, int32_t tb, int32_t M, int32_t N, int32_t K,
 int crnn_gemm_bf16(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K,
                    const void* d_A_bf16, int64_t lda, const void* d_B_bf16, int64_t ldb,
                    float* d_C, int64_t ldc, const float* d_bias, int32_t accumulate, void* stream);
+
+/* The same with split operands (CRNN_PREC_BF16X3): op(A) = A_hi + A_lo, op(B) = B_hi + B_lo, each
+ * twin laid out exactly like its hi array; computes A_hi*B_hi + A_lo*B_hi + A_hi*B_lo.           */
+int crnn_gemm_bf16x3(int32_t a_mn, int32_t b_mn, int32_t M, int32_t N, int32_t K,
+                     const void* d_A_hi, const void* d_A_lo, int64_t lda,
+                     const void* d_B_hi, const void* d_B_lo, int64_t ldb,
+                     float* d_C, int64_t ldc, const float* d_bias, int32_t accumulate, void* stream);
 
 #ifdef __cplusplus
 }
