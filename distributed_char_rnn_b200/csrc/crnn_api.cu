@@ -717,7 +717,12 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // sized for the shortest K extent, H
     a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64), split);
     { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) a.ckb = std::min(ck_env, ceil_div(H, 64)); }
+    a.rotate = env_int("CRNN_TC_ROTATE", 0);
     a.ring_bytes = backward ? p.ring_bwd : p.ring_fwd;
+    {   // at least two stages must fit in the ring
+        const int tile = tc::rt_tile_bytes(p.box_rows);
+        while (a.ckb > 1 && (a.ring_bytes - tc::RT_MROWS_BYTES + tile) / (tile * a.ckb * (1 + split)) < env_int("CRNN_TC_MIN_STAGES", 2)) --a.ckb;
+    }
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb, split, a.ring_bytes);
     a.use3d = (H % 64 == 0 && env_int("CRNN_TC_3D", 1)) ? 1 : 0;
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
@@ -751,9 +756,15 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         }
     }
     if (rc != CRNN_OK) return rc;
+    // elements per epilogue thread per batch: one batch per 128-row pass when 8 per thread cover it, so every global
+    // load of the pass is in flight before the accumulator arrives
+    const int per_pass = std::min(128, p.BT) * p.HC;
+    const bool ub8 = per_pass > tc::RT_EPI_THREADS * 4 && env_int("CRNN_TC_UB8", 1);
+    a.defer = env_int("CRNN_TC_DEFER", 1);
+    a.expt = env_int("CRNN_TC_EXPT", 0);
     void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
-        h->fast_act ? (backward ? tc::rec_bwd_tc_kernel<MODEL, true> : tc::rec_fwd_tc_kernel<MODEL, true>)
-                    : (backward ? tc::rec_bwd_tc_kernel<MODEL, false> : tc::rec_fwd_tc_kernel<MODEL, false>);
+        h->fast_act ? (backward ? (ub8 ? tc::rec_bwd_tc_kernel<MODEL, true, 8> : tc::rec_bwd_tc_kernel<MODEL, true, 4>) : (ub8 ? tc::rec_fwd_tc_kernel<MODEL, true, 8> : tc::rec_fwd_tc_kernel<MODEL, true, 4>))
+                    : (backward ? (ub8 ? tc::rec_bwd_tc_kernel<MODEL, false, 8> : tc::rec_bwd_tc_kernel<MODEL, false, 4>) : (ub8 ? tc::rec_fwd_tc_kernel<MODEL, false, 8> : tc::rec_fwd_tc_kernel<MODEL, false, 4>));
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // Optional clusters along the slice index (CRNN_TC_CLUSTER=2|4|8): the CTAs of a cluster work on the

@@ -45,7 +45,7 @@ __host__ __device__ inline int rt_chunk_kb(int box_rows, int nkb, int split = 0)
 }
 __host__ __device__ inline int rt_num_stages(int box_rows, int chunk_kb, int split = 0, int ring_bytes = RT_RING_BYTES) {
     int n = (ring_bytes - RT_MROWS_BYTES + rt_tile_bytes(box_rows)) / (rt_tile_bytes(box_rows) * chunk_kb * (1 + split));
-    if (n < 2) n = 2;
+    if (n < 1) n = 1;            // (the launcher shrinks chunk_kb until a stage fits)
     return n > RT_MAX_STAGES ? RT_MAX_STAGES : n;
 }
 
@@ -67,6 +67,10 @@ struct RecTcArgs {
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
     int split;                  // 1: every bf16 operand is a (hi, lo) pair (CRNN_PREC_BF16X3): hi*hi + lo*hi + hi*lo per K step
     long long hxb_lo, rsb_lo, dzb_lo;   // element offsets of the lo twins of hxb / rsb / dzb (0 when not split)
+    int expt;                   // timing experiments only (CRNN_TC_EXPT; results are wrong when set): 1 no critical stores, 2 no math
+    int defer;                  // 1: stores only this CTA reads later are issued after the step barrier's release
+    int rotate;                 // 1: slices of a tile walk the K blocks from different starting stages, so they do not all
+                                // ask L2 for the same rows at the same moment
     int ring_bytes;             // size of the TMA ring (>= RT_RING_BYTES, multiple of 1024)
     int zs_floats;              // shared staging for one accumulator pass: rows x (columns + 1)
     float* gates;               // [S,B,GS*H]  in: x-projection + bias, out: activations
@@ -79,7 +83,7 @@ struct RecTcArgs {
     __nv_bfloat16* hxb;         // [(S+1),B,H] bf16 copy of hx (fwd out; MMA operand)
     __nv_bfloat16* rsb;         // gru [S,B,H] bf16 r*h (fwd out; MMA operand)
     __nv_bfloat16* dzb;         // bwd [(S+1),B,GZ*H] bf16 copy of dz (MMA operand)
-    long long* dbg;             // optional: CTA 0 writes clock64 stamps [phase][8] (CRNN_TC_DEBUG)
+    long long* dbg;             // optional (CRNN_TC_DEBUG): four CTAs record clock64 stamps [cta][phase 20..27][16] in shared memory and dump them at exit
     unsigned* barrier;          // one zeroed counter per batch tile: rows of different tiles never interact
 };
 
@@ -107,13 +111,14 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 #define RT_STAMP(slot)                                                                     \
     do {                                                                                   \
-        if (a.dbg && blockIdx.x == 0 && dbg_phase < 60) a.dbg[dbg_phase * 16 + (slot)] = clock64(); \
+        if (dbgs && dbg_phase >= 20 && dbg_phase < 28) dbgs[(dbg_phase - 20) * 24 + (slot)] = clock64(); \
     } while (0)
 
 struct RtSmem {
     uint8_t* wsa; uint8_t* wsb; uint8_t* ring; float* zs;
     uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar, *step_bar, *zs_ready, *zs_free;
     uint32_t* tmem_slot;
+    long long* dbg;          // 8 phases x 24 stamps
 };
 
 __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, size_t wsb_bytes, int zs_floats, int ring_bytes) {
@@ -132,11 +137,12 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     s.zs_ready = s.step_bar + 1;
     s.zs_free = s.zs_ready + 1;
     s.tmem_slot = reinterpret_cast<uint32_t*>(s.zs_free + 1);
+    s.dbg = reinterpret_cast<long long*>(s.tmem_slot + 2);
     return s;
 }
 
 inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats, int ring_bytes = RT_RING_BYTES) {
-    return wsa_bytes + wsb_bytes + ring_bytes + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024;
+    return wsa_bytes + wsb_bytes + ring_bytes + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024 + 2048;
 }
 
 // Role-private pipeline state.
@@ -155,7 +161,7 @@ struct RtPipe {
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
                                            int ckb, int nst, int use3d, int csize_in, int crank, int mcast, int kb_ofs = 0,
-                                           const CUtensorMap* tmAlo = nullptr) {
+                                           const CUtensorMap* tmAlo = nullptr, int rot = 0, long long* stamps = nullptr) {
     const int csize = mcast ? csize_in : 1;
     const int tile = rt_tile_bytes(box_rows);
     if (tmAlo) {                                       // split operands: hi tiles then lo tiles, one barrier per stage
@@ -167,13 +173,14 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
             mbar_expect_tx(&s.a_full[st], 2u * (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n));
             uint8_t* hi = s.ring + st * stage;
             uint8_t* lo = hi + ckb * tile;
+            const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;      // rotated start (rot is a multiple of ckb)
             if (use3d) {
-                tma_load_3d(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kb);
-                tma_load_3d(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kb);
+                tma_load_3d(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
+                tma_load_3d(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kbr);
             } else {
                 for (int j = 0; j < n; ++j) {
-                    tma_load_2d(hi + j * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow);
-                    tma_load_2d(lo + j * tile, tmAlo, &s.a_full[st], (kb_ofs + kb + j) * 64, arow);
+                    tma_load_2d(hi + j * tile, tmA, &s.a_full[st], (kb_ofs + kbr + j) * 64, arow);
+                    tma_load_2d(lo + j * tile, tmAlo, &s.a_full[st], (kb_ofs + kbr + j) * 64, arow);
                 }
             }
         }
@@ -186,6 +193,7 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
         // (cluster: the empty barrier collects the MMA commits of EVERY CTA of the cluster, because the
         //  CTA whose turn it is overwrites this stage in all of them)
         mbar_wait(&s.a_empty[st], p.ph ^ 1u);
+        if (stamps && kb <= ckb) stamps[kb == 0 ? 19 : 21] = clock64();
         const uint32_t bytes = (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n);
         mbar_expect_tx(&s.a_full[st], bytes);
         if (csize > 1) {
@@ -199,10 +207,13 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
                     tma_load_2d_mc(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow, mask);
             }
         } else if (use3d) {                            // whole stage in one instruction (out-of-range k-blocks read zero)
-            tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kb);
+            const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;
+            tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
+            if (stamps && kb <= ckb) stamps[kb == 0 ? 20 : 22] = clock64();
         } else {
+            const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;
             for (int j = 0; j < n; ++j)
-                tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow);
+                tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kbr + j) * 64, arow);
         }
     }
 }
@@ -211,66 +222,68 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 //            the MMA cost is max(M,128)*N/256 cycles per K=16, so the smaller of (nc, rows) goes to N.
 //            Weight regions hold nc < 128 rows; the rows the M=128 operand reads past them are other
 //            resident data whose products land in accumulator lanes nobody reads.
+// Executed by ALL lanes of the (converged) MMA warp with warp-uniform arguments; one elected lane issues.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
                                        int swap, int nrows16, int box_rows, int ckb, int nst, int m64, int csize,
-                                       long long* stamps = nullptr, int split = 0) {
+                                       long long* stamps = nullptr, int split = 0, int rot = 0) {
     const int tile = rt_tile_bytes(box_rows);
+    const bool lane0 = (threadIdx.x & 31) == 0;
     // split: lo tiles sit ckb tiles after their hi tiles in the stage, the lo weight region right after the hi one
     const uint64_t a_lo = (uint64_t)((ckb * tile) >> 4), w_lo = (uint64_t)(((uint32_t)nkb * (uint32_t)nc * 128u) >> 4);
     mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
     tc_fence_after();
-    if (stamps) stamps[10] = clock64();
+    if (stamps && lane0) stamps[10] = clock64();
     const uint32_t idesc = swap ? idesc_bf16(128, nrows16, 0, 0) : idesc_bf16(m64 ? 64 : 128, nc, 0, 0);
     const uint32_t w0 = smem_u32(wbase);
     for (int kb0 = 0; kb0 < nkb; kb0 += ckb, p.advance(nst)) {
         const int st = (int)p.st;
         mbar_wait(&s.a_full[st], p.ph);
         tc_fence_after();
-        if (stamps) stamps[kb0 == 0 ? 11 : 12] = clock64();
+        if (stamps && lane0) stamps[kb0 == 0 ? 11 : 12] = clock64();
         const int n = min(ckb, nkb - kb0);
-        // Descriptors are built once per stage and advanced by plain adds: the issuing thread is a
-        // single scalar instruction stream, and every instruction between two tcgen05.mma costs
-        // tensor-pipe idle time (K step of 16 bf16 = 32 B = +2 in the descriptor's address field).
+        // Descriptors are built once per stage and advanced by plain adds (K step of 16 bf16 = 32 B = +2 in
+        // the descriptor's address field): every instruction between two tcgen05.mma costs tensor-pipe idle time.
         uint64_t da = desc_kmajor(smem_u32(s.ring + st * ckb * tile * (1 + split)));
-        uint64_t db = desc_kmajor(w0 + (uint32_t)kb0 * (uint32_t)nc * 128u);
+        const int kbr = kb0 + rot >= nkb ? kb0 + rot - nkb : kb0 + rot;
+        uint64_t db = desc_kmajor(w0 + (uint32_t)kbr * (uint32_t)nc * 128u);
         const uint64_t da_step = (uint64_t)(tile >> 4), db_step = (uint64_t)((nc * 128) >> 4);
         if (split) {
             for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
 #pragma unroll
                 for (int k = 0; k < 8; k += 2) {
-                    if (!swap) mma_bf16(tmem, da + k, db + k, idesc, (uint32_t)((kb0 + j + k) != 0));
-                    else       mma_bf16(tmem, db + k, da + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+                    if (!swap) mma_bf16_elect(tmem, da + k, db + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+                    else       mma_bf16_elect(tmem, db + k, da + k, idesc, (uint32_t)((kb0 + j + k) != 0));
                 }
 #pragma unroll
                 for (int k = 0; k < 8; k += 2) {
-                    if (!swap) mma_bf16(tmem, da + a_lo + k, db + k, idesc, 1u);
-                    else       mma_bf16(tmem, db + k, da + a_lo + k, idesc, 1u);
+                    if (!swap) mma_bf16_elect(tmem, da + a_lo + k, db + k, idesc, 1u);
+                    else       mma_bf16_elect(tmem, db + k, da + a_lo + k, idesc, 1u);
                 }
 #pragma unroll
                 for (int k = 0; k < 8; k += 2) {
-                    if (!swap) mma_bf16(tmem, da + k, db + w_lo + k, idesc, 1u);
-                    else       mma_bf16(tmem, db + w_lo + k, da + k, idesc, 1u);
+                    if (!swap) mma_bf16_elect(tmem, da + k, db + w_lo + k, idesc, 1u);
+                    else       mma_bf16_elect(tmem, db + w_lo + k, da + k, idesc, 1u);
                 }
             }
         } else if (!swap) {
             for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
-                mma_bf16(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
-                mma_bf16(tmem, da + 2, db + 2, idesc, 1u);
-                mma_bf16(tmem, da + 4, db + 4, idesc, 1u);
-                mma_bf16(tmem, da + 6, db + 6, idesc, 1u);
+                mma_bf16_elect(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
+                mma_bf16_elect(tmem, da + 2, db + 2, idesc, 1u);
+                mma_bf16_elect(tmem, da + 4, db + 4, idesc, 1u);
+                mma_bf16_elect(tmem, da + 6, db + 6, idesc, 1u);
             }
         } else {
             for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
-                mma_bf16(tmem, db, da, idesc, (uint32_t)((kb0 + j) != 0));
-                mma_bf16(tmem, db + 2, da + 2, idesc, 1u);
-                mma_bf16(tmem, db + 4, da + 4, idesc, 1u);
-                mma_bf16(tmem, db + 6, da + 6, idesc, 1u);
+                mma_bf16_elect(tmem, db, da, idesc, (uint32_t)((kb0 + j) != 0));
+                mma_bf16_elect(tmem, db + 2, da + 2, idesc, 1u);
+                mma_bf16_elect(tmem, db + 4, da + 4, idesc, 1u);
+                mma_bf16_elect(tmem, db + 6, da + 6, idesc, 1u);
             }
         }
-        if (csize > 1) mma_commit_mc(&s.a_empty[st], (uint16_t)((1u << csize) - 1u));
-        else           mma_commit(&s.a_empty[st]);
+        if (csize > 1) { if (lane0) mma_commit_mc(&s.a_empty[st], (uint16_t)((1u << csize) - 1u)); __syncwarp(); }
+        else           mma_commit_elect(&s.a_empty[st]);
     }
-    mma_commit(s.z_full);
+    mma_commit_elect(s.z_full);
     ++p.z_i;
 }
 
@@ -351,46 +364,41 @@ __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane
     }
 }
 
-constexpr int RT_UB = 4;     // (row, unit) elements per epilogue thread per batch
 
 // Element -> (row, unit) mapping shared by all epilogues: consecutive threads take consecutive
 // hidden units of one batch row, so every global access of a warp is one contiguous segment.
+// Offsets are 32-bit and relative to per-pass base pointers (r < 128): r*H + jj into [B,H] tensors,
+// r*gw + jj into the gate stash, r*zw + jj into dz.
 struct EpiIdx {
     bool ok;
-    int zi;          // r*ldz + jj*gstride: index of the unit's first accumulator column in Zs
-    int64_t o;       // b*H + j
-    int64_t row;     // t*B + b
-    int j;
+    int r, jj;       // batch row inside the pass, unit inside the slice
+    int zi;          // r*ldz + (jcol0 + jj)*gstride: index of the unit's first accumulator column in Zs
 };
-__device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ldz, int gstride, int b0row, int j0,
-                                            int H, int64_t tB, int jcol0 = 0) {
+__device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ldz, int gstride, int jcol0 = 0) {
     EpiIdx e;
     e.ok = idx < nunits;
-    const int r = e.ok ? idx / hcv : 0;
-    const int jj = e.ok ? idx - r * hcv : 0;
-    e.zi = r * ldz + (jcol0 + jj) * gstride;
-    e.j = j0 + jj;
-    e.o = (int64_t)(b0row + r) * H + e.j;
-    e.row = tB + b0row + r;
+    e.r = e.ok ? idx / hcv : 0;
+    e.jj = e.ok ? idx - e.r * hcv : 0;
+    e.zi = e.r * ldz + (jcol0 + e.jj) * gstride;
     return e;
 }
 
 // Accumulator values of a batch of elements: NV consecutive columns per element, summed over the K
 // parts (cluster ranks, always in rank order).  All remote loads are issued before any is consumed,
 // so their distributed-shared-memory latencies overlap instead of adding up.
-template <int NV>
-__device__ __forceinline__ void rt_zgather(float (&zv)[RT_UB][4], const EpiIdx (&e)[RT_UB], const float* __restrict__ Zs,
+template <int NV, int UB>
+__device__ __forceinline__ void rt_zgather(float (&zv)[UB][4], const EpiIdx (&e)[UB], const float* __restrict__ Zs,
                                            const uint32_t* zpeer, int Q, int kq) {
     if (Q == 1) {
 #pragma unroll
-        for (int u = 0; u < RT_UB; ++u)
+        for (int u = 0; u < UB; ++u)
 #pragma unroll
             for (int k = 0; k < NV; ++k) zv[u][k] = e[u].ok ? Zs[e[u].zi + k] : 0.f;
         return;
     }
-    float part[RT_UB][NV][4];
+    float part[UB][NV][4];
 #pragma unroll
-    for (int u = 0; u < RT_UB; ++u)
+    for (int u = 0; u < UB; ++u)
 #pragma unroll
         for (int k = 0; k < NV; ++k)
 #pragma unroll
@@ -400,7 +408,7 @@ __device__ __forceinline__ void rt_zgather(float (&zv)[RT_UB][4], const EpiIdx (
                 part[u][k][r] = v;
             }
 #pragma unroll
-    for (int u = 0; u < RT_UB; ++u)
+    for (int u = 0; u < UB; ++u)
 #pragma unroll
         for (int k = 0; k < NV; ++k) zv[u][k] = ((part[u][k][0] + part[u][k][1]) + part[u][k][2]) + part[u][k][3];
 }
@@ -433,7 +441,7 @@ __device__ __forceinline__ void rt_zgather(float (&zv)[RT_UB][4], const EpiIdx (
 // of W_h this CTA's local column lc contracts with, K contiguous.  lc = jj*G1 + g for the first
 // contraction; GRU candidate rows follow at lc = 2*HC + jj.
 // ------------------------------------------------------------------------------------------
-template <int MODEL, bool FAST>
+template <int MODEL, bool FAST, int UB>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmH,
                                                                    const __grid_constant__ CUtensorMap tmRS,
                                                                    const __grid_constant__ CUtensorMap tmW0,
@@ -455,7 +463,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const RtSmem s = rt_carve(smem_raw, (size_t)nsp * nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nsp * nkb * HCG * 128 : 0, a.zs_floats, a.ring_bytes);
     float* Zs = s.zs;
     const int ldz = NCA + 1;                          // (GRU candidate pass uses the first HCG columns)
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for ptxas
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
     const int grp = slice / Q, kq = slice % Q;        // unit group, K part (== rank in the cluster)
     const int j0 = grp * HCG + kq * HC, hcv = min(HC, H - j0);   // the units this CTA finishes in its epilogue
@@ -481,10 +489,14 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const uint32_t tmem = *s.tmem_slot;
     const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
     if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
+    int dbg_slot = -1;
+    if (a.dbg) dbg_slot = blockIdx.x == 0 ? 0 : blockIdx.x == 1 ? 1 : blockIdx.x == gridDim.x / 2 ? 2 : blockIdx.x == gridDim.x - 1 ? 3 : -1;
+    long long* dbgs = dbg_slot >= 0 ? s.dbg : nullptr;
 
     RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
     const int nphase = MODEL == CRNN_MODEL_GRU ? 2 : 1;
+    const int rot = (a.rotate && !a.mcast && nkb % a.ckb == 0) ? (grp % (nkb / a.ckb)) * a.ckb : 0;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -505,22 +517,24 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb,
-                                   a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr);
+                                   a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr, rot,
+                                   (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
                     RT_STAMP(2);
                     ++phases_done;
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // the whole warp runs the issue loop (see mma_bf16_elect)
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_begin; t < a.t_end; ++t)
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
-                               (a.dbg && blockIdx.x == 0 && dbg_phase < 60) ? a.dbg + dbg_phase * 16 : nullptr, a.split);
-                    RT_STAMP(3);
+                        rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
+                               (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot);
+                    if (lane == 0) RT_STAMP(3);
                 }
         }
     } else {
@@ -536,71 +550,116 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
             float* hnext = a.hx + (int64_t)(t + 1) * BH;
             __nv_bfloat16* hnb = a.hxb + (int64_t)(t + 1) * BH;
             for (int ph = 0; ph < nphase; ++ph) {
+                // The batch in flight.  Declared here so that the LAST batch of the phase can keep its results in
+                // registers across the step barrier: only the bf16 rows other CTAs stream next (hxb / rsb) are
+                // stored before the release, everything this CTA alone reads later (fp32 h, c, the gate stash for
+                // BPTT) is stored after it - the release waits for every store issued before it.
+                EpiIdx e[UB];
+                float x0[UB], x1[UB], x2[UB], x3[UB], ax[UB], hv[UB];
+                bool pending = false;
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(128, bt - ps * 128);
                     const int nunits = nr * hcv;
                     const int b0row = b0 + ps * 128;
                     const int gstride = ph == 0 ? G1 : 1;
-                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * RT_UB) {
+                    const int64_t ob = (int64_t)b0row * H + j0;                  // [B,H] tensors
+                    float* gp = gt + (tB + b0row) * gw + j0;                     // gate stash rows of this pass
+                    const float* hp_ = hprev + ob;
+                    float* hn_ = hnext + ob;
+                    __nv_bfloat16* hb_ = hnb + ob;
+                    const float* cp_ = MODEL == CRNN_MODEL_LSTM ? a.cx + (int64_t)t * BH + ob : nullptr;
+                    float* cn_ = MODEL == CRNN_MODEL_LSTM ? a.cx + (int64_t)(t + 1) * BH + ob : nullptr;
+                    __nv_bfloat16* rs_ = MODEL == CRNN_MODEL_GRU ? a.rsb + (tB + b0row) * H + j0 : nullptr;
+                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * UB) {
+                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * UB >= nunits;
                         // ---- issue every global load of this batch before touching the accumulator
-                        EpiIdx e[RT_UB];
-                        float x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], ax[RT_UB];
 #pragma unroll
-                        for (int u = 0; u < RT_UB; ++u) {
-                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, gstride, b0row, j0, H, tB, kq * HC);
-                            x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = 0.f;
+                        for (int u = 0; u < UB; ++u) {
+                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, gstride, kq * HC);
+                            x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = hv[u] = 0.f;
                             if (e[u].ok) {
-                                const float* g = gt + e[u].row * gw + e[u].j;
+                                const float* g = gp + e[u].r * (int)gw + e[u].jj;
+                                const int o = e[u].r * H + e[u].jj;
                                 if (MODEL == CRNN_MODEL_LSTM) {
                                     x0[u] = g[0]; x1[u] = g[H]; x2[u] = g[2 * H]; x3[u] = g[3 * H];
-                                    ax[u] = a.cx[(int64_t)t * BH + e[u].o];
+                                    ax[u] = cp_[o];
                                 } else if (MODEL == CRNN_MODEL_RNN) {
                                     x0[u] = g[0];
                                 } else if (ph == 0) {
-                                    x0[u] = g[0]; x1[u] = g[H]; ax[u] = hprev[e[u].o];
+                                    x0[u] = g[0]; x1[u] = g[H]; ax[u] = hp_[o];
                                 } else {
-                                    x0[u] = g[2 * H]; x1[u] = g[H]; ax[u] = hprev[e[u].o];
+                                    x0[u] = g[2 * H]; x1[u] = g[H]; ax[u] = hp_[o];
                                 }
                             }
                         }
                         const int dbg_phase = (t - a.t_begin) * nphase + ph;
-                        if (epi_tid == 0) RT_STAMP(4);
-                        if (base == 0) RT_TAKE_ACC(nr, ph == 0 ? NCA : HCG);
-                        if (epi_tid == 0) RT_STAMP(5);
-                        float zv[RT_UB][4];
-                        if (ph == 0) rt_zgather<G1>(zv, e, Zs, zpeer, Q, kq);
-                        else         rt_zgather<1>(zv, e, Zs, zpeer, Q, kq);
+                        if (epi_tid == 0 && base == 0) RT_STAMP(4);
+                        if (base == 0) {
+                            if (dbgs) { mbar_wait(s.z_full, p.z_i & 1); if (epi_tid == 0) RT_STAMP(14); if (epi_tid == RT_EPI_THREADS - 1) RT_STAMP(15); }
+                            RT_TAKE_ACC(nr, ph == 0 ? NCA : HCG);
+                        }
+                        if (epi_tid == 0 && base == 0) RT_STAMP(5);
+                        float zv[UB][4];
+                        if (ph == 0) rt_zgather<G1, UB>(zv, e, Zs, zpeer, Q, kq);
+                        else         rt_zgather<1, UB>(zv, e, Zs, zpeer, Q, kq);
+                        if (dbgs && epi_tid == 0 && base == 0) {
+                            asm volatile("" ::"f"(zv[0][0]), "f"(zv[UB - 1][0]));
+                            RT_STAMP(16);                                          // accumulator values in registers
+                            asm volatile("" ::"f"(x0[0]), "f"(x0[UB - 1]), "f"(x1[0]), "f"(x1[UB - 1]));
+                            RT_STAMP(17);                                          // gate-stash loads have landed
+                            asm volatile("" ::"f"(ax[0]), "f"(ax[UB - 1]));
+                            RT_STAMP(18);                                          // previous state has landed
+                        }
+                        // ---- cell update; results replace the inputs in x0..x3 / ax / hv.  No branches in the math
+                        //      (inactive elements compute on zeros), so the UB dependency chains interleave.
 #pragma unroll
-                        for (int u = 0; u < RT_UB; ++u) {
-                            if (!e[u].ok) continue;
-                            float* g = gt + e[u].row * gw + e[u].j;
+                        for (int u = 0; u < UB; ++u) {
+                            if (a.expt & 2) { hv[u] = zv[u][0] + x0[u] + x1[u] + ax[u]; continue; }
                             if (MODEL == CRNN_MODEL_LSTM) {
-                                float si = fast_sigmoid(zv[u][0] + x0[u]);
-                                float tj = fast_tanh(zv[u][1] + x1[u]);
-                                float sf = fast_sigmoid(zv[u][2] + x2[u] + 1.0f);      // forget_bias
-                                float so = fast_sigmoid(zv[u][3] + x3[u]);
-                                float cn = fmaf(sf, ax[u], si * tj);
-                                float hn = so * fast_tanh(cn);
-                                hnext[e[u].o] = hn;
-                                store_bf16_split(hnb + e[u].o, a.hxb_lo, hn);
-                                a.cx[(int64_t)(t + 1) * BH + e[u].o] = cn;
-                                g[0] = si; g[H] = tj; g[2 * H] = sf; g[3 * H] = so;
+                                x0[u] = fast_sigmoid(zv[u][0] + x0[u]);                   // i
+                                x1[u] = fast_tanh(zv[u][1] + x1[u]);                      // j
+                                x2[u] = fast_sigmoid(zv[u][2] + x2[u] + 1.0f);            // f (forget_bias)
+                                x3[u] = fast_sigmoid(zv[u][3] + x3[u]);                   // o
+                                ax[u] = fmaf(x2[u], ax[u], x0[u] * x1[u]);                // c'
+                                hv[u] = x3[u] * fast_tanh(ax[u]);
                             } else if (MODEL == CRNN_MODEL_RNN) {
-                                float hn = fast_tanh(zv[u][0] + x0[u]);
-                                hnext[e[u].o] = hn;
-                                store_bf16_split(hnb + e[u].o, a.hxb_lo, hn);
+                                hv[u] = fast_tanh(zv[u][0] + x0[u]);
                             } else if (ph == 0) {
-                                float r_ = fast_sigmoid(zv[u][0] + x0[u]);
-                                float u_ = fast_sigmoid(zv[u][1] + x1[u]);
-                                float rs = r_ * ax[u];                                   // reset BEFORE the matmul
-                                store_bf16_split(a.rsb + e[u].row * H + e[u].j, a.rsb_lo, rs);
-                                g[0] = r_; g[H] = u_; g[3 * H] = rs;
+                                x0[u] = fast_sigmoid(zv[u][0] + x0[u]);                   // r
+                                x1[u] = fast_sigmoid(zv[u][1] + x1[u]);                   // u
+                                hv[u] = x0[u] * ax[u];                                    // reset BEFORE the matmul
                             } else {
-                                float cand = fast_tanh(zv[u][0] + x0[u]);
-                                float hn = fmaf(x1[u], ax[u] - cand, cand);              // u*h + (1-u)*cand
-                                hnext[e[u].o] = hn;
-                                store_bf16_split(hnb + e[u].o, a.hxb_lo, hn);
-                                g[2 * H] = cand;
+                                x0[u] = fast_tanh(zv[u][0] + x0[u]);                      // candidate
+                                hv[u] = fmaf(x1[u], ax[u] - x0[u], x0[u]);                // u*h + (1-u)*cand
+                            }
+                        }
+                        // the rows other CTAs stream in the next phase
+#pragma unroll
+                        for (int u = 0; u < UB; ++u) {
+                            if (!e[u].ok || (a.expt & 1)) continue;
+                            const int o = e[u].r * H + e[u].jj;
+                            if (MODEL == CRNN_MODEL_GRU && ph == 0) store_bf16_split(rs_ + o, a.rsb_lo, hv[u]);
+                            else                                    store_bf16_split(hb_ + o, a.hxb_lo, hv[u]);
+                        }
+                        pending = defer;
+                        if (!defer) {
+#pragma unroll
+                            for (int u = 0; u < UB; ++u) {
+                                if (!e[u].ok) continue;
+                                float* g = gp + e[u].r * (int)gw + e[u].jj;
+                                const int o = e[u].r * H + e[u].jj;
+                                if (MODEL == CRNN_MODEL_LSTM) {
+                                    hn_[o] = hv[u];
+                                    cn_[o] = ax[u];
+                                    g[0] = x0[u]; g[H] = x1[u]; g[2 * H] = x2[u]; g[3 * H] = x3[u];
+                                } else if (MODEL == CRNN_MODEL_RNN) {
+                                    hn_[o] = hv[u];
+                                } else if (ph == 0) {
+                                    g[0] = x0[u]; g[H] = x1[u]; g[3 * H] = hv[u];
+                                } else {
+                                    hn_[o] = hv[u];
+                                    g[2 * H] = x0[u];
+                                }
                             }
                         }
                     }
@@ -612,10 +671,34 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 if (epi_tid == 0) RT_STAMP(6);
                 if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
                 if (epi_tid == 0) RT_STAMP(7);
+                if (pending) {               // the stores nobody else waits for
+#pragma unroll
+                    for (int u = 0; u < UB; ++u) {
+                        if (!e[u].ok) continue;
+                        const int b0row = b0 + (a.npass - 1) * 128;                  // the deferred batch belongs to the last pass
+                        const int64_t ob = (int64_t)b0row * H + j0;
+                        float* g = gt + (tB + b0row) * gw + j0 + e[u].r * (int)gw + e[u].jj;
+                        const int o = e[u].r * H + e[u].jj;
+                        if (MODEL == CRNN_MODEL_LSTM) {
+                            hnext[ob + o] = hv[u];
+                            a.cx[(int64_t)(t + 1) * BH + ob + o] = ax[u];
+                            g[0] = x0[u]; g[H] = x1[u]; g[2 * H] = x2[u]; g[3 * H] = x3[u];
+                        } else if (MODEL == CRNN_MODEL_RNN) {
+                            hnext[ob + o] = hv[u];
+                        } else if (ph == 0) {
+                            g[0] = x0[u]; g[H] = x1[u]; g[3 * H] = hv[u];
+                        } else {
+                            hnext[ob + o] = hv[u];
+                            g[2 * H] = x0[u];
+                        }
+                    }
+                }
+                if (epi_tid == 0) RT_STAMP(13);
             }
         }
     }
     __syncthreads();
+    if (dbgs) for (int i = threadIdx.x; i < 192; i += RT_THREADS) a.dbg[dbg_slot * 192 + i] = dbgs[i];
     if (a.csize > 1) cluster_sync_all();             // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
@@ -627,7 +710,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
 // backward.  dh_t = dy_t + dz_{t+1} * W_h^T: the B operand is rows H+j0.. of the bf16 copy of
 // the cell kernel itself (K = gate columns, contiguous) - no packing needed.
 // ------------------------------------------------------------------------------------------
-template <int MODEL, bool FAST>
+template <int MODEL, bool FAST, int UB>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmZ0,   // dzb, first contraction
                                                                    const __grid_constant__ CUtensorMap tmZ1,   // gru: dzb candidate columns
                                                                    const __grid_constant__ CUtensorMap tmW0,
@@ -649,7 +732,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     const RtSmem s = rt_carve(smem_raw, (size_t)nsp * nkb0 * HCG * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nsp * nkb1 * HCG * 128 : 0, a.zs_floats, a.ring_bytes);
     float* Zs = s.zs;
     const int ldz = HCG + 1;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for ptxas
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
     const int grp = slice / Q, kq = slice % Q;
     const int jg0 = grp * HCG;                        // first unit of the group whose dh this CTA contracts
@@ -678,6 +761,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
 
     RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
+    const bool rot_on = a.rotate && !a.mcast;
+    const int rot0 = (rot_on && nkb0 % a.ckb == 0) ? (grp % (nkb0 / a.ckb)) * a.ckb : 0;
+    const int rot1 = (rot_on && nkb1 % a.ckb == 0) ? (grp % (nkb1 / a.ckb)) * a.ckb : 0;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -696,26 +782,27 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb0,
-                                   a.split ? &tmZ0l : nullptr);
+                                   a.split ? &tmZ0l : nullptr, rot0);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb1,
-                                   a.split ? &tmZ1l : nullptr);
+                                   a.split ? &tmZ1l : nullptr, rot1);
                     ++phases_done;
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // the whole warp runs the issue loop (see mma_bf16_elect)
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split, rot0);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split, rot1);
             }
         }
     } else {
@@ -734,67 +821,101 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         for (int t = a.t_end - 1; t >= a.t_begin; --t) {
             const bool has_next = t + 1 < a.S;
             const int64_t tB = (int64_t)t * B;
+            // Same split as the forward epilogue: only the bf16 dz rows other CTAs stream next are stored before the
+            // step barrier's release; fp32 dz (read by the weight-gradient GEMMs' bias sums after the kernel) and the
+            // carries (read back by the same thread) of the phase's last batch go out after it.
+            EpiIdx e[UB];
+            float v0[UB], v1[UB], v2[UB], v3[UB], v4[UB];
+            bool pending = false;
             for (int ps = 0; ps < a.npass; ++ps) {
                 const int nr = min(128, bt - ps * 128);
                 const int nunits = nr * hcv;
                 const int b0row = b0 + ps * 128;
-                for (int base = 0; base < nunits; base += RT_EPI_THREADS * RT_UB) {
-                    EpiIdx e[RT_UB];
-                    float dyv[RT_UB], x0[RT_UB], x1[RT_UB], x2[RT_UB], x3[RT_UB], c0v[RT_UB], c1v[RT_UB], cr[RT_UB];
+                const int64_t ob = (int64_t)b0row * H + j0;
+                const float* gp = a.gates + (tB + b0row) * gw + j0;
+                float* dzp = a.dz + (tB + b0row) * zw + j0;
+                __nv_bfloat16* dzbp = a.dzb + (tB + b0row) * zw + j0;
+                for (int base = 0; base < nunits; base += RT_EPI_THREADS * UB) {
+                    const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * UB >= nunits;
+                    float dyv[UB], c0v[UB], c1v[UB], cr[UB];
 #pragma unroll
-                    for (int u = 0; u < RT_UB; ++u) {
-                        e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB, kq * HC);
-                        dyv[u] = x0[u] = x1[u] = x2[u] = x3[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
+                    for (int u = 0; u < UB; ++u) {
+                        e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, kq * HC);
+                        dyv[u] = v0[u] = v1[u] = v2[u] = v3[u] = v4[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
                         if (e[u].ok) {
-                            const float* g = a.gates + e[u].row * gw + e[u].j;
-                            dyv[u] = a.dy[(int64_t)t * BH + e[u].o];
+                            const float* g = gp + e[u].r * (int)gw + e[u].jj;
+                            const int64_t o = ob + e[u].r * H + e[u].jj;
+                            dyv[u] = a.dy[(int64_t)t * BH + o];
                             if (MODEL == CRNN_MODEL_LSTM) {
-                                x0[u] = g[0]; x1[u] = g[H]; x2[u] = g[2 * H]; x3[u] = g[3 * H];
-                                c0v[u] = a.cx[(int64_t)t * BH + e[u].o];
-                                c1v[u] = a.cx[(int64_t)(t + 1) * BH + e[u].o];
-                                cr[u] = a.carry0[e[u].o];
+                                v0[u] = g[0]; v1[u] = g[H]; v2[u] = g[2 * H]; v3[u] = g[3 * H];
+                                c0v[u] = a.cx[(int64_t)t * BH + o];
+                                c1v[u] = a.cx[(int64_t)(t + 1) * BH + o];
+                                cr[u] = a.carry0[o];
                             } else if (MODEL == CRNN_MODEL_RNN) {
-                                x0[u] = a.hx[(int64_t)(t + 1) * BH + e[u].o];
+                                v0[u] = a.hx[(int64_t)(t + 1) * BH + o];
                             } else {
-                                x1[u] = g[H]; x2[u] = g[2 * H];
-                                c0v[u] = a.hx[(int64_t)t * BH + e[u].o];
-                                cr[u] = a.carry0[e[u].o];
+                                v1[u] = g[H]; v2[u] = g[2 * H];
+                                c0v[u] = a.hx[(int64_t)t * BH + o];
+                                cr[u] = a.carry0[o];
                             }
                         }
                     }
                     if (base == 0 && has_next) RT_TAKE_ACC(nr, HCG);
-                    float zv[RT_UB][4];
-                    if (has_next) rt_zgather<1>(zv, e, Zs, zpeer, Q, kq);
+                    float zv[UB][4];
+                    if (has_next) rt_zgather<1, UB>(zv, e, Zs, zpeer, Q, kq);
+                    // results: lstm v0..v3 = di,dj,df,dO, v4 = carry ; rnn v0 = d ; gru v1 = du, v2 = dc, v4 = dh
+                    // (branch-free math: the UB chains interleave)
 #pragma unroll
-                    for (int u = 0; u < RT_UB; ++u) {
-                        if (!e[u].ok) continue;
+                    for (int u = 0; u < UB; ++u) {
                         float dht = dyv[u] + (has_next ? zv[u][0] : 0.f);
-                        float* dz = a.dz + e[u].row * zw + e[u].j;
-                        __nv_bfloat16* dzb = a.dzb + e[u].row * zw + e[u].j;
                         if (MODEL == CRNN_MODEL_LSTM) {
-                            const float si = x0[u], tj = x1[u], sf = x2[u], so = x3[u];
+                            const float si = v0[u], tj = v1[u], sf = v2[u], so = v3[u];
                             const float tcn = fast_tanh(c1v[u]);
                             const float dct = cr[u] + dht * so * (1.0f - tcn * tcn);
-                            const float di = dct * tj * si * (1.0f - si);
-                            const float dj = dct * si * (1.0f - tj * tj);
-                            const float df = dct * c0v[u] * sf * (1.0f - sf);
-                            const float dO = dht * tcn * so * (1.0f - so);
-                            a.carry0[e[u].o] = dct * sf;
-                            dz[0] = di; dz[H] = dj; dz[2 * H] = df; dz[3 * H] = dO;
-                            store_bf16_split(dzb, a.dzb_lo, di); store_bf16_split(dzb + H, a.dzb_lo, dj);
-                            store_bf16_split(dzb + 2 * H, a.dzb_lo, df); store_bf16_split(dzb + 3 * H, a.dzb_lo, dO);
+                            v0[u] = dct * tj * si * (1.0f - si);
+                            v1[u] = dct * si * (1.0f - tj * tj);
+                            v2[u] = dct * c0v[u] * sf * (1.0f - sf);
+                            v3[u] = dht * tcn * so * (1.0f - so);
+                            v4[u] = dct * sf;
                         } else if (MODEL == CRNN_MODEL_RNN) {
-                            const float d = dht * (1.0f - x0[u] * x0[u]);
-                            dz[0] = d;
-                            store_bf16_split(dzb, a.dzb_lo, d);
+                            v0[u] = dht * (1.0f - v0[u] * v0[u]);
                         } else {
                             dht += cr[u];
-                            const float u_ = x1[u], cand = x2[u], hp = c0v[u];
-                            const float dc = dht * (1.0f - u_) * (1.0f - cand * cand);   // d candidate pre-activation
-                            const float du = dht * (hp - cand) * u_ * (1.0f - u_);       // d update-gate pre-activation
-                            dz[2 * H] = dc; dz[H] = du;
-                            store_bf16_split(dzb + 2 * H, a.dzb_lo, dc); store_bf16_split(dzb + H, a.dzb_lo, du);
-                            a.carry1[e[u].o] = dht;
+                            const float u_ = v1[u], cand = v2[u], hp = c0v[u];
+                            v2[u] = dht * (1.0f - u_) * (1.0f - cand * cand);     // d candidate pre-activation
+                            v1[u] = dht * (hp - cand) * u_ * (1.0f - u_);         // d update-gate pre-activation
+                            v4[u] = dht;
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < UB; ++u) {
+                        if (!e[u].ok) continue;
+                        __nv_bfloat16* dzb = dzbp + e[u].r * (int)zw + e[u].jj;
+                        if (MODEL == CRNN_MODEL_LSTM) {
+                            store_bf16_split(dzb, a.dzb_lo, v0[u]); store_bf16_split(dzb + H, a.dzb_lo, v1[u]);
+                            store_bf16_split(dzb + 2 * H, a.dzb_lo, v2[u]); store_bf16_split(dzb + 3 * H, a.dzb_lo, v3[u]);
+                        } else if (MODEL == CRNN_MODEL_RNN) {
+                            store_bf16_split(dzb, a.dzb_lo, v0[u]);
+                        } else {
+                            store_bf16_split(dzb + 2 * H, a.dzb_lo, v2[u]); store_bf16_split(dzb + H, a.dzb_lo, v1[u]);
+                        }
+                    }
+                    pending = defer;
+                    if (!defer) {
+#pragma unroll
+                        for (int u = 0; u < UB; ++u) {
+                            if (!e[u].ok) continue;
+                            float* dz = dzp + e[u].r * (int)zw + e[u].jj;
+                            const int64_t o = ob + e[u].r * H + e[u].jj;
+                            if (MODEL == CRNN_MODEL_LSTM) {
+                                a.carry0[o] = v4[u];
+                                dz[0] = v0[u]; dz[H] = v1[u]; dz[2 * H] = v2[u]; dz[3 * H] = v3[u];
+                            } else if (MODEL == CRNN_MODEL_RNN) {
+                                dz[0] = v0[u];
+                            } else {
+                                dz[2 * H] = v2[u]; dz[H] = v1[u];
+                                a.carry1[o] = v4[u];
+                            }
                         }
                     }
                 }
@@ -802,43 +923,89 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (has_next) RT_RELEASE_PARTIALS();
             }
             if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+            if (pending) {
+                const int b0row = b0 + (a.npass - 1) * 128;
+                const int64_t ob = (int64_t)b0row * H + j0;
+                float* dzp = a.dz + (tB + b0row) * zw + j0;
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    if (!e[u].ok) continue;
+                    float* dz = dzp + e[u].r * (int)zw + e[u].jj;
+                    const int64_t o = ob + e[u].r * H + e[u].jj;
+                    if (MODEL == CRNN_MODEL_LSTM) {
+                        a.carry0[o] = v4[u];
+                        dz[0] = v0[u]; dz[H] = v1[u]; dz[2 * H] = v2[u]; dz[3 * H] = v3[u];
+                    } else if (MODEL == CRNN_MODEL_RNN) {
+                        dz[0] = v0[u];
+                    } else {
+                        dz[2 * H] = v2[u]; dz[H] = v1[u];
+                        a.carry1[o] = v4[u];
+                    }
+                }
+            }
             if (MODEL == CRNN_MODEL_GRU) {
+                pending = false;
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(128, bt - ps * 128);
                     const int nunits = nr * hcv;
                     const int b0row = b0 + ps * 128;
-                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * RT_UB) {
-                        EpiIdx e[RT_UB];
-                        float x0[RT_UB], x1[RT_UB], hp[RT_UB], c1v[RT_UB];
+                    const int64_t ob = (int64_t)b0row * H + j0;
+                    const float* gp = a.gates + (tB + b0row) * gw + j0;
+                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * UB) {
+                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * UB >= nunits;
+                        float hp[UB], c1v[UB];
 #pragma unroll
-                        for (int u = 0; u < RT_UB; ++u) {
-                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, b0row, j0, H, tB, kq * HC);
-                            x0[u] = x1[u] = hp[u] = c1v[u] = 0.f;
+                        for (int u = 0; u < UB; ++u) {
+                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, kq * HC);
+                            v0[u] = v1[u] = hp[u] = c1v[u] = 0.f;
                             if (e[u].ok) {
-                                const float* g = a.gates + e[u].row * gw + e[u].j;
-                                x0[u] = g[0]; x1[u] = g[H];
-                                hp[u] = a.hx[(int64_t)t * BH + e[u].o];
-                                c1v[u] = a.carry1[e[u].o];
+                                const float* g = gp + e[u].r * (int)gw + e[u].jj;
+                                const int64_t o = ob + e[u].r * H + e[u].jj;
+                                v0[u] = g[0]; v1[u] = g[H];
+                                hp[u] = a.hx[(int64_t)t * BH + o];
+                                c1v[u] = a.carry1[o];
                             }
                         }
                         if (base == 0) RT_TAKE_ACC(nr, HCG);
-                        float zv[RT_UB][4];
-                        rt_zgather<1>(zv, e, Zs, zpeer, Q, kq);
+                        float zv[UB][4];
+                        rt_zgather<1, UB>(zv, e, Zs, zpeer, Q, kq);
+                        // results: v0 = dr, v4 = carry into step t-1
 #pragma unroll
-                        for (int u = 0; u < RT_UB; ++u) {
-                            if (!e[u].ok) continue;
+                        for (int u = 0; u < UB; ++u) {
                             const float drs = zv[u][0];
-                            const float r_ = x0[u], u_ = x1[u];
-                            const float dr = drs * hp[u] * r_ * (1.0f - r_);
-                            a.dz[e[u].row * zw + e[u].j] = dr;
-                            store_bf16_split(a.dzb + e[u].row * zw + e[u].j, a.dzb_lo, dr);
-                            a.carry0[e[u].o] = fmaf(c1v[u], u_, drs * r_);
+                            const float r_ = v0[u], u_ = v1[u];
+                            v0[u] = drs * hp[u] * r_ * (1.0f - r_);
+                            v4[u] = fmaf(c1v[u], u_, drs * r_);
+                        }
+#pragma unroll
+                        for (int u = 0; u < UB; ++u) {
+                            if (!e[u].ok) continue;
+                            store_bf16_split(a.dzb + (tB + b0row) * zw + j0 + e[u].r * (int)zw + e[u].jj, a.dzb_lo, v0[u]);
+                        }
+                        pending = defer;
+                        if (!defer) {
+#pragma unroll
+                            for (int u = 0; u < UB; ++u) {
+                                if (!e[u].ok) continue;
+                                a.dz[(tB + b0row) * zw + j0 + e[u].r * (int)zw + e[u].jj] = v0[u];
+                                a.carry0[ob + e[u].r * H + e[u].jj] = v4[u];
+                            }
                         }
                     }
                     epi_bar_sync();
                     RT_RELEASE_PARTIALS();
                 }
                 if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+                if (pending) {
+                    const int b0row = b0 + (a.npass - 1) * 128;
+                    const int64_t ob = (int64_t)b0row * H + j0;
+#pragma unroll
+                    for (int u = 0; u < UB; ++u) {
+                        if (!e[u].ok) continue;
+                        a.dz[(tB + b0row) * zw + j0 + e[u].r * (int)zw + e[u].jj] = v0[u];
+                        a.carry0[ob + e[u].r * H + e[u].jj] = v4[u];
+                    }
+                }
             }
         }
     }

@@ -9,11 +9,13 @@ rng=np.random.default_rng(0)
 x=rng.integers(0,96,(256,50)).astype(np.int32); y=rng.integers(0,96,(256,50)).astype(np.int32)
 for _ in range(3): m.step(x,y)
 torch.cuda.synchronize()
-d=m.workspace[24576:24576+8*16*60].view(torch.int64).cpu().numpy().reshape(60,16)
-# phases 20..39
-base=d[20,0]
-names=['prod_start','await_done','tma_issued','mma_done','epi_loaded','acc_taken','epi_synced','published','w0_computed','w3_computed','mma_zempty','mma_full0','mma_full1']
-print(names)
+d=m.workspace[24576:24576+8*4*192].view(torch.int64).cpu().numpy().reshape(4,8,24)
+names=['prod_start','await_done','tma_issued','mma_issued','epi_at_wait','acc_taken','epi_synced','published','w0_computed','w9_computed','mma_zempty','mma_full_first','mma_full_last','deferred_done','zfull_seen_t0','zfull_seen_t255','zv_in_regs','gates_landed','state_landed','p_empty0','p_issued0','p_empty1','p_issued1','-']
 print('precision',prec,'env',{k:v for k,v in os.environ.items() if k.startswith('CRNN_')})
-for p in range(20,28):
-    print(p, [int(v-d[p,0]) for v in d[p][:13]], 'phase_len', int(d[p+1,0]-d[p,0]))
+print('stamps are relative to the producer\'s await_done of the same phase (the moment every CTA has published the previous phase)')
+order=[0,10,19,20,21,22,2,11,12,3,4,14,5,16,8,6,7,13]
+print('cta ph | '+' '.join('%s'%names[i][:12].rjust(12) for i in order)+' | phase_len')
+for c in (0,3):
+    for p in range(1,7):
+        ref=d[c,p,1]
+        print(c,p,'|',' '.join(str(int(d[c,p,i]-ref)).rjust(12) for i in order),'|',int(d[c,p+1,1]-d[c,p,1]))
