@@ -273,6 +273,18 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         };
         grow(&o->smem_fwd, &o->ring_fwd);
         grow(&o->smem_bwd, &o->ring_bwd);
+        // One TMA instruction per phase when the phase's whole K extent of streamed rows fits: the loads of a phase
+        // do not overlap each other in practice (measured: 2 x 32 KB complete 1.3 k and 3.0 k cycles after issue, one
+        // 64 KB load after 1.6 k), so the ring is grown to hold the H extent as a single stage where that is possible.
+        if (env_int("CRNN_TC_ONE_STAGE", 1) && o->npass == 1) {
+            const int tile = tc::rt_tile_bytes(o->box_rows);
+            auto one = [&](size_t* smem, int* ring, int q) {
+                const int want = ((nkb / q) * tile * (1 + h->split) + tc::RT_MROWS_BYTES - tile + 1023) & ~1023;
+                if (want > *ring && want <= 96 * 1024 && (int)*smem + (want - *ring) <= h->max_smem) { *smem += (size_t)(want - *ring); *ring = want; }
+            };
+            one(&o->smem_fwd, &o->ring_fwd, o->q_fwd);
+            one(&o->smem_bwd, &o->ring_bwd, o->q_bwd);
+        }
         return true;
     };
     // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
@@ -716,6 +728,11 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // ring geometry is per launch (every contraction of the kernel shares the ring and its barriers):
     // sized for the shortest K extent, H
     a.ckb = tc::rt_chunk_kb(p.box_rows, ceil_div(H, 64), split);
+    a.ring_bytes = backward ? p.ring_bwd : p.ring_fwd;
+    {   // the whole H extent (of this CTA's K part) as one stage when the ring holds it
+        const int nkb_h = ceil_div(H, 64) / Q, tile = tc::rt_tile_bytes(p.box_rows);
+        if (env_int("CRNN_TC_ONE_STAGE", 1) && p.npass == 1 && nkb_h * tile * (1 + split) + tc::RT_MROWS_BYTES - tile <= a.ring_bytes) a.ckb = nkb_h;
+    }
     { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) a.ckb = std::min(ck_env, ceil_div(H, 64)); }
     a.rotate = env_int("CRNN_TC_ROTATE", 0);
     a.ring_bytes = backward ? p.ring_bwd : p.ring_fwd;
@@ -762,9 +779,17 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const bool ub8 = per_pass > tc::RT_EPI_THREADS * 4 && env_int("CRNN_TC_UB8", 1);
     a.defer = env_int("CRNN_TC_DEFER", 1);
     a.expt = env_int("CRNN_TC_EXPT", 0);
-    void (*fn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs) =
-        h->fast_act ? (backward ? (ub8 ? tc::rec_bwd_tc_kernel<MODEL, true, 8> : tc::rec_bwd_tc_kernel<MODEL, true, 4>) : (ub8 ? tc::rec_fwd_tc_kernel<MODEL, true, 8> : tc::rec_fwd_tc_kernel<MODEL, true, 4>))
-                    : (backward ? (ub8 ? tc::rec_bwd_tc_kernel<MODEL, false, 8> : tc::rec_bwd_tc_kernel<MODEL, false, 4>) : (ub8 ? tc::rec_fwd_tc_kernel<MODEL, false, 8> : tc::rec_fwd_tc_kernel<MODEL, false, 4>));
+    // K-split launches read their partial sums from distributed shared memory; there consecutive lanes on consecutive
+    // units (scalar epilogue) beat quads (config 4 BPTT 5.4 vs 6.6 ms, split-precision config 3 BPTT 2.9 vs 3.6 ms)
+    const bool vec4 = env_int("CRNN_TC_VEC4", Q > 1 ? 0 : 1) != 0;
+    typedef void (*RecFn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs);
+    RecFn fn;
+#define CRNN_PICK(KERNEL, F)                                                                                   \
+    (ub8 ? (vec4 ? (RecFn)tc::KERNEL<MODEL, F, 8, 4> : (RecFn)tc::KERNEL<MODEL, F, 8, 1>)                       \
+         : (vec4 ? (RecFn)tc::KERNEL<MODEL, F, 4, 4> : (RecFn)tc::KERNEL<MODEL, F, 4, 1>))
+    if (h->fast_act) fn = backward ? CRNN_PICK(rec_bwd_tc_kernel, true) : CRNN_PICK(rec_fwd_tc_kernel, true);
+    else             fn = backward ? CRNN_PICK(rec_bwd_tc_kernel, false) : CRNN_PICK(rec_fwd_tc_kernel, false);
+#undef CRNN_PICK
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // Optional clusters along the slice index (CRNN_TC_CLUSTER=2|4|8): the CTAs of a cluster work on the

@@ -365,35 +365,64 @@ __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane
 }
 
 
-// Element -> (row, unit) mapping shared by all epilogues: consecutive threads take consecutive
-// hidden units of one batch row, so every global access of a warp is one contiguous segment.
-// Offsets are 32-bit and relative to per-pass base pointers (r < 128): r*H + jj into [B,H] tensors,
-// r*gw + jj into the gate stash, r*zw + jj into dz.
+// Element -> (row, 4 consecutive units) mapping shared by all epilogues: a thread owns QUADS of adjacent
+// hidden units of one batch row, so every global access is a 16-byte vector (8 bytes for bf16) and a warp's
+// accesses cover whole contiguous segments.  Offsets are 32-bit and relative to per-pass base pointers
+// (r < 128): r*H + jj into [B,H] tensors, r*gw + jj into the gate stash, r*zw + jj into dz.
 struct EpiIdx {
     bool ok;
-    int r, jj;       // batch row inside the pass, unit inside the slice
-    int zi;          // r*ldz + (jcol0 + jj)*gstride: index of the unit's first accumulator column in Zs
+    int r, jj;       // batch row inside the pass, first unit of the quad inside the slice (multiple of 4)
+    int zi;          // r*ldz + (jcol0 + jj)*gstride: Zs index of the quad's first accumulator column
 };
-__device__ __forceinline__ EpiIdx epi_index(int idx, int nunits, int hcv, int ldz, int gstride, int jcol0 = 0) {
+template <int VEC>
+__device__ __forceinline__ EpiIdx epi_index(int idx, int nquads, int hq, int ldz, int gstride, int jcol0 = 0) {
     EpiIdx e;
-    e.ok = idx < nunits;
-    e.r = e.ok ? idx / hcv : 0;
-    e.jj = e.ok ? idx - e.r * hcv : 0;
+    e.ok = idx < nquads;
+    e.r = e.ok ? idx / hq : 0;
+    e.jj = e.ok ? VEC * (idx - e.r * hq) : 0;
     e.zi = e.r * ldz + (jcol0 + e.jj) * gstride;
     return e;
 }
+// VEC = 4: 16-byte vectors (8 bytes for bf16); VEC = 1: scalars (the K-split kernels, whose partial sums are read
+// from distributed shared memory unit by unit with consecutive lanes on consecutive units)
+template <int VEC>
+__device__ __forceinline__ void ldv(const float* __restrict__ p, float* dst) {
+    if (VEC == 4) { const float4 v = *reinterpret_cast<const float4*>(p); dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w; }
+    else dst[0] = p[0];
+}
+template <int VEC>
+__device__ __forceinline__ void stv(float* __restrict__ p, const float* src) {
+    if (VEC == 4) *reinterpret_cast<float4*>(p) = make_float4(src[0], src[1], src[2], src[3]);
+    else p[0] = src[0];
+}
+// adjacent bf16 (one 8-byte store for four), plus the lo twins when lo_ofs != 0 (see store_bf16_split)
+template <int VEC>
+__device__ __forceinline__ void stv_bf16_split(__nv_bfloat16* __restrict__ p, int64_t lo_ofs, const float* v) {
+    if (VEC == 1) { store_bf16_split(p, lo_ofs, v[0]); return; }
+    const __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[VEC > 1 ? 1 : 0]), h1 = __floats2bfloat162_rn(v[VEC > 2 ? 2 : 0], v[VEC > 3 ? 3 : 0]);
+    uint2 w;
+    w.x = *reinterpret_cast<const uint32_t*>(&h0); w.y = *reinterpret_cast<const uint32_t*>(&h1);
+    *reinterpret_cast<uint2*>(p) = w;
+    if (lo_ofs) {
+        const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+        const __nv_bfloat162 l0 = __floats2bfloat162_rn(v[0] - f0.x, v[VEC > 1 ? 1 : 0] - f0.y),
+                             l1 = __floats2bfloat162_rn(v[VEC > 2 ? 2 : 0] - f1.x, v[VEC > 3 ? 3 : 0] - f1.y);
+        w.x = *reinterpret_cast<const uint32_t*>(&l0); w.y = *reinterpret_cast<const uint32_t*>(&l1);
+        *reinterpret_cast<uint2*>(p + lo_ofs) = w;
+    }
+}
 
-// Accumulator values of a batch of elements: NV consecutive columns per element, summed over the K
-// parts (cluster ranks, always in rank order).  All remote loads are issued before any is consumed,
-// so their distributed-shared-memory latencies overlap instead of adding up.
-template <int NV, int UB>
-__device__ __forceinline__ void rt_zgather(float (&zv)[UB][4], const EpiIdx (&e)[UB], const float* __restrict__ Zs,
+// Accumulator values of a batch of quads: NV consecutive columns per unit, `gstride` columns from unit to unit,
+// summed over the K parts (cluster ranks, always in rank order).  All remote loads are issued before any is
+// consumed, so their distributed-shared-memory latencies overlap instead of adding up.
+template <int NV, int UB, int VEC>
+__device__ __forceinline__ void rt_zgather(float (&zv)[UB][4], const EpiIdx (&e)[UB / VEC], int gstride, const float* __restrict__ Zs,
                                            const uint32_t* zpeer, int Q, int kq) {
     if (Q == 1) {
 #pragma unroll
         for (int u = 0; u < UB; ++u)
 #pragma unroll
-            for (int k = 0; k < NV; ++k) zv[u][k] = e[u].ok ? Zs[e[u].zi + k] : 0.f;
+            for (int k = 0; k < NV; ++k) zv[u][k] = e[u / VEC].ok ? Zs[e[u / VEC].zi + (u % VEC) * gstride + k] : 0.f;
         return;
     }
     float part[UB][NV][4];
@@ -404,7 +433,8 @@ __device__ __forceinline__ void rt_zgather(float (&zv)[UB][4], const EpiIdx (&e)
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
                 float v = 0.f;
-                if (r < Q && e[u].ok) v = (r == kq) ? Zs[e[u].zi + k] : ld_dsmem_f32(zpeer[r] + 4u * (uint32_t)(e[u].zi + k));
+                const int zi = e[u / VEC].zi + (u % VEC) * gstride + k;
+                if (r < Q && e[u / VEC].ok) v = (r == kq) ? Zs[zi] : ld_dsmem_f32(zpeer[r] + 4u * (uint32_t)zi);
                 part[u][k][r] = v;
             }
 #pragma unroll
@@ -441,7 +471,7 @@ __device__ __forceinline__ void rt_zgather(float (&zv)[UB][4], const EpiIdx (&e)
 // of W_h this CTA's local column lc contracts with, K contiguous.  lc = jj*G1 + g for the first
 // contraction; GRU candidate rows follow at lc = 2*HC + jj.
 // ------------------------------------------------------------------------------------------
-template <int MODEL, bool FAST, int UB>
+template <int MODEL, bool FAST, int UB, int VEC>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmH,
                                                                    const __grid_constant__ CUtensorMap tmRS,
                                                                    const __grid_constant__ CUtensorMap tmW0,
@@ -554,12 +584,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 // registers across the step barrier: only the bf16 rows other CTAs stream next (hxb / rsb) are
                 // stored before the release, everything this CTA alone reads later (fp32 h, c, the gate stash for
                 // BPTT) is stored after it - the release waits for every store issued before it.
-                EpiIdx e[UB];
+                EpiIdx e[UB / VEC];
                 float x0[UB], x1[UB], x2[UB], x3[UB], ax[UB], hv[UB];
                 bool pending = false;
+                const int hq = hcv / VEC;                                        // vectors per row of the slice
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(128, bt - ps * 128);
-                    const int nunits = nr * hcv;
+                    const int nquads = nr * hq;
                     const int b0row = b0 + ps * 128;
                     const int gstride = ph == 0 ? G1 : 1;
                     const int64_t ob = (int64_t)b0row * H + j0;                  // [B,H] tensors
@@ -570,25 +601,26 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     const float* cp_ = MODEL == CRNN_MODEL_LSTM ? a.cx + (int64_t)t * BH + ob : nullptr;
                     float* cn_ = MODEL == CRNN_MODEL_LSTM ? a.cx + (int64_t)(t + 1) * BH + ob : nullptr;
                     __nv_bfloat16* rs_ = MODEL == CRNN_MODEL_GRU ? a.rsb + (tB + b0row) * H + j0 : nullptr;
-                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * UB) {
-                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * UB >= nunits;
+                    for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {
+                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
                         // ---- issue every global load of this batch before touching the accumulator
 #pragma unroll
-                        for (int u = 0; u < UB; ++u) {
-                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, gstride, kq * HC);
-                            x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = hv[u] = 0.f;
-                            if (e[u].ok) {
-                                const float* g = gp + e[u].r * (int)gw + e[u].jj;
-                                const int o = e[u].r * H + e[u].jj;
+                        for (int u = 0; u < UB; ++u) x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = hv[u] = 0.f;
+#pragma unroll
+                        for (int qd = 0; qd < UB / VEC; ++qd) {
+                            e[qd] = epi_index<VEC>(base + qd * RT_EPI_THREADS + epi_tid, nquads, hq, ldz, gstride, kq * HC);
+                            if (e[qd].ok) {
+                                const float* g = gp + e[qd].r * (int)gw + e[qd].jj;
+                                const int o = e[qd].r * H + e[qd].jj;
                                 if (MODEL == CRNN_MODEL_LSTM) {
-                                    x0[u] = g[0]; x1[u] = g[H]; x2[u] = g[2 * H]; x3[u] = g[3 * H];
-                                    ax[u] = cp_[o];
+                                    ldv<VEC>(g, x0 + VEC * qd); ldv<VEC>(g + H, x1 + VEC * qd); ldv<VEC>(g + 2 * H, x2 + VEC * qd); ldv<VEC>(g + 3 * H, x3 + VEC * qd);
+                                    ldv<VEC>(cp_ + o, ax + VEC * qd);
                                 } else if (MODEL == CRNN_MODEL_RNN) {
-                                    x0[u] = g[0];
+                                    ldv<VEC>(g, x0 + VEC * qd);
                                 } else if (ph == 0) {
-                                    x0[u] = g[0]; x1[u] = g[H]; ax[u] = hp_[o];
+                                    ldv<VEC>(g, x0 + VEC * qd); ldv<VEC>(g + H, x1 + VEC * qd); ldv<VEC>(hp_ + o, ax + VEC * qd);
                                 } else {
-                                    x0[u] = g[2 * H]; x1[u] = g[H]; ax[u] = hp_[o];
+                                    ldv<VEC>(g + 2 * H, x0 + VEC * qd); ldv<VEC>(g + H, x1 + VEC * qd); ldv<VEC>(hp_ + o, ax + VEC * qd);
                                 }
                             }
                         }
@@ -600,8 +632,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         }
                         if (epi_tid == 0 && base == 0) RT_STAMP(5);
                         float zv[UB][4];
-                        if (ph == 0) rt_zgather<G1, UB>(zv, e, Zs, zpeer, Q, kq);
-                        else         rt_zgather<1, UB>(zv, e, Zs, zpeer, Q, kq);
+                        if (ph == 0) rt_zgather<G1, UB, VEC>(zv, e, gstride, Zs, zpeer, Q, kq);
+                        else         rt_zgather<1, UB, VEC>(zv, e, gstride, Zs, zpeer, Q, kq);
                         if (dbgs && epi_tid == 0 && base == 0) {
                             asm volatile("" ::"f"(zv[0][0]), "f"(zv[UB - 1][0]));
                             RT_STAMP(16);                                          // accumulator values in registers
@@ -635,30 +667,30 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         }
                         // the rows other CTAs stream in the next phase
 #pragma unroll
-                        for (int u = 0; u < UB; ++u) {
-                            if (!e[u].ok || (a.expt & 1)) continue;
-                            const int o = e[u].r * H + e[u].jj;
-                            if (MODEL == CRNN_MODEL_GRU && ph == 0) store_bf16_split(rs_ + o, a.rsb_lo, hv[u]);
-                            else                                    store_bf16_split(hb_ + o, a.hxb_lo, hv[u]);
+                        for (int qd = 0; qd < UB / VEC; ++qd) {
+                            if (!e[qd].ok || (a.expt & 1)) continue;
+                            const int o = e[qd].r * H + e[qd].jj;
+                            if (MODEL == CRNN_MODEL_GRU && ph == 0) stv_bf16_split<VEC>(rs_ + o, a.rsb_lo, hv + VEC * qd);
+                            else                                    stv_bf16_split<VEC>(hb_ + o, a.hxb_lo, hv + VEC * qd);
                         }
                         pending = defer;
                         if (!defer) {
 #pragma unroll
-                            for (int u = 0; u < UB; ++u) {
-                                if (!e[u].ok) continue;
-                                float* g = gp + e[u].r * (int)gw + e[u].jj;
-                                const int o = e[u].r * H + e[u].jj;
+                            for (int qd = 0; qd < UB / VEC; ++qd) {
+                                if (!e[qd].ok) continue;
+                                float* g = gp + e[qd].r * (int)gw + e[qd].jj;
+                                const int o = e[qd].r * H + e[qd].jj;
                                 if (MODEL == CRNN_MODEL_LSTM) {
-                                    hn_[o] = hv[u];
-                                    cn_[o] = ax[u];
-                                    g[0] = x0[u]; g[H] = x1[u]; g[2 * H] = x2[u]; g[3 * H] = x3[u];
+                                    stv<VEC>(hn_ + o, hv + VEC * qd);
+                                    stv<VEC>(cn_ + o, ax + VEC * qd);
+                                    stv<VEC>(g, x0 + VEC * qd); stv<VEC>(g + H, x1 + VEC * qd); stv<VEC>(g + 2 * H, x2 + VEC * qd); stv<VEC>(g + 3 * H, x3 + VEC * qd);
                                 } else if (MODEL == CRNN_MODEL_RNN) {
-                                    hn_[o] = hv[u];
+                                    stv<VEC>(hn_ + o, hv + VEC * qd);
                                 } else if (ph == 0) {
-                                    g[0] = x0[u]; g[H] = x1[u]; g[3 * H] = hv[u];
+                                    stv<VEC>(g, x0 + VEC * qd); stv<VEC>(g + H, x1 + VEC * qd); stv<VEC>(g + 3 * H, hv + VEC * qd);
                                 } else {
-                                    hn_[o] = hv[u];
-                                    g[2 * H] = x0[u];
+                                    stv<VEC>(hn_ + o, hv + VEC * qd);
+                                    stv<VEC>(g + 2 * H, x0 + VEC * qd);
                                 }
                             }
                         }
@@ -672,24 +704,24 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
                 if (epi_tid == 0) RT_STAMP(7);
                 if (pending) {               // the stores nobody else waits for
+                    const int b0row = b0 + (a.npass - 1) * 128;                  // the deferred batch belongs to the last pass
+                    const int64_t ob = (int64_t)b0row * H + j0;
 #pragma unroll
-                    for (int u = 0; u < UB; ++u) {
-                        if (!e[u].ok) continue;
-                        const int b0row = b0 + (a.npass - 1) * 128;                  // the deferred batch belongs to the last pass
-                        const int64_t ob = (int64_t)b0row * H + j0;
-                        float* g = gt + (tB + b0row) * gw + j0 + e[u].r * (int)gw + e[u].jj;
-                        const int o = e[u].r * H + e[u].jj;
+                    for (int qd = 0; qd < UB / VEC; ++qd) {
+                        if (!e[qd].ok) continue;
+                        float* g = gt + (tB + b0row) * gw + j0 + e[qd].r * (int)gw + e[qd].jj;
+                        const int64_t o = ob + e[qd].r * H + e[qd].jj;
                         if (MODEL == CRNN_MODEL_LSTM) {
-                            hnext[ob + o] = hv[u];
-                            a.cx[(int64_t)(t + 1) * BH + ob + o] = ax[u];
-                            g[0] = x0[u]; g[H] = x1[u]; g[2 * H] = x2[u]; g[3 * H] = x3[u];
+                            stv<VEC>(hnext + o, hv + VEC * qd);
+                            stv<VEC>(a.cx + (int64_t)(t + 1) * BH + o, ax + VEC * qd);
+                            stv<VEC>(g, x0 + VEC * qd); stv<VEC>(g + H, x1 + VEC * qd); stv<VEC>(g + 2 * H, x2 + VEC * qd); stv<VEC>(g + 3 * H, x3 + VEC * qd);
                         } else if (MODEL == CRNN_MODEL_RNN) {
-                            hnext[ob + o] = hv[u];
+                            stv<VEC>(hnext + o, hv + VEC * qd);
                         } else if (ph == 0) {
-                            g[0] = x0[u]; g[H] = x1[u]; g[3 * H] = hv[u];
+                            stv<VEC>(g, x0 + VEC * qd); stv<VEC>(g + H, x1 + VEC * qd); stv<VEC>(g + 3 * H, hv + VEC * qd);
                         } else {
-                            hnext[ob + o] = hv[u];
-                            g[2 * H] = x0[u];
+                            stv<VEC>(hnext + o, hv + VEC * qd);
+                            stv<VEC>(g + 2 * H, x0 + VEC * qd);
                         }
                     }
                 }
@@ -710,7 +742,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
 // backward.  dh_t = dy_t + dz_{t+1} * W_h^T: the B operand is rows H+j0.. of the bf16 copy of
 // the cell kernel itself (K = gate columns, contiguous) - no packing needed.
 // ------------------------------------------------------------------------------------------
-template <int MODEL, bool FAST, int UB>
+template <int MODEL, bool FAST, int UB, int VEC>
 __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmZ0,   // dzb, first contraction
                                                                    const __grid_constant__ CUtensorMap tmZ1,   // gru: dzb candidate columns
                                                                    const __grid_constant__ CUtensorMap tmW0,
@@ -824,45 +856,47 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             // Same split as the forward epilogue: only the bf16 dz rows other CTAs stream next are stored before the
             // step barrier's release; fp32 dz (read by the weight-gradient GEMMs' bias sums after the kernel) and the
             // carries (read back by the same thread) of the phase's last batch go out after it.
-            EpiIdx e[UB];
+            EpiIdx e[UB / VEC];
             float v0[UB], v1[UB], v2[UB], v3[UB], v4[UB];
             bool pending = false;
+            const int hq = hcv / VEC;
             for (int ps = 0; ps < a.npass; ++ps) {
                 const int nr = min(128, bt - ps * 128);
-                const int nunits = nr * hcv;
+                const int nquads = nr * hq;
                 const int b0row = b0 + ps * 128;
                 const int64_t ob = (int64_t)b0row * H + j0;
                 const float* gp = a.gates + (tB + b0row) * gw + j0;
                 float* dzp = a.dz + (tB + b0row) * zw + j0;
                 __nv_bfloat16* dzbp = a.dzb + (tB + b0row) * zw + j0;
-                for (int base = 0; base < nunits; base += RT_EPI_THREADS * UB) {
-                    const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * UB >= nunits;
+                for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {
+                    const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
                     float dyv[UB], c0v[UB], c1v[UB], cr[UB];
 #pragma unroll
-                    for (int u = 0; u < UB; ++u) {
-                        e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, kq * HC);
-                        dyv[u] = v0[u] = v1[u] = v2[u] = v3[u] = v4[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
-                        if (e[u].ok) {
-                            const float* g = gp + e[u].r * (int)gw + e[u].jj;
-                            const int64_t o = ob + e[u].r * H + e[u].jj;
-                            dyv[u] = a.dy[(int64_t)t * BH + o];
+                    for (int u = 0; u < UB; ++u) dyv[u] = v0[u] = v1[u] = v2[u] = v3[u] = v4[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
+#pragma unroll
+                    for (int qd = 0; qd < UB / VEC; ++qd) {
+                        e[qd] = epi_index<VEC>(base + qd * RT_EPI_THREADS + epi_tid, nquads, hq, ldz, 1, kq * HC);
+                        if (e[qd].ok) {
+                            const float* g = gp + e[qd].r * (int)gw + e[qd].jj;
+                            const int64_t o = ob + e[qd].r * H + e[qd].jj;
+                            ldv<VEC>(a.dy + (int64_t)t * BH + o, dyv + VEC * qd);
                             if (MODEL == CRNN_MODEL_LSTM) {
-                                v0[u] = g[0]; v1[u] = g[H]; v2[u] = g[2 * H]; v3[u] = g[3 * H];
-                                c0v[u] = a.cx[(int64_t)t * BH + o];
-                                c1v[u] = a.cx[(int64_t)(t + 1) * BH + o];
-                                cr[u] = a.carry0[o];
+                                ldv<VEC>(g, v0 + VEC * qd); ldv<VEC>(g + H, v1 + VEC * qd); ldv<VEC>(g + 2 * H, v2 + VEC * qd); ldv<VEC>(g + 3 * H, v3 + VEC * qd);
+                                ldv<VEC>(a.cx + (int64_t)t * BH + o, c0v + VEC * qd);
+                                ldv<VEC>(a.cx + (int64_t)(t + 1) * BH + o, c1v + VEC * qd);
+                                ldv<VEC>(a.carry0 + o, cr + VEC * qd);
                             } else if (MODEL == CRNN_MODEL_RNN) {
-                                v0[u] = a.hx[(int64_t)(t + 1) * BH + o];
+                                ldv<VEC>(a.hx + (int64_t)(t + 1) * BH + o, v0 + VEC * qd);
                             } else {
-                                v1[u] = g[H]; v2[u] = g[2 * H];
-                                c0v[u] = a.hx[(int64_t)t * BH + o];
-                                cr[u] = a.carry0[o];
+                                ldv<VEC>(g + H, v1 + VEC * qd); ldv<VEC>(g + 2 * H, v2 + VEC * qd);
+                                ldv<VEC>(a.hx + (int64_t)t * BH + o, c0v + VEC * qd);
+                                ldv<VEC>(a.carry0 + o, cr + VEC * qd);
                             }
                         }
                     }
                     if (base == 0 && has_next) RT_TAKE_ACC(nr, HCG);
                     float zv[UB][4];
-                    if (has_next) rt_zgather<1, UB>(zv, e, Zs, zpeer, Q, kq);
+                    if (has_next) rt_zgather<1, UB, VEC>(zv, e, 1, Zs, zpeer, Q, kq);
                     // results: lstm v0..v3 = di,dj,df,dO, v4 = carry ; rnn v0 = d ; gru v1 = du, v2 = dc, v4 = dh
                     // (branch-free math: the UB chains interleave)
 #pragma unroll
@@ -888,33 +922,33 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                         }
                     }
 #pragma unroll
-                    for (int u = 0; u < UB; ++u) {
-                        if (!e[u].ok) continue;
-                        __nv_bfloat16* dzb = dzbp + e[u].r * (int)zw + e[u].jj;
+                    for (int qd = 0; qd < UB / VEC; ++qd) {
+                        if (!e[qd].ok) continue;
+                        __nv_bfloat16* dzb = dzbp + e[qd].r * (int)zw + e[qd].jj;
                         if (MODEL == CRNN_MODEL_LSTM) {
-                            store_bf16_split(dzb, a.dzb_lo, v0[u]); store_bf16_split(dzb + H, a.dzb_lo, v1[u]);
-                            store_bf16_split(dzb + 2 * H, a.dzb_lo, v2[u]); store_bf16_split(dzb + 3 * H, a.dzb_lo, v3[u]);
+                            stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
+                            stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + 3 * H, a.dzb_lo, v3 + VEC * qd);
                         } else if (MODEL == CRNN_MODEL_RNN) {
-                            store_bf16_split(dzb, a.dzb_lo, v0[u]);
+                            stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd);
                         } else {
-                            store_bf16_split(dzb + 2 * H, a.dzb_lo, v2[u]); store_bf16_split(dzb + H, a.dzb_lo, v1[u]);
+                            stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
                         }
                     }
                     pending = defer;
                     if (!defer) {
 #pragma unroll
-                        for (int u = 0; u < UB; ++u) {
-                            if (!e[u].ok) continue;
-                            float* dz = dzp + e[u].r * (int)zw + e[u].jj;
-                            const int64_t o = ob + e[u].r * H + e[u].jj;
+                        for (int qd = 0; qd < UB / VEC; ++qd) {
+                            if (!e[qd].ok) continue;
+                            float* dz = dzp + e[qd].r * (int)zw + e[qd].jj;
+                            const int64_t o = ob + e[qd].r * H + e[qd].jj;
                             if (MODEL == CRNN_MODEL_LSTM) {
-                                a.carry0[o] = v4[u];
-                                dz[0] = v0[u]; dz[H] = v1[u]; dz[2 * H] = v2[u]; dz[3 * H] = v3[u];
+                                stv<VEC>(a.carry0 + o, v4 + VEC * qd);
+                                stv<VEC>(dz, v0 + VEC * qd); stv<VEC>(dz + H, v1 + VEC * qd); stv<VEC>(dz + 2 * H, v2 + VEC * qd); stv<VEC>(dz + 3 * H, v3 + VEC * qd);
                             } else if (MODEL == CRNN_MODEL_RNN) {
-                                dz[0] = v0[u];
+                                stv<VEC>(dz, v0 + VEC * qd);
                             } else {
-                                dz[2 * H] = v2[u]; dz[H] = v1[u];
-                                a.carry1[o] = v4[u];
+                                stv<VEC>(dz + 2 * H, v2 + VEC * qd); stv<VEC>(dz + H, v1 + VEC * qd);
+                                stv<VEC>(a.carry1 + o, v4 + VEC * qd);
                             }
                         }
                     }
@@ -928,18 +962,18 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 const int64_t ob = (int64_t)b0row * H + j0;
                 float* dzp = a.dz + (tB + b0row) * zw + j0;
 #pragma unroll
-                for (int u = 0; u < UB; ++u) {
-                    if (!e[u].ok) continue;
-                    float* dz = dzp + e[u].r * (int)zw + e[u].jj;
-                    const int64_t o = ob + e[u].r * H + e[u].jj;
+                for (int qd = 0; qd < UB / VEC; ++qd) {
+                    if (!e[qd].ok) continue;
+                    float* dz = dzp + e[qd].r * (int)zw + e[qd].jj;
+                    const int64_t o = ob + e[qd].r * H + e[qd].jj;
                     if (MODEL == CRNN_MODEL_LSTM) {
-                        a.carry0[o] = v4[u];
-                        dz[0] = v0[u]; dz[H] = v1[u]; dz[2 * H] = v2[u]; dz[3 * H] = v3[u];
+                        stv<VEC>(a.carry0 + o, v4 + VEC * qd);
+                        stv<VEC>(dz, v0 + VEC * qd); stv<VEC>(dz + H, v1 + VEC * qd); stv<VEC>(dz + 2 * H, v2 + VEC * qd); stv<VEC>(dz + 3 * H, v3 + VEC * qd);
                     } else if (MODEL == CRNN_MODEL_RNN) {
-                        dz[0] = v0[u];
+                        stv<VEC>(dz, v0 + VEC * qd);
                     } else {
-                        dz[2 * H] = v2[u]; dz[H] = v1[u];
-                        a.carry1[o] = v4[u];
+                        stv<VEC>(dz + 2 * H, v2 + VEC * qd); stv<VEC>(dz + H, v1 + VEC * qd);
+                        stv<VEC>(a.carry1 + o, v4 + VEC * qd);
                     }
                 }
             }
@@ -947,28 +981,29 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 pending = false;
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(128, bt - ps * 128);
-                    const int nunits = nr * hcv;
+                    const int nquads = nr * hq;
                     const int b0row = b0 + ps * 128;
                     const int64_t ob = (int64_t)b0row * H + j0;
                     const float* gp = a.gates + (tB + b0row) * gw + j0;
-                    for (int base = 0; base < nunits; base += RT_EPI_THREADS * UB) {
-                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * UB >= nunits;
+                    for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {
+                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
                         float hp[UB], c1v[UB];
 #pragma unroll
-                        for (int u = 0; u < UB; ++u) {
-                            e[u] = epi_index(base + u * RT_EPI_THREADS + epi_tid, nunits, hcv, ldz, 1, kq * HC);
-                            v0[u] = v1[u] = hp[u] = c1v[u] = 0.f;
-                            if (e[u].ok) {
-                                const float* g = gp + e[u].r * (int)gw + e[u].jj;
-                                const int64_t o = ob + e[u].r * H + e[u].jj;
-                                v0[u] = g[0]; v1[u] = g[H];
-                                hp[u] = a.hx[(int64_t)t * BH + o];
-                                c1v[u] = a.carry1[o];
+                        for (int u = 0; u < UB; ++u) v0[u] = v1[u] = v4[u] = hp[u] = c1v[u] = 0.f;
+#pragma unroll
+                        for (int qd = 0; qd < UB / VEC; ++qd) {
+                            e[qd] = epi_index<VEC>(base + qd * RT_EPI_THREADS + epi_tid, nquads, hq, ldz, 1, kq * HC);
+                            if (e[qd].ok) {
+                                const float* g = gp + e[qd].r * (int)gw + e[qd].jj;
+                                const int64_t o = ob + e[qd].r * H + e[qd].jj;
+                                ldv<VEC>(g, v0 + VEC * qd); ldv<VEC>(g + H, v1 + VEC * qd);
+                                ldv<VEC>(a.hx + (int64_t)t * BH + o, hp + VEC * qd);
+                                ldv<VEC>(a.carry1 + o, c1v + VEC * qd);
                             }
                         }
                         if (base == 0) RT_TAKE_ACC(nr, HCG);
                         float zv[UB][4];
-                        rt_zgather<1, UB>(zv, e, Zs, zpeer, Q, kq);
+                        rt_zgather<1, UB, VEC>(zv, e, 1, Zs, zpeer, Q, kq);
                         // results: v0 = dr, v4 = carry into step t-1
 #pragma unroll
                         for (int u = 0; u < UB; ++u) {
@@ -978,17 +1013,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                             v4[u] = fmaf(c1v[u], u_, drs * r_);
                         }
 #pragma unroll
-                        for (int u = 0; u < UB; ++u) {
-                            if (!e[u].ok) continue;
-                            store_bf16_split(a.dzb + (tB + b0row) * zw + j0 + e[u].r * (int)zw + e[u].jj, a.dzb_lo, v0[u]);
+                        for (int qd = 0; qd < UB / VEC; ++qd) {
+                            if (!e[qd].ok) continue;
+                            stv_bf16_split<VEC>(a.dzb + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, a.dzb_lo, v0 + VEC * qd);
                         }
                         pending = defer;
                         if (!defer) {
 #pragma unroll
-                            for (int u = 0; u < UB; ++u) {
-                                if (!e[u].ok) continue;
-                                a.dz[(tB + b0row) * zw + j0 + e[u].r * (int)zw + e[u].jj] = v0[u];
-                                a.carry0[ob + e[u].r * H + e[u].jj] = v4[u];
+                            for (int qd = 0; qd < UB / VEC; ++qd) {
+                                if (!e[qd].ok) continue;
+                                stv<VEC>(a.dz + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, v0 + VEC * qd);
+                                stv<VEC>(a.carry0 + ob + e[qd].r * H + e[qd].jj, v4 + VEC * qd);
                             }
                         }
                     }
@@ -1000,10 +1035,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     const int b0row = b0 + (a.npass - 1) * 128;
                     const int64_t ob = (int64_t)b0row * H + j0;
 #pragma unroll
-                    for (int u = 0; u < UB; ++u) {
-                        if (!e[u].ok) continue;
-                        a.dz[(tB + b0row) * zw + j0 + e[u].r * (int)zw + e[u].jj] = v0[u];
-                        a.carry0[ob + e[u].r * H + e[u].jj] = v4[u];
+                    for (int qd = 0; qd < UB / VEC; ++qd) {
+                        if (!e[qd].ok) continue;
+                        stv<VEC>(a.dz + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, v0 + VEC * qd);
+                        stv<VEC>(a.carry0 + ob + e[qd].r * H + e[qd].jj, v4 + VEC * qd);
                     }
                 }
             }
