@@ -239,9 +239,8 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         auto pick_q = [&](int ncols_per_unit, int env) -> int {
             for (int Qc = 4; Qc >= 2; Qc >>= 1) {
                 if (env > 0 && Qc != env) continue;
-                // only long K, keep N <= 128.  Split operands stream twice the bytes per K block through a ring that
-                // holds two stages of them, so the K split pays from K = 512 on (config 3: 8.05 -> 6.70 ms per step)
-                if (env == 0 && (nkb < (h->split ? 8 : 16) || ncols_per_unit * HC * Qc > 128)) continue;
+                // only long K, keep N <= 128
+                if (env == 0 && (nkb < 16 || ncols_per_unit * HC * Qc > 128)) continue;
                 // measured (B200): Q = 4 pays (config 4 BPTT 9.9 -> 5.9 ms); Q = 2 pays only when one column per
                 // unit is exchanged (config 5: 26.3 -> 23.9 ms per direction) and loses for the LSTM forward
                 // pass, which gathers four (config 4: 4.6 -> 6.0 ms)

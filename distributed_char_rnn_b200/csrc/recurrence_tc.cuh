@@ -247,43 +247,47 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
         const int kbr = kb0 + rot >= nkb ? kb0 + rot - nkb : kb0 + rot;
         uint64_t db = desc_kmajor(w0 + (uint32_t)kbr * (uint32_t)nc * 128u);
         const uint64_t da_step = (uint64_t)(tile >> 4), db_step = (uint64_t)((nc * 128) >> 4);
-        if (split) {
-            for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+        // One divergent region per stage: the elected lane issues the stage's MMAs back to back and commits.
+        if (elect_one()) {
+            if (split && !swap) {
+                for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
 #pragma unroll
-                for (int k = 0; k < 8; k += 2) {
-                    if (!swap) mma_bf16_elect(tmem, da + k, db + k, idesc, (uint32_t)((kb0 + j + k) != 0));
-                    else       mma_bf16_elect(tmem, db + k, da + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+#pragma unroll
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + a_lo + k, db + k, idesc, 1u);
+#pragma unroll
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + w_lo + k, idesc, 1u);
                 }
+            } else if (split) {
+                for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
 #pragma unroll
-                for (int k = 0; k < 8; k += 2) {
-                    if (!swap) mma_bf16_elect(tmem, da + a_lo + k, db + k, idesc, 1u);
-                    else       mma_bf16_elect(tmem, db + k, da + a_lo + k, idesc, 1u);
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, db + k, da + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+#pragma unroll
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, db + k, da + a_lo + k, idesc, 1u);
+#pragma unroll
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, db + w_lo + k, da + k, idesc, 1u);
                 }
-#pragma unroll
-                for (int k = 0; k < 8; k += 2) {
-                    if (!swap) mma_bf16_elect(tmem, da + k, db + w_lo + k, idesc, 1u);
-                    else       mma_bf16_elect(tmem, db + w_lo + k, da + k, idesc, 1u);
+            } else if (!swap) {
+                for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+                    mma_bf16(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
+                    mma_bf16(tmem, da + 2, db + 2, idesc, 1u);
+                    mma_bf16(tmem, da + 4, db + 4, idesc, 1u);
+                    mma_bf16(tmem, da + 6, db + 6, idesc, 1u);
+                }
+            } else {
+                for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+                    mma_bf16(tmem, db, da, idesc, (uint32_t)((kb0 + j) != 0));
+                    mma_bf16(tmem, db + 2, da + 2, idesc, 1u);
+                    mma_bf16(tmem, db + 4, da + 4, idesc, 1u);
+                    mma_bf16(tmem, db + 6, da + 6, idesc, 1u);
                 }
             }
-        } else if (!swap) {
-            for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
-                mma_bf16_elect(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
-                mma_bf16_elect(tmem, da + 2, db + 2, idesc, 1u);
-                mma_bf16_elect(tmem, da + 4, db + 4, idesc, 1u);
-                mma_bf16_elect(tmem, da + 6, db + 6, idesc, 1u);
-            }
-        } else {
-            for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
-                mma_bf16_elect(tmem, db, da, idesc, (uint32_t)((kb0 + j) != 0));
-                mma_bf16_elect(tmem, db + 2, da + 2, idesc, 1u);
-                mma_bf16_elect(tmem, db + 4, da + 4, idesc, 1u);
-                mma_bf16_elect(tmem, db + 6, da + 6, idesc, 1u);
-            }
+            if (csize > 1) mma_commit_mc(&s.a_empty[st], (uint16_t)((1u << csize) - 1u));
+            else           mma_commit(&s.a_empty[st]);
+            if (kb0 + ckb >= nkb) mma_commit(s.z_full);      // last stage: the accumulator is complete
         }
-        if (csize > 1) { if (lane0) mma_commit_mc(&s.a_empty[st], (uint16_t)((1u << csize) - 1u)); __syncwarp(); }
-        else           mma_commit_elect(&s.a_empty[st]);
+        __syncwarp();
     }
-    mma_commit_elect(s.z_full);
     ++p.z_i;
 }
 

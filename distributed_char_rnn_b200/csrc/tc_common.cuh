@@ -180,6 +180,12 @@ __device__ __forceinline__ void mma_bf16_elect(uint32_t tmem_d, uint64_t adesc, 
         "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// One lane of the converged warp (the same one every time).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\tselp.u32 %0, 1, 0, q;\n\t}" : "=r"(ok));
+    return ok != 0;
+}
 __device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
     asm volatile(
         "{\n\t.reg .pred q;\n\t"

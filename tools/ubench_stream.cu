@@ -44,7 +44,69 @@ __global__ void __launch_bounds__(128, 1) stream_kernel(const __grid_constant__ 
     const int grp = blockIdx.x / a.share;
     const int row0 = grp * a.rows;
     const int nstage = a.nkb / a.ckb;                  // stages per round (one round = one phase's K extent)
+    __shared__ uint64_t go_bar;
+    __shared__ long long seen[16];
+    if (threadIdx.x == 0) { mbar_init(&go_bar, 1); fence_barrier_init(); }
+    __syncthreads();
     const int wid = threadIdx.x >> 5;
+    __shared__ uint32_t tm_slot;
+    __shared__ uint64_t mma_done;
+    if (a.mode == 6) {                                  // mode 5 + the consumer warp issues MMAs on every stage that arrives
+        if (threadIdx.x == 0) { mbar_init(&mma_done, 1); fence_barrier_init(); }
+        if (wid == 1) tmem_alloc(&tm_slot, 64);
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+    }
+    if (a.mode == 5 || a.mode == 6) {
+        uint64_t* full = full_all[0];
+        if (a.mode == 6 && wid == 1) {
+            const uint32_t tmem = __shfl_sync(0xffffffffu, tm_slot, 0);
+            const uint32_t idesc = idesc_bf16(a.rows >= 128 ? 128 : 64, 32, 0, 0);
+            uint8_t* B = ring + 8 * a.rows * 128;            // 4 KB of zeros behind the ring (never written)
+            uint32_t ncommit = 0;
+            for (int r = 0; r < a.rounds; ++r) {
+                const long long t0 = clock64();
+                for (int i = 0; i < nstage; ++i) {
+                    mbar_wait(&full[i], r & 1);
+                    tc_fence_after();
+                    if (r == a.rounds - 1 && threadIdx.x == 32) seen[i] = clock64() - t0;
+                    uint64_t da = desc_kmajor(smem_u32(ring + i * stage)), db = desc_kmajor(smem_u32(B));
+                    for (int j = 0; j < a.ckb; ++j, da += (uint64_t)(tile >> 4))
+                        for (int rep = 0; rep < 3; ++rep) {      // three products per K block, as the split-precision kernels issue
+                            mma_bf16_elect(tmem, da, db, idesc, 1u); mma_bf16_elect(tmem, da + 2, db + 2, idesc, 1u);
+                            mma_bf16_elect(tmem, da + 4, db + 4, idesc, 1u); mma_bf16_elect(tmem, da + 6, db + 6, idesc, 1u);
+                        }
+                }
+                mma_commit_elect(&mma_done);
+                mbar_wait(&mma_done, ncommit & 1); ++ncommit;
+                if (threadIdx.x == 32) mbar_arrive(&go_bar);
+                __syncwarp();
+            }
+            if (blockIdx.x == 0 && threadIdx.x == 32) { printf("with MMAs: stage arrival:"); for (int i = 0; i < nstage; ++i) printf(" %lld", seen[i]); printf("\n"); }
+            tc_fence_before();
+        }
+        if (threadIdx.x == 0) {
+            long long t0 = clock64();
+            for (int r = 0; r < a.rounds; ++r) {
+                if (r > 0) mbar_wait(&go_bar, (r - 1) & 1);          // the consumer has seen every stage of the previous round
+                for (int i = 0; i < nstage; ++i) {
+                    mbar_expect_tx(&full[i], (uint32_t)stage);
+                    tma_load_3d(ring + i * stage, &tm3, &full[i], 0, row0, i * a.ckb);
+                }
+            }
+            mbar_wait(&go_bar, (a.rounds - 1) & 1);
+            a.out[blockIdx.x] = clock64() - t0;
+        } else if (a.mode == 5 && threadIdx.x == 32) {
+            for (int r = 0; r < a.rounds; ++r) {
+                const long long t0 = clock64();
+                for (int i = 0; i < nstage; ++i) { mbar_wait(&full[i], r & 1); if (r == a.rounds - 1) seen[i] = clock64() - t0; }
+                mbar_arrive(&go_bar);
+            }
+            if (blockIdx.x == 0) { printf("stage arrival (cycles after the consumer started waiting):"); for (int i = 0; i < nstage; ++i) printf(" %lld", seen[i]); printf("\n"); }
+        }
+        return;
+    }
     if ((threadIdx.x & 31) == 0 && wid < a.nw) {
         uint64_t* full = full_all[wid];
         ring += (size_t)wid * a.nst * stage;
@@ -91,7 +153,7 @@ int main(int argc, char** argv) {
     printf("issuing warps = %d (bytes below are PER WARP)\n", nw);
     printf("wait = %s\n", poll ? "test_wait poll" : "try_wait");
     printf("mode rows ckb nst ctas share | KB/round  cyc/round  B/clk/SM  chip TB/s@1.9GHz\n");
-    for (int mode : {0, 3, 4})
+    for (int mode : {5, 6})
         for (int rows : {64, 128})
             for (int ckb : {1, 2})
                 for (int nst : {8})
