@@ -14,6 +14,7 @@ MODEL_IDS = {"rnn": 0, "gru": 1, "lstm": 2}
 PREC_IDS = {"fp32": 0, "bf16": 1, "bf16x3": 2}
 GRAD_TAIL = 2
 NUM_PHASES = 12
+CRNN_ERR_ARG, CRNN_ERR_CUDA, CRNN_ERR_UNSUP = -1, -2, -3        # include/crnn.h
 
 c_i32, c_i64, c_f32, c_vp = ctypes.c_int32, ctypes.c_int64, ctypes.c_float, ctypes.c_void_p
 

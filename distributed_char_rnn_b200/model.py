@@ -58,11 +58,20 @@ class Model(object):
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
 
         self.dropout_seed = int(np.random.SeedSequence(seed).generate_state(1)[0] & 0x7FFFFFFF) if (ikp < 1 or okp < 1) else 0
-        cfg = CrnnConfig(MODEL_IDS[args.model], args.rnn_size, args.num_layers, args.seq_length, args.batch_size,
-                         args.vocab_size, PREC_IDS[precision], self.device.index or 0, ikp, okp, self.dropout_seed, 0)
-        self.training_calls = 0                 # crnn_forward_backward calls so far = index of the next dropout mask set
+        # "auto": the fp32-grade tensor-core mode where the shape allows it (rnn_size % 16 == 0 and the hi + lo
+        # recurrent slices fit in shared memory), else the fp32 FFMA kernels - both CUDA, both at the 1e-4 parity bar.
+        candidates = ["bf16x3", "fp32"] if precision == "auto" else [precision]
         h = ctypes.c_void_p()
-        check(self._lib.crnn_create(ctypes.byref(cfg), ctypes.byref(h)))
+        for i, prec in enumerate(candidates):
+            cfg = CrnnConfig(MODEL_IDS[args.model], args.rnn_size, args.num_layers, args.seq_length, args.batch_size,
+                             args.vocab_size, PREC_IDS[prec], self.device.index or 0, ikp, okp, self.dropout_seed, 0)
+            rc = self._lib.crnn_create(ctypes.byref(cfg), ctypes.byref(h))
+            if rc == 0:
+                break
+            if rc != _lib.CRNN_ERR_UNSUP or i + 1 == len(candidates):
+                check(rc)
+        self.precision = prec
+        self.training_calls = 0                 # crnn_forward_backward calls so far = index of the next dropout mask set
         self._h = h
         self.P = int(self._lib.crnn_flat_size(h))
         self.layout = []

@@ -27,7 +27,7 @@ def sample(args):
         args.prime = chars[0]
     from .model import Model
     saved_args.distributed = False
-    model = Model(saved_args, training=False, precision=getattr(saved_args, "precision", "fp32"))
+    model = Model(saved_args, training=False, precision=getattr(saved_args, "precision", "auto"))
     ckpt = ckpt_io.latest_checkpoint(args.save_dir)
     if ckpt:                                # sample.py:42-46: silent when there is no checkpoint
         model.load_state_dict(ckpt_io.load(ckpt))

@@ -61,8 +61,9 @@ def build_parser():
     p.add_argument('--task_index', type=int, default=None, help="Index of task for given job (= replica rank)")
     p.add_argument('--tensor_file', default=None, help="Tensor file of the specific training data for given node.")
     # engine options (not in the reference)
-    p.add_argument('--precision', choices=['fp32', 'bf16'], default='fp32',
-                   help='fp32: FFMA contractions (1e-4 parity mode); bf16: tcgen05 tensor-core contractions')
+    p.add_argument('--precision', choices=['auto', 'fp32', 'bf16x3', 'bf16'], default='auto',
+                   help='bf16x3: tcgen05 contractions on split-bf16 operands, fp32-grade (1e-4 parity); fp32: FFMA contractions '
+                        '(1e-4 parity); bf16: plain bf16 tcgen05 contractions (1e-2); auto: bf16x3 where the shape allows it, else fp32')
     p.add_argument('--seed', type=int, default=None, help='seed of the variable initialiser (reference: unseeded)')
     p.add_argument('--max_steps', type=int, default=None, help='stop after this many steps (smoke tests)')
     return p

@@ -51,6 +51,12 @@ extern "C" {
 
 #define CRNN_GRAD_TAIL  2
 
+/* return codes */
+#define CRNN_OK            0
+#define CRNN_ERR_ARG      -1   /* bad argument                                                   */
+#define CRNN_ERR_CUDA     -2   /* a CUDA call failed, or there is no sm_100 device               */
+#define CRNN_ERR_UNSUP    -3   /* shape / precision combination this build has no kernel plan for */
+
 /* phases of one step, for crnn_profile_* (bench.py's per-kernel roofline figures) */
 #define CRNN_PHASE_EMBED_GATHER  0
 #define CRNN_PHASE_XPROJ_GEMM    1
