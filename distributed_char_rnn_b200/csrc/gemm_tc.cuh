@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
     uint64_t* tmem_full = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for ptxas
     const int m0 = blockIdx.y * GT_BM, n0 = blockIdx.x * BN;
     const int total_kb = ceil_div(g.K, GT_BK);
     const int kb0 = blockIdx.z * g.kblocks_per_split;
@@ -113,8 +113,9 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (single thread) =====
-        if (lane == 0) {
+        // ===== MMA issuer: the whole warp runs the loop, one elected lane issues (operands stay in uniform registers) =====
+        {
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
             const uint32_t idesc = idesc_bf16(GT_BM, BN, g.a_mn, g.b_mn);
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
@@ -127,20 +128,24 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
                 const uint64_t ad = g.a_mn ? desc_mnmajor(sa, 8192) : desc_kmajor(sa);
                 const uint64_t bd = g.b_mn ? desc_mnmajor(sb, 8192) : desc_kmajor(sb);
                 const uint64_t as = g.a_mn ? 128u : 2u, bs = g.b_mn ? 128u : 2u;
-                mma_bf16(tmem_base, ad, bd, idesc, (uint32_t)(i != 0));
-                mma_bf16(tmem_base, ad + as, bd + bs, idesc, 1u);
-                mma_bf16(tmem_base, ad + 2 * as, bd + 2 * bs, idesc, 1u);
-                mma_bf16(tmem_base, ad + 3 * as, bd + 3 * bs, idesc, 1u);
-                if (SPLIT) {                        // + lo(A)*hi(B) + hi(A)*lo(B); smallest terms could go first, fp32 adds make it moot
-                    const uint64_t lo = (uint64_t)(L::HALF_BYTES >> 4);
+                if (elect_one()) {
+                    mma_bf16(tmem_u, ad, bd, idesc, (uint32_t)(i != 0));
+                    mma_bf16(tmem_u, ad + as, bd + bs, idesc, 1u);
+                    mma_bf16(tmem_u, ad + 2 * as, bd + 2 * bs, idesc, 1u);
+                    mma_bf16(tmem_u, ad + 3 * as, bd + 3 * bs, idesc, 1u);
+                    if (SPLIT) {                    // + lo(A)*hi(B) + hi(A)*lo(B)
+                        const uint64_t lo = (uint64_t)(L::HALF_BYTES >> 4);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) mma_bf16(tmem_base, ad + lo + k * as, bd + k * bs, idesc, 1u);
+                        for (int k = 0; k < 4; ++k) mma_bf16(tmem_u, ad + lo + k * as, bd + k * bs, idesc, 1u);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) mma_bf16(tmem_base, ad + k * as, bd + lo + k * bs, idesc, 1u);
+                        for (int k = 0; k < 4; ++k) mma_bf16(tmem_u, ad + k * as, bd + lo + k * bs, idesc, 1u);
+                    }
+                    mma_commit(&empty_bar[s]);          // frees the smem slot once these MMAs retire
+                    if (i + 1 == nkb) mma_commit(tmem_full);   // accumulator complete
                 }
-                mma_commit(&empty_bar[s]);          // frees the smem slot once these MMAs retire
+                __syncwarp();
             }
-            mma_commit(tmem_full);                  // accumulator complete
+            if (nkb <= 0 && elect_one()) mma_commit(tmem_full);
         }
     } else {
         // ===== epilogue: TMEM -> registers -> global =====
