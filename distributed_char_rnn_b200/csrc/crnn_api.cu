@@ -1002,6 +1002,30 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     CRNN_CUDA(cudaMemsetAsync(ws_barrier(ws, 0), 0, 512 * 256, st));
     // In wavefront mode the "rec_fwd" phase is the whole fork..join span: the recurrences of all layers
     // plus their chunked x-projections, which run interleaved with them.
+    // Layer 0's x-projection depends only on the embeddings: with CRNN_WF_HOIST0=1 it runs as ONE full-GPU GEMM here (and
+    // layer 0's input-gradient GEMM as one after the BPTT join), so the SMs left beside the recurrence kernels serve only
+    // the chunk GEMMs on the layers' critical path.  Measured on config 3: the recurrence spans shrink (2.14 -> 2.09 and
+    // 2.65 -> 2.58 ms, split precision) but the two GEMMs are then serial, 5.03 -> 5.19 ms per step: off by default.
+    const bool hoist0 = wf && env_int("CRNN_WF_HOIST0", 0);
+    if (hoist0) {
+        LayerParams lp = layer_params(h, params, 0);
+        const bf16_t* inb0 = x0b;
+        if (drop) {
+            rc = drop_apply(h, drop_call, 0, x0, nullptr, wsb(ws, h->ws.xinb[0]), 0, SB * H, st, lo.act);
+            if (rc != CRNN_OK) return rc;
+            inb0 = wsb(ws, h->ws.xinb[0]);
+        }
+        prof_mark(h, st, CRNN_PHASE_XPROJ_GEMM);
+        float* g0 = wsf(ws, h->ws.gates[0]);
+        if (c.model == CRNN_MODEL_GRU) {
+            rc = gemm_tc(h, (int)SB, 2 * H, H, inb0, H, 0, lo.act, pbf + lp.oW, 2 * H, 1, lo.pbf, g0, gw, lp.b, 0, st);
+            if (rc == CRNN_OK) rc = gemm_tc(h, (int)SB, H, H, inb0, H, 0, lo.act, pbf + lp.oWc, H, 1, lo.pbf, g0 + 2 * H, gw, lp.bc, 0, st);
+        } else {
+            rc = gemm_tc(h, (int)SB, h->G * H, H, inb0, H, 0, lo.act, pbf + lp.oW, h->G * H, 1, lo.pbf, g0, gw, lp.b, 0, st);
+        }
+        if (rc != CRNN_OK) return rc;
+        prof_mark(h, st, CRNN_PHASE_MISC);
+    }
     if (wf) prof_mark(h, st, CRNN_PHASE_REC_FWD);
     rc = wf_fork(h, st, 0);
     if (rc != CRNN_OK) return rc;
@@ -1046,7 +1070,8 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
                 rc = wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }
-            if (drop) {                              // masked bf16 copy of this chunk's inputs
+            const bool hoisted = hoist0 && l == 0;   // done above for the whole sequence
+            if (drop && !hoisted) {                  // masked bf16 copy of this chunk's inputs
                 rc = drop_apply(h, drop_call, l, in32 + (int64_t)t0 * BH, nullptr, wsb(ws, h->ws.xinb[l]) + (int64_t)t0 * BH,
                                 (int64_t)t0 * BH, (int64_t)rows * H, gs, lo.act);
                 if (rc != CRNN_OK) return rc;
@@ -1055,7 +1080,9 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             // x half of [x,h]*W for the chunk's steps: A = inputs (K-major), B = kernel rows 0..H stored [K,N]
             const bf16_t* ain = inb + (int64_t)t0 * BH;
             float* gch = gates + (int64_t)t0 * B * gw;
-            if (c.model == CRNN_MODEL_GRU) {
+            if (hoisted) {
+                rc = CRNN_OK;
+            } else if (c.model == CRNN_MODEL_GRU) {
                 rc = gemm_tc(h, rows, 2 * H, H, ain, H, 0, in_lo, pbf + lp.oW, 2 * H, 1, lo.pbf, gch, gw, lp.b, 0, gs);
                 if (rc == CRNN_OK) rc = gemm_tc(h, rows, H, H, ain, H, 0, in_lo, pbf + lp.oWc, H, 1, lo.pbf, gch + 2 * H, gw, lp.bc, 0, gs);
             } else {
@@ -1145,6 +1172,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     // BPTT, top layer first.  Wavefront: layer l works on chunk c (late steps first) as soon as layer
     // l+1 has turned that chunk's dz into input gradients; "rec_bwd" then times the whole fork..join
     // span (recurrences + interleaved input-gradient GEMMs), weight gradients included at its tail.
+    const bool hoist0 = wf && env_int("CRNN_WF_HOIST0", 0);     // see run_forward_bf16
     if (wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
     rc = wf_fork(h, st, 1 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
@@ -1206,7 +1234,9 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             if (!wf) prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
             const bf16_t* dzc = dzb + (int64_t)t0 * B * zw;
             float* dn = dnext + (int64_t)t0 * BH;
-            if (c.model == CRNN_MODEL_GRU) {
+            if (hoist0 && l == 0) {
+                continue;                            // nothing waits for the embedding-side gradients: one GEMM after the join
+            } else if (c.model == CRNN_MODEL_GRU) {
                 rc = gemm_tc(h, rows, H, 2 * H, dzc, zw, 0, lo.dzb, pbf + lp.oW, 2 * H, 0, lo.pbf, dn, H, nullptr, 0, gs);
                 if (rc == CRNN_OK) rc = gemm_tc(h, rows, H, H, dzc + 2 * H, zw, 0, lo.dzb, pbf + lp.oWc, H, 0, lo.pbf, dn, H, nullptr, 1, gs);
             } else {
@@ -1246,6 +1276,20 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     }
     rc = wf_join(h, st, 2 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
+    if (hoist0) {                                    // layer 0's input gradients for the whole sequence
+        prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
+        LayerParams lp = layer_params(h, params, 0);
+        const bf16_t* dzb0 = wsb(ws, h->ws.dzbv[0]);
+        float* dn = wsf(ws, h->ws.gx0);
+        if (c.model == CRNN_MODEL_GRU) {
+            rc = gemm_tc(h, (int)SB, H, 2 * H, dzb0, zw, 0, lo.dzb, pbf + lp.oW, 2 * H, 0, lo.pbf, dn, H, nullptr, 0, st);
+            if (rc == CRNN_OK) rc = gemm_tc(h, (int)SB, H, H, dzb0 + 2 * H, zw, 0, lo.dzb, pbf + lp.oWc, H, 0, lo.pbf, dn, H, nullptr, 1, st);
+        } else {
+            rc = gemm_tc(h, (int)SB, H, h->G * H, dzb0, zw, 0, lo.dzb, pbf + lp.oW, h->G * H, 0, lo.pbf, dn, H, nullptr, 0, st);
+        }
+        if (rc == CRNN_OK && drop) rc = drop_apply(h, call, 0, dn, dn, nullptr, 0, SB * H, st);
+        if (rc != CRNN_OK) return rc;
+    }
     prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
     embed_scatter_kernel<<<grid_for(SB * H, sc), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, wsf(ws, h->ws.gx0), ws_sq(ws));
     CRNN_LAUNCH_CHECK("embed_scatter_kernel");
