@@ -58,3 +58,15 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(_lib.CrnnError, match="no CPU fallback"):
         _lib.load()
+
+
+def test_python_constants_match_the_header():
+    """Precision ids and return codes of the ctypes layer are the header's."""
+    import re
+    from distributed_char_rnn_b200 import _lib
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "crnn.h")).read()
+    defs = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define\s+(CRNN_[A-Z0-9_]+)\s+(-?\d+)", hdr)}
+    assert _lib.PREC_IDS == {"fp32": defs["CRNN_PREC_FP32"], "bf16": defs["CRNN_PREC_BF16"], "bf16x3": defs["CRNN_PREC_BF16X3"]}
+    assert (_lib.CRNN_ERR_ARG, _lib.CRNN_ERR_CUDA, _lib.CRNN_ERR_UNSUP) == (defs["CRNN_ERR_ARG"], defs["CRNN_ERR_CUDA"], defs["CRNN_ERR_UNSUP"])
+    assert _lib.MODEL_IDS == {"rnn": defs["CRNN_MODEL_RNN"], "gru": defs["CRNN_MODEL_GRU"], "lstm": defs["CRNN_MODEL_LSTM"]}
+    assert _lib.GRAD_TAIL == defs["CRNN_GRAD_TAIL"]
