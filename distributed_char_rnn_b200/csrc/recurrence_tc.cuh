@@ -67,7 +67,7 @@ struct RecTcArgs {
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
     int split;                  // 1: every bf16 operand is a (hi, lo) pair (CRNN_PREC_BF16X3): hi*hi + lo*hi + hi*lo per K step
     long long hxb_lo, rsb_lo, dzb_lo;   // element offsets of the lo twins of hxb / rsb / dzb (0 when not split)
-    int expt;                   // timing experiments only (CRNN_TC_EXPT; results are wrong when set): 1 no critical stores, 2 no math
+    int expt;                   // timing experiments only (CRNN_TC_EXPT; results are wrong when set): 1 no critical stores, 2 no math, 4 no deferred stores (fwd)
     // One launch for the whole sequence while its inputs / consumers work chunk by chunk on other streams
     // (layer wavefront): before the first step of chunk c the epilogue waits until in_flags[c] != 0 (the batch GEMM
     // that produces the chunk's hoisted inputs has finished), and after the last step of chunk c every CTA adds 1 to
@@ -734,7 +734,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 if (epi_tid == 0) RT_STAMP(6);
                 if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
                 if (epi_tid == 0) RT_STAMP(7);
-                if (pending) {               // the stores nobody else waits for
+                if (pending && !(a.expt & 4)) {   // the stores nobody else waits for
                     const int b0row = b0 + (a.npass - 1) * 128;                  // the deferred batch belongs to the last pass
                     const int64_t ob = (int64_t)b0row * H + j0;
 #pragma unroll
