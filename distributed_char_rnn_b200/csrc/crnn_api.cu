@@ -87,6 +87,7 @@ struct crnn_handle {
     int split;            // 1: CRNN_PREC_BF16X3, every bf16 operand array is followed by its lo twin
     long long fb_calls;
     long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
+    int dbg_layer;        // the layer whose forward launches record stamps
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
     int fast_act;
     WsPlan ws;
@@ -466,7 +467,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             h->wf_W = W;
             int C = W > 1 ? std::max(1, std::min(16, cfg->seq_length / 10)) : 1;
             const int c_env = env_int("CRNN_WAVEFRONT_CHUNKS", 0);
-            if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 16);
+            if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 32);
             if (W == 1) C = 1;
             h->wf_C = C;
             // Measured on B200: one launch per layer instead of one per chunk pays where the per-chunk launches are short
@@ -735,7 +736,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
     a.swap = backward ? p.swap_bwd : p.swap_fwd;
     a.m64 = (!a.swap && p.npass == 1 && p.BT <= 64 && env_int("CRNN_TC_M64", 1)) ? 1 : 0;
-    a.dbg = (!backward && env_int("CRNN_TC_DEBUG", 0)) ? h->dbg_ptr : nullptr;
+    a.dbg = (!backward && env_int("CRNN_TC_DEBUG", 0) && h->dbg_layer == env_int("CRNN_TC_DEBUG_LAYER", 0)) ? h->dbg_ptr : nullptr;
     CUtensorMap t0, t1, w0, w1, t0l, t1l, w0l, w1l;
     int rc;
     const int split = h->split;
@@ -1030,6 +1031,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     rc = wf_fork(h, st, 0);
     if (rc != CRNN_OK) return rc;
     for (int l = 0; l < L; ++l) {
+        h->dbg_layer = l;
         cudaStream_t s = wf_stream(h, st, l);
         LayerParams lp = layer_params(h, params, l);
         float* hx = wsf(ws, h->ws.hx[l]);

@@ -2,11 +2,12 @@ import os, sys, argparse, numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ['CRNN_TC_DEBUG']='1'
 from distributed_char_rnn_b200.model import Model
-ns=argparse.Namespace(model='gru',rnn_size=512,num_layers=1,seq_length=50,batch_size=256,vocab_size=96,grad_clip=5.0)
+ns=argparse.Namespace(model='gru',rnn_size=512,num_layers=int(os.environ.get('DBG_LAYERS','1')),seq_length=int(os.environ.get('DBG_S','50')),batch_size=256,vocab_size=96,grad_clip=5.0)
 prec=sys.argv[1] if len(sys.argv)>1 else 'bf16'
 m=Model(ns,device='cuda:0',precision=prec,seed=0); m.assign_lr(0.002)
 rng=np.random.default_rng(0)
-x=rng.integers(0,96,(256,50)).astype(np.int32); y=rng.integers(0,96,(256,50)).astype(np.int32)
+S_=ns.seq_length
+x=rng.integers(0,96,(256,S_)).astype(np.int32); y=rng.integers(0,96,(256,S_)).astype(np.int32)
 for _ in range(3): m.step(x,y)
 torch.cuda.synchronize()
 d=m.workspace[24576:24576+8*4*192].view(torch.int64).cpu().numpy().reshape(4,8,24)
