@@ -800,6 +800,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const int per_pass = std::min(128, p.BT) * p.HC;
     const bool ub8 = per_pass > tc::RT_EPI_THREADS * 4 && env_int("CRNN_TC_UB8", 1);
     a.defer = env_int("CRNN_TC_DEFER", 1);
+    a.acq_poll = env_int("CRNN_TC_ACQ_POLL", 1);
     a.expt = env_int("CRNN_TC_EXPT", 0);
     // K-split launches read their partial sums from distributed shared memory; there consecutive lanes on consecutive
     // units (scalar epilogue) beat quads (config 4 BPTT 5.4 vs 6.6 ms, split-precision config 3 BPTT 2.9 vs 3.6 ms)

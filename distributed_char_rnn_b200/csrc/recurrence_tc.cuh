@@ -75,6 +75,7 @@ struct RecTcArgs {
     int nchunks;
     const unsigned* in_flags;
     unsigned* out_flags;
+    int acq_poll;               // 1: the step barrier is polled with acquire loads (no fence after the poll loop)
     int defer;                  // 1: stores only this CTA reads later are issued after the step barrier's release
     int rotate;                 // 1: slices of a tile walk the K blocks from different starting stages, so they do not all
                                 // ask L2 for the same rows at the same moment
@@ -335,12 +336,20 @@ __device__ __forceinline__ void rt_await_cluster(uint64_t* step_bar, unsigned ph
     mbar_wait_cluster(step_bar, (phases_done - 1u) & 1u);
     asm volatile("fence.proxy.async;" ::: "memory");
 }
-__device__ __forceinline__ void rt_await(const unsigned* counter, unsigned target) {
+__device__ __forceinline__ void rt_await(const unsigned* counter, unsigned target, int acq_poll) {
     unsigned v;
-    do {   // relaxed polls (one L2 round trip each) ...
-        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-    } while (v < target);
-    asm volatile("fence.acq_rel.gpu;" ::: "memory");  // ... then one acquire, and hand over to the async proxy (TMA)
+    if (acq_poll) {
+        // acquire polls: the load that sees the last slice's release synchronises with it (the reds form its release
+        // sequence); no separate fence afterwards, only the hand-over to the async proxy (TMA)
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+        } while (v < target);
+    } else {
+        do {   // relaxed polls (one L2 round trip each) ...
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+        } while (v < target);
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");  // ... then one acquire
+    }
     asm volatile("fence.proxy.async;" ::: "memory");
 }
 
@@ -569,7 +578,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (int)phases_done;
                     RT_STAMP(0);
-                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
+                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb,
@@ -847,14 +856,14 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
                 if (t + 1 < a.S) {
-                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices); }
+                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb0,
                                    a.split ? &tmZ0l : nullptr, rot0);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
-                    if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices);
+                    if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb1,
                                    a.split ? &tmZ1l : nullptr, rot1);
