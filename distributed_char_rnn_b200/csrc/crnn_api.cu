@@ -823,7 +823,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     int csize = 1;
     const int cmax = env_int("CRNN_TC_CLUSTER", 1);
     for (int cs = 16; cs >= 2; cs >>= 1)
-        if (cs <= cmax && p.nslices % cs == 0 && !split) { csize = cs; break; }   // (multicast of split operands: not built)
+        if (cs <= cmax && p.nslices % cs == 0 && (!split || a.use3d)) { csize = cs; break; }
     a.mcast = csize > 1 ? 1 : 0;
     a.cbar = 0;
     // Cluster barrier: when ALL slices of a batch tile fit in one cluster, the steps are ordered by remote

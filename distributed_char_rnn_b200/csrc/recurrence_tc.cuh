@@ -195,7 +195,12 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
             uint8_t* hi = s.ring + st * stage;
             uint8_t* lo = hi + ckb * tile;
             const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;      // rotated start (rot is a multiple of ckb)
-            if (use3d) {
+            if (csize > 1) {                           // multicast (3-D maps only): the cluster's CTAs take turns, stage by stage
+                if ((int)(p.ring_i % (uint32_t)csize) != crank) continue;
+                const uint16_t mask = (uint16_t)((1u << csize) - 1u);
+                tma_load_3d_mc(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kb, mask);
+                tma_load_3d_mc(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kb, mask);
+            } else if (use3d) {
                 tma_load_3d(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
                 tma_load_3d(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kbr);
             } else {
