@@ -287,7 +287,10 @@ inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda
     g.kblocks_per_split = ceil_div(total_kb, splits);
     grid.z = ceil_div(total_kb, g.kblocks_per_split);
     g.mode = accumulate ? (grid.z > 1 ? 2 : 1) : 0;
-    static bool attr_set = false;
+    static bool attr_done[64] = {};                      // per device (function attributes are per context)
+    int dev = 0;
+    CRNN_CUDA(cudaGetDevice(&dev));
+    bool& attr_set = attr_done[dev & 63];
     if (!attr_set) {
         CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        GemmTcSmem<BN, STAGES, false>::TOTAL));
