@@ -252,7 +252,7 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
                 // pass, which gathers four (config 4: 4.6 -> 6.0 ms)
                 if (env == 0 && Qc == 2 && ncols_per_unit > 1) continue;
                 if (H % (64 * Qc) != 0 || H % (HC * Qc) != 0 || nslices % Qc != 0) continue;
-                if (ncols_per_unit * HC * Qc > 256) continue;
+                if (ncols_per_unit * HC * Qc > (h->split ? 128 : 256)) continue;   // split: the MMA's N is twice the columns
                 if ((int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1)) > h->max_smem) continue;
                 return Qc;
             }
@@ -294,7 +294,7 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
     };
     // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
     // while that leaves SMs idle: every SM should hold a (slice, tile) pair.
-    const int hc_max = std::min(256 / g1, H) & ~15;
+    const int hc_max = std::min((h->split ? 128 : 256) / g1, H) & ~15;   // MMA N <= 256 (split operands: N = 2 * columns)
     int best = 0;
     RecPlanTc cand;
     for (int HC = hc_max; HC >= 16; HC -= 16) {

@@ -276,13 +276,18 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
         // One divergent region per stage: the elected lane issues the stage's MMAs back to back and commits.
         if (elect_one()) {
             if (split && !swap) {
-                for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
+                // Weights of a K block are resident as [hi rows ; lo rows] (2*nc rows): one MMA of N = 2*nc gives
+                // A_hi*W_hi in accumulator columns [0, nc) and A_hi*W_lo in [nc, 2nc), a second of N = nc adds A_lo*W_hi
+                // to [0, nc); the epilogue sums the two column halves.  Two instructions and one read of the A_hi tile
+                // less per K step than three separate products (the MMAs are paced by their shared-memory reads).
+                const uint32_t idesc2 = idesc_bf16(m64 ? 64 : 128, 2 * nc, 0, 0);
+                db = desc_kmajor(w0 + (uint32_t)kbr * (uint32_t)(2 * nc) * 128u);
+                const uint64_t db2_step = (uint64_t)((2 * nc * 128) >> 4);
+                for (int j = 0; j < n; ++j, da += da_step, db += db2_step) {
 #pragma unroll
-                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + k, idesc, (uint32_t)((kb0 + j + k) != 0));
+                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + k, idesc2, (uint32_t)((kb0 + j + k) != 0));
 #pragma unroll
                     for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + a_lo + k, db + k, idesc, 1u);
-#pragma unroll
-                    for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + w_lo + k, idesc, 1u);
                 }
             } else if (split) {
                 for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
@@ -360,9 +365,11 @@ __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned targe
 
 // Accumulator -> shared Zs[r*ldz + c] for batch rows r < nr and gate columns c < nc (ldz odd).
 // A warp can only read its own TMEM lane quarter; quarters holding nothing useful skip the load.
+// pair != 0: the accumulator holds two column halves [0, nc) and [nc, 2nc) whose sum is the result (split operands).
 __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane, int nr, int nc, float* __restrict__ Zs,
-                                        int ldz, int swap, int m64) {
+                                        int ldz, int swap, int m64, int pair = 0) {
     float v[32];
+    float w[32];
     constexpr int NH = RT_EPI_WARPS / 4;             // warps per lane quarter
     if (m64 && !swap) {
         // M=64 accumulator: batch row 16*q + lane lives in lane (32*q + lane), lane < 16
@@ -370,6 +377,11 @@ __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane
             const int r = 16 * q + lane;
             for (int c0 = 32 * half; c0 < nc; c0 += 32 * NH) {
                 tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
+                if (pair) {
+                    tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(nc + c0), w);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += w[i];
+                }
                 if (lane < 16 && r < nr) {
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
@@ -382,6 +394,11 @@ __device__ __forceinline__ void zs_dump(uint32_t tmem, int q, int half, int lane
             const int r = 32 * q + lane;
             for (int c0 = 32 * half; c0 < nc; c0 += 32 * NH) {
                 tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
+                if (pair) {
+                    tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(nc + c0), w);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += w[i];
+                }
                 if (r < nr) {
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
@@ -489,7 +506,7 @@ __device__ __forceinline__ void rt_zgather(float (&zv)[UB][4], const EpiIdx (&e)
         if (Q > 1) mbar_wait_cluster(s.zs_free, (p.z_i & 1) ^ 1);  /* peers have read the previous partials */ \
         mbar_wait(s.z_full, p.z_i & 1);                                           \
         tc_fence_after();                                                         \
-        zs_dump(tmem, q, ehalf, lane, nr_, nc_, Zs, ldz, a.swap, a.m64);                                \
+        zs_dump(tmem, q, ehalf, lane, nr_, nc_, Zs, ldz, a.swap, a.m64, a.split && !a.swap);            \
         tc_fence_before();                                                        \
         mbar_arrive(s.z_empty);                                                   \
         epi_bar_sync();                                                           \
@@ -540,7 +557,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
-    while ((int)tcols < (a.swap ? 128 : NCA)) tcols <<= 1;
+    while ((int)tcols < (a.swap ? 128 : (a.split ? 2 * NCA + 32 : NCA))) tcols <<= 1;   // split: two column halves (zs_dump reads 32 columns from nc + c0)
 
     // zero the ring once: rows past the TMA box are never written and must not hold NaNs
     for (int i = threadIdx.x; i < a.ring_bytes / 16; i += RT_THREADS)
@@ -575,9 +592,11 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
             mbar_expect_tx(s.w_bar, wbytes * (uint32_t)nsp);
             for (int half = 0; half < nsp; ++half)
                 for (int kb = 0; kb < nkb; ++kb) {
-                    tma_load_2d(s.wsa + (size_t)(half * nkb + kb) * NCA * 128, half ? &tmW0l : &tmW0, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG);
+                    // (not swapped: [hi rows ; lo rows] per K block, see rt_mma; swapped: all hi blocks, then all lo blocks)
+                    const int wblk = (nsp == 2 && !a.swap) ? kb * 2 + half : half * nkb + kb;
+                    tma_load_2d(s.wsa + (size_t)wblk * NCA * 128, half ? &tmW0l : &tmW0, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG);
                     if (MODEL == CRNN_MODEL_GRU)
-                        tma_load_2d(s.wsb + (size_t)(half * nkb + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
+                        tma_load_2d(s.wsb + (size_t)wblk * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
                 }
             for (int t = a.t_begin; t < a.t_end; ++t) {
                 for (int ph = 0; ph < nphase; ++ph) {
@@ -822,7 +841,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     const int b0 = tile * a.BT, bt = min(a.BT, B - b0);
     const int64_t gw = (int64_t)a.GS * H, zw = (int64_t)GZ * H, BH = (int64_t)B * H;
     uint32_t tcols = 32;
-    while ((int)tcols < (a.swap ? 128 : HCG)) tcols <<= 1;
+    while ((int)tcols < (a.swap ? 128 : (a.split ? 2 * HCG + 32 : HCG))) tcols <<= 1;
 
     for (int i = threadIdx.x; i < a.ring_bytes / 16; i += RT_THREADS)
         reinterpret_cast<uint4*>(s.ring)[i] = make_uint4(0, 0, 0, 0);
@@ -852,11 +871,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             uint32_t wbytes = (uint32_t)nkb0 * HCG * 128u + (MODEL == CRNN_MODEL_GRU ? (uint32_t)nkb1 * HCG * 128u : 0u);
             mbar_expect_tx(s.w_bar, wbytes * (uint32_t)nsp);
             for (int half = 0; half < nsp; ++half) {
+                const bool il = nsp == 2 && !a.swap;         // [hi rows ; lo rows] per K block, see rt_mma
                 for (int kb = 0; kb < nkb0; ++kb)
-                    tma_load_2d(s.wsa + (size_t)(half * nkb0 + kb) * HCG * 128, half ? &tmW0l : &tmW0, s.w_bar, (kq * nkb0 + kb) * 64, H + jg0);
+                    tma_load_2d(s.wsa + (size_t)(il ? kb * 2 + half : half * nkb0 + kb) * HCG * 128, half ? &tmW0l : &tmW0, s.w_bar, (kq * nkb0 + kb) * 64, H + jg0);
                 if (MODEL == CRNN_MODEL_GRU)
                     for (int kb = 0; kb < nkb1; ++kb)
-                        tma_load_2d(s.wsb + (size_t)(half * nkb1 + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
+                        tma_load_2d(s.wsb + (size_t)(il ? kb * 2 + half : half * nkb1 + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
             }
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
