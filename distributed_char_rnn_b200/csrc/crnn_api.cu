@@ -267,10 +267,11 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         o->smem_fwd = tc::rt_smem_bytes(wbytes, 0, o->zs_fwd);
         o->smem_bwd = tc::rt_smem_bytes(wbytes, 0, o->zs_bwd);
         if ((int)std::max(o->smem_fwd, o->smem_bwd) > h->max_smem) return false;
-        // A larger ring (CRNN_TC_RING_KB) is possible where shared memory is left, but measured on B200 it buys
-        // nothing: config 3 at 64 / 96 / 128 KB: 4.20 / 4.22 / 4.22 ms (bf16), 6.69 / 6.85 / 6.86 ms (split) - the
-        // stream is bound by the rate L2 serves the same rows to every slice of a tile, not by stages in flight.
-        const int ring_cap = env_int("CRNN_TC_RING_KB", 64) * 1024;
+        // A larger ring (CRNN_TC_RING_KB) where shared memory is left.  Plain bf16: measured no gain (config 3 at 64 / 96 /
+        // 128 KB: 4.20 / 4.22 / 4.22 ms).  Split operands stream twice the bytes per K block, a 64 KB ring holds two
+        // stages of them, and a third stage in flight pays once the MMAs no longer pace the stream (config 3: 4.84 ->
+        // 4.62 ms at 96 KB), so the split ring takes what is left up to 112 KB.
+        const int ring_cap = env_int("CRNN_TC_RING_KB", h->split ? 112 : 64) * 1024;
         auto grow = [&](size_t* smem, int* ring) {
             const int spare = ((h->max_smem - (int)*smem) / 1024) * 1024;
             const int add = std::max(0, std::min(spare, ring_cap - *ring));
