@@ -825,6 +825,17 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const int cmax = env_int("CRNN_TC_CLUSTER", 1);
     for (int cs = 16; cs >= 2; cs >>= 1)
         if (cs <= cmax && p.nslices % cs == 0 && (!split || a.use3d)) { csize = cs; break; }
+    if (csize > 1) {
+        // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+        // memory hung the GPU.  The streamed rows live in the caller's workspace: unless the driver reports that buffer
+        // as plain device memory of the handle's own GPU, the launch falls back to one load per CTA.
+        const void* streamed = backward ? (const void*)a.dzb : (const void*)a.hxb;
+        cudaPointerAttributes pa;
+        if (cudaPointerGetAttributes(&pa, streamed) != cudaSuccess || pa.type != cudaMemoryTypeDevice || pa.device != h->cfg.device) {
+            cudaGetLastError();
+            csize = 1;
+        }
+    }
     a.mcast = csize > 1 ? 1 : 0;
     a.cbar = 0;
     // Cluster barrier: when ALL slices of a batch tile fit in one cluster, the steps are ordered by remote
