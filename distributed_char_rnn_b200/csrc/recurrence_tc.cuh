@@ -4,15 +4,21 @@
 // reverse-mode mirror (model.py:88-91): per time step only h_{t-1} * W_h (forward) or
 // dz_{t+1} * W_h^T (backward) remains once the x halves are hoisted into batch GEMMs.
 //
-// One cooperative launch per layer and direction.  CTA (slice, tile) owns hidden units
-// [j0, j0+HC) for batch rows [b0, b0+BT).  Its slice of the recurrent weights is loaded by TMA
-// ONCE into shared memory as a K-major, 128-byte-swizzled UMMA operand and stays resident
-// for all S steps.  Per step: warp 0 streams the previous step's bf16 rows (all CTAs' output,
-// via L2) through a 4-stage TMA ring, one thread of warp 1 issues tcgen05.mma (M=128 batch
-// rows x N=gate columns, fp32 accumulators in TMEM), warps 2-5 read the accumulators with
-// tcgen05.ld, fuse bias(x-projection) + sigmoid/tanh + the cell update in registers, publish
-// h_t (fp32 for the optimiser side, bf16 for the next step's MMA) and join a grid barrier.
-// c_t / gate activations are stashed for BPTT on the way.
+// One cooperative launch per layer and direction (per sequence chunk, or for the whole sequence with chunk
+// flags, see RecTcArgs::nchunks).  CTA (slice, tile) owns hidden units [j0, j0+HC) for batch rows [b0, b0+BT).
+// Its slice of the recurrent weights is loaded by TMA ONCE into shared memory as a K-major, 128-byte-swizzled
+// UMMA operand and stays resident for all steps.  Per step and contraction:
+//   warp 0, one thread: waits (acquire polls) until every slice of the tile has released the previous step,
+//           then streams that step's bf16 rows from L2 - one 3-D TMA instruction for the whole K extent
+//           where it fits the ring, else a ring of ~32 KB stages;
+//   warp 1, converged: runs the MMA loop with warp-uniform operands; one elected lane issues the stage's
+//           tcgen05.mma (M = 64/128 batch rows x N = gate columns, fp32 accumulators in TMEM) back to back;
+//   warps 2-9: have every global operand of the cell update in flight before the accumulator arrives, move
+//           it TMEM -> shared, then each thread updates quads of adjacent units of one row (16-byte loads
+//           and stores), stores the re-quantised bf16 rows, releases the step (bar.sync + red.release.gpu)
+//           and only then writes what no other CTA waits for (fp32 state, gate stash for BPTT).
+// CRNN_PREC_BF16X3 ("split"): every bf16 array has a lo twin; weights are resident as [hi ; lo] rows per K
+// block and each K step issues A_hi*[W_hi|W_lo] and A_lo*W_hi (see rt_mma).
 #pragma once
 #include "tc_common.cuh"
 
