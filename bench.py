@@ -443,9 +443,13 @@ def main():
     if rank == 0:
         line = {"metric": "train_chars_per_sec", "value": value, "unit": "chars/s", "n_gpus": world, "steps": K,
                 "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": {"fp32": "f32", "bf16": "bf16", "bf16x3": "bf16x3 (split-bf16 tensor-core products, fp32 accumulate: fp32-grade)"}[args.precision], "data": "synthetic",
+                "dtype": {"fp32": "f32", "bf16": "bf16", "bf16x3": "bf16x3"}[args.precision], "data": "synthetic",
                 "config": {"workload": c["desc"], "name": args.config, "global_batch": world * B, "seq_length": S,
                            "parallelism": "dp%d" % world, "precision": args.precision,
+                           "precision_note": {"fp32": "fp32 FFMA contractions, 1e-4 parity",
+                                              "bf16": "bf16 tcgen05 contractions, fp32 accumulate and state, 1e-2 parity",
+                                              "bf16x3": "tcgen05 contractions on split-bf16 operands (hi*hi + lo*hi + hi*lo), fp32 "
+                                                        "accumulate and state: fp32-grade, 1e-4 parity"}[args.precision],
                            "l2": ("256 MB flush write between timed steps (excluded from timing)" if flush else
                                   "per-step working set %.0f MB > 126 MB L2, new batch every step" % (ws_bytes / 1e6))},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
