@@ -816,27 +816,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
 #undef CRNN_PICK
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
     CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // Optional clusters along the slice index (CRNN_TC_CLUSTER=2|4|8): the CTAs of a cluster work on the
-    // same batch tile, so the streamed rows are fetched from L2 once per cluster and multicast.  Measured
-    // on B200 it does not pay: config 4 is unchanged at 2 and 4 (its BPTT is bound by the number of small
-    // MMAs, N = 16, not by L2), a 16 x 8 cluster grid with ~200 KB of shared memory per CTA does not get
-    // co-scheduled at all, and config 3 loses 60 % at 8 - so it is off unless asked for.
     int csize = 1;
-    const int cmax = env_int("CRNN_TC_CLUSTER", 1);
-    for (int cs = 16; cs >= 2; cs >>= 1)
-        if (cs <= cmax && p.nslices % cs == 0 && (!split || a.use3d)) { csize = cs; break; }
-    if (csize > 1) {
-        // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
-        // memory hung the GPU.  The streamed rows live in the caller's workspace: unless the driver reports that buffer
-        // as plain device memory of the handle's own GPU, the launch falls back to one load per CTA.
-        const void* streamed = backward ? (const void*)a.dzb : (const void*)a.hxb;
-        cudaPointerAttributes pa;
-        if (cudaPointerGetAttributes(&pa, streamed) != cudaSuccess || pa.type != cudaMemoryTypeDevice || pa.device != h->cfg.device) {
-            cudaGetLastError();
-            csize = 1;
-        }
-    }
-    a.mcast = csize > 1 ? 1 : 0;
     a.cbar = 0;
     // Cluster barrier: when ALL slices of a batch tile fit in one cluster, the steps are ordered by remote
     // mbarrier arrives inside the cluster instead of a global counter polled through L2, and nothing ties
@@ -845,11 +825,11 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // config 3 but eight of them with ~190 KB of shared memory per CTA are not co-scheduled, which costs
     // the layer wavefront far more than that.
     const int cbar_max = env_int("CRNN_TC_CBAR", 8);
-    if (!a.mcast && p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
+    if (p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
         csize = p.nslices;
         a.cbar = 1;
     }
-    if (Q > 1) { csize = Q; a.mcast = 0; a.cbar = 0; }     // the cluster is the K-split group
+    if (Q > 1) { csize = Q; a.cbar = 0; }     // the cluster is the K-split group
     if (csize > 8) CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     a.csize = csize;
     void* args[] = {&t0, &t1, &w0, &w1, &t0l, &t1l, &w0l, &w1l, &a};

@@ -67,9 +67,8 @@ struct RecTcArgs {
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
     int ksplit;                 // Q: the contraction index is split over Q CTAs of a cluster; each contracts the columns of Q*HC
                                 // units over 1/Q of K and the partial sums are exchanged through distributed shared memory
-    int mcast;                  // 1: the streamed rows are TMA-multicast inside the cluster (ring barriers become cluster-wide)
     int cbar;                   // 1: the cluster holds ALL slices of a batch tile: steps are ordered by remote mbarrier arrives, no global counter
-    int csize;                  // CTAs per cluster along the slice index (1: no cluster); they share one batch tile's rows via TMA multicast
+    int csize;                  // CTAs per cluster along the slice index (1: no cluster): the K-split group or the slices of one batch tile (cbar)
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
     int split;                  // 1: every bf16 operand is a (hi, lo) pair (CRNN_PREC_BF16X3): hi*hi + lo*hi + hi*lo per K step
     long long hxb_lo, rsb_lo, dzb_lo;   // element offsets of the lo twins of hxb / rsb / dzb (0 when not split)
@@ -187,9 +186,8 @@ struct RtPipe {
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
-                                           int ckb, int nst, int use3d, int csize_in, int crank, int mcast, int kb_ofs = 0,
+                                           int ckb, int nst, int use3d, int kb_ofs = 0,
                                            const CUtensorMap* tmAlo = nullptr, int rot = 0, long long* stamps = nullptr) {
-    const int csize = mcast ? csize_in : 1;
     const int tile = rt_tile_bytes(box_rows);
     if (tmAlo) {                                       // split operands: hi tiles then lo tiles, one barrier per stage
         const int stage = 2 * ckb * tile;
@@ -201,12 +199,7 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
             uint8_t* hi = s.ring + st * stage;
             uint8_t* lo = hi + ckb * tile;
             const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;      // rotated start (rot is a multiple of ckb)
-            if (csize > 1) {                           // multicast (3-D maps only): the cluster's CTAs take turns, stage by stage
-                if ((int)(p.ring_i % (uint32_t)csize) != crank) continue;
-                const uint16_t mask = (uint16_t)((1u << csize) - 1u);
-                tma_load_3d_mc(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kb, mask);
-                tma_load_3d_mc(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kb, mask);
-            } else if (use3d) {
+            if (use3d) {
                 tma_load_3d(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
                 tma_load_3d(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kbr);
             } else {
@@ -218,32 +211,18 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
         }
         return;
     }
-    const uint16_t mask = (uint16_t)((1u << csize) - 1u);
     for (int kb = 0; kb < nkb; kb += ckb, p.advance(nst)) {
         const int st = (int)p.st;
         const int n = min(ckb, nkb - kb);
-        // (cluster: the empty barrier collects the MMA commits of EVERY CTA of the cluster, because the
-        //  CTA whose turn it is overwrites this stage in all of them)
         mbar_wait(&s.a_empty[st], p.ph ^ 1u);
         if (stamps && kb <= ckb) stamps[kb == 0 ? 19 : 21] = clock64();
         const uint32_t bytes = (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n);
         mbar_expect_tx(&s.a_full[st], bytes);
-        if (csize > 1) {
-            // every CTA arms its own barrier; the stages are issued round-robin by the cluster's CTAs and
-            // each issue is multicast to all of them
-            if ((int)(p.ring_i % (uint32_t)csize) != crank) continue;
-            if (use3d) {
-                tma_load_3d_mc(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kb, mask);
-            } else {
-                for (int j = 0; j < n; ++j)
-                    tma_load_2d_mc(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kb + j) * 64, arow, mask);
-            }
-        } else if (use3d) {                            // whole stage in one instruction (out-of-range k-blocks read zero)
-            const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;
+        const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;
+        if (use3d) {                                   // whole stage in one instruction (out-of-range k-blocks read zero)
             tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
             if (stamps && kb <= ckb) stamps[kb == 0 ? 20 : 22] = clock64();
         } else {
-            const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;
             for (int j = 0; j < n; ++j)
                 tma_load_2d(s.ring + (st * ckb + j) * tile, tmA, &s.a_full[st], (kb_ofs + kbr + j) * 64, arow);
         }
@@ -256,7 +235,7 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 //            resident data whose products land in accumulator lanes nobody reads.
 // Executed by ALL lanes of the (converged) MMA warp with warp-uniform arguments; one elected lane issues.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
-                                       int swap, int nrows16, int box_rows, int ckb, int nst, int m64, int csize,
+                                       int swap, int nrows16, int box_rows, int ckb, int nst, int m64,
                                        long long* stamps = nullptr, int split = 0, int rot = 0) {
     const int tile = rt_tile_bytes(box_rows);
     const bool lane0 = (threadIdx.x & 31) == 0;
@@ -319,8 +298,7 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
                     mma_bf16(tmem, db + 6, da + 6, idesc, 1u);
                 }
             }
-            if (csize > 1) mma_commit_mc(&s.a_empty[st], (uint16_t)((1u << csize) - 1u));
-            else           mma_commit(&s.a_empty[st]);
+            mma_commit(&s.a_empty[st]);
             if (kb0 + ckb >= nkb) mma_commit(s.z_full);      // last stage: the accumulator is complete
         }
         __syncwarp();
@@ -571,7 +549,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)(a.mcast ? a.csize : 1)); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
@@ -580,8 +558,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s.tmem_slot;
-    const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
-    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
+    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive
     int dbg_slot = -1;
     if (a.dbg) dbg_slot = blockIdx.x == 0 ? 0 : blockIdx.x == 1 ? 1 : blockIdx.x == gridDim.x / 2 ? 2 : blockIdx.x == gridDim.x - 1 ? 3 : -1;
     long long* dbgs = dbg_slot >= 0 ? s.dbg : nullptr;
@@ -589,7 +566,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
     const int nphase = MODEL == CRNN_MODEL_GRU ? 2 : 1;
-    const int rot = (a.rotate && !a.mcast && nkb % a.ckb == 0) ? (grp % (nkb / a.ckb)) * a.ckb : 0;
+    const int rot = (a.rotate && nkb % a.ckb == 0) ? (grp % (nkb / a.ckb)) * a.ckb : 0;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -611,7 +588,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb,
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb,
                                    a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr, rot,
                                    (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
                     RT_STAMP(2);
@@ -627,7 +604,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1,
+                        rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
                                (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot);
                     if (lane == 0) RT_STAMP(3);
                 }
@@ -854,7 +831,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], (uint32_t)(a.mcast ? a.csize : 1)); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
@@ -863,12 +840,11 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s.tmem_slot;
-    const int crank = a.csize > 1 ? (int)cluster_ctarank() : 0;
-    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive / multicast
+    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive
 
     RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
-    const bool rot_on = a.rotate && !a.mcast;
+    const bool rot_on = a.rotate != 0;
     const int rot0 = (rot_on && nkb0 % a.ckb == 0) ? (grp % (nkb0 / a.ckb)) * a.ckb : 0;
     const int rot1 = (rot_on && nkb1 % a.ckb == 0) ? (grp % (nkb1 / a.ckb)) * a.ckb : 0;
 
@@ -889,14 +865,14 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (t + 1 < a.S) {
                     if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb0,
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb0,
                                    a.split ? &tmZ0l : nullptr, rot0);
                 }
                 ++phases_done;
                 if (MODEL == CRNN_MODEL_GRU) {
                     if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll);
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, a.csize, crank, a.mcast, kq * nkb1,
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb1,
                                    a.split ? &tmZ1l : nullptr, rot1);
                     ++phases_done;
                 }
@@ -908,9 +884,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split, rot0);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, a.mcast ? a.csize : 1, nullptr, a.split, rot1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1);
             }
         }
     } else {

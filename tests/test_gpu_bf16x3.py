@@ -127,8 +127,7 @@ SHAPES = [
     ("rnn", 256, 2, 5, 70, 13, {"CRNN_TC_HC": 32, "CRNN_TC_KSPLIT": 2}),
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 0}),
     ("gru", 80, 2, 6, 24, 13, {"CRNN_TC_3D": 0}),           # H % 64 != 0: 2-D tile loads
-    ("gru", 64, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CLUSTER": 4}),   # hi and lo rows multicast inside a cluster
-    ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CLUSTER": 8}),
+    ("gru", 64, 2, 6, 40, 13, {"CRNN_TC_HC": 16}),
     ("gru", 512, 2, 12, 64, 96, {}),                        # config-3 layers, a short sequence
 ]
 

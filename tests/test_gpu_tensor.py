@@ -123,12 +123,8 @@ BF16_SHAPES = [
     ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_PERSIST": 0}),
     ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4, "CRNN_WF_PERSIST": 1, "CRNN_WF_HOIST0": 1}),
     ("rnn", 48, 3, 6, 12, 13, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_PERSIST": 0, "CRNN_WF_HOIST0": 1}),
-    # clusters of 8 / 4 / 2 slices sharing a batch tile through TMA multicast (and the same shape without)
-    ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CLUSTER": 8}), ("gru", 64, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CLUSTER": 8}),
-    ("rnn", 96, 2, 6, 70, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CLUSTER": 8}),
-    ("gru", 128, 1, 5, 300, 13, {"CRNN_TC_HC": 16, "CRNN_TC_TILES": 2, "CRNN_TC_CLUSTER": 8}),
-    ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16}),
-    ("gru", 128, 2, 7, 24, 13, {"CRNN_TC_HC": 16, "CRNN_WAVEFRONT": 1, "CRNN_TC_CLUSTER": 4}),
+    ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16}), ("rnn", 96, 2, 6, 70, 13, {"CRNN_TC_HC": 16}),
+    ("gru", 128, 1, 5, 300, 13, {"CRNN_TC_HC": 16, "CRNN_TC_TILES": 2}),
     # K split over a cluster of 2 / 4 CTAs, partial sums exchanged through distributed shared memory
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 2}),
     ("gru", 256, 1, 5, 20, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 4}),
