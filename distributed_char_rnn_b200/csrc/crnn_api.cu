@@ -77,7 +77,6 @@ struct crnn_handle {
     RecPlanTc tcp;
     // wavefront over layers (tensor path): wf_W layer streams, each sequence cut into wf_C chunks
     int wf_W, wf_C;
-    int wf_persist;   // 1: one recurrence launch per layer and direction, chunk hand-over through device flags
     std::vector<cudaStream_t> wf_streams;
     std::vector<cudaEvent_t> wf_events;
     // dropout (training calls only): keep probabilities, seed, and the count of training calls so far
@@ -149,10 +148,6 @@ static const float kBeta1 = 0.9f, kBeta2 = 0.999f, kEps = 1e-8f;
 static const size_t kScratchBytes = 32768 + 512 * 256;   // 512 barrier blocks after the first 32 KB
 // one 256-byte block of barrier counters per recurrence launch (2 per layer), after the first 8 KB
 static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>((char*)ws + 32768 + (size_t)i * 256); }
-// chunk flags of the persistent wavefront launches: one 256-byte block (64 chunks) per layer and kind,
-// taken from the top of the barrier-block pool (blocks 384..511; the per-launch barrier blocks use 0..2*L*C)
-static inline unsigned* ws_flags(void* ws, int kind, int l) { return ws_barrier(ws, 384 + kind * 32 + l); }
-enum { FLAG_XREADY = 0, FLAG_FWD_DONE = 1, FLAG_DYREADY = 2, FLAG_BWD_DONE = 3 };
 static inline double* ws_loss(void* ws) { return reinterpret_cast<double*>((char*)ws + 256); }
 static inline double* ws_sq(void* ws) { return reinterpret_cast<double*>((char*)ws + 264); }
 static inline double* ws_partials(void* ws) { return reinterpret_cast<double*>((char*)ws + 1024); }
@@ -445,7 +440,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->okp = (cfg->output_keep_prob > 0.f && cfg->output_keep_prob < 1.f) ? cfg->output_keep_prob : 1.0f;
     h->drop_on = h->ikp < 1.0f || h->okp < 1.0f;
     h->fb_calls = 0;
-    h->wf_W = 1; h->wf_C = 1; h->wf_persist = 0;
+    h->wf_W = 1; h->wf_C = 1;
     if (rc == CRNN_OK && h->tc) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
         // 1/W of the SMs, the sequence cut into C chunks so layer l+1 starts when layer l has produced
@@ -471,23 +466,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 32);
             if (W == 1) C = 1;
             h->wf_C = C;
-            // Measured on B200: one launch per layer instead of one per chunk pays where the per-chunk launches are short
-            // (config 1: 0.75 -> 0.70 ms bf16, 0.84 -> 0.78 ms split) and not where the chunk GEMMs need the SMs the
-            // chunked launches free between chunks (config 3: 3.11 -> 3.17 ms bf16, 5.08 -> 5.91 ms split), so it is on for
-            // recurrent weights <= 512 KB per layer.
-            h->wf_persist = (W > 1 && cfg->num_layers <= 32 && C <= 64 && env_int("CRNN_WF_PERSIST", wbytes <= (512 << 10) ? 1 : 0)) ? 1 : 0;
-            if (h->wf_persist) {
-                // A persistent recurrence kernel spins on flags that LATER launches on other streams set.  With lazy module
-                // loading the first launch of a kernel may wait for running kernels to finish - a deadlock - so every
-                // kernel that can be launched while one is spinning is loaded here.
-                cudaFuncAttributes fa;
-                const void* fns[] = {(const void*)tc::gemm_bf16_tc_kernel<128, 3, false>, (const void*)tc::gemm_bf16_tc_kernel<128, 3, true>,
-                                     (const void*)wait_ge_kernel, (const void*)set_flags_kernel, (const void*)dropout_apply_kernel,
-                                     (const void*)tc::cast_bf16_kernel, (const void*)colsum_kernel};
-                for (const void* f : fns)
-                    if (cudaFuncGetAttributes(&fa, f) != cudaSuccess) { rc = set_err(CRNN_ERR_CUDA, "cudaFuncGetAttributes failed"); break; }
-            }
-            if (!h->wf_persist) while (C > 1 && 2 * cfg->num_layers * C > 384) --C, h->wf_C = C;   // barrier blocks 0..383
+            while (C > 1 && 2 * cfg->num_layers * C > 384) --C, h->wf_C = C;   // barrier blocks 0..383
             for (int i = 0; i < 2 * W && W > 1; ++i) {      // [0,W): recurrence streams, [W,2W): GEMM streams
                 cudaStream_t s;
                 if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { rc = set_err(CRNN_ERR_CUDA, "cudaStreamCreate failed"); break; }
@@ -1041,27 +1020,10 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, s>>>(hin, H, B, H, hxb, H, lo.hxb);
         CRNN_LAUNCH_CHECK("cast_bf16_kernel");
         cudaStream_t gs = wf_gstream(h, st, l);
-        // Persistent form of the wavefront: ONE recurrence launch per layer covers the whole sequence and follows
-        // the chunked GEMMs through flags in device memory (rt_wait_flag / rt_signal_flag in the kernel, a stream-ordered
-        // memset / wait_ge_kernel on the GEMM stream), instead of one launch + event per chunk.
-        const bool persist = wf && h->wf_persist && env_int("CRNN_WF_PERSIST_FWD", 1);
-        if (persist) {
-            tc::RecTcArgs a{};
-            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = 0; a.t_end = S;
-            a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
-            a.rsb = c.model == CRNN_MODEL_GRU ? wsb(ws, h->ws.rsb[l]) : nullptr;
-            a.barrier = ws_barrier(ws, l);
-            a.nchunks = C; a.in_flags = ws_flags(ws, FLAG_XREADY, l); a.out_flags = ws_flags(ws, FLAG_FWD_DONE, l);
-            rc = launch_rec_tc_model(h, false, a, nullptr, nullptr, wsb(ws, h->ws.wr[l]), s);
-            if (rc != CRNN_OK) return rc;
-        }
         for (int ck = 0; ck < C; ++ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
-            if (persist && l > 0) {                  // layer l-1 has finished this chunk on every CTA
-                wait_ge_kernel<<<1, 1, 0, gs>>>(ws_flags(ws, FLAG_FWD_DONE, l - 1) + ck, (unsigned)(h->tcp.nslices * h->tcp.ntiles));
-                CRNN_LAUNCH_CHECK("wait_ge_kernel");
-            } else if (wf && l > 0) {                // layer l-1 has produced this chunk's inputs
+            if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
                 rc = wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }
@@ -1085,11 +1047,6 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
                 rc = gemm_tc(h, rows, GH, H, ain, H, 0, in_lo, pbf + lp.oW, GH, 1, lo.pbf, gch, gw, lp.b, 0, gs);
             }
             if (rc != CRNN_OK) return rc;
-            if (persist) {                           // the running kernel may start this chunk
-                set_flags_kernel<<<1, 32, 0, gs>>>(ws_flags(ws, FLAG_XREADY, l) + ck, 1);
-                CRNN_LAUNCH_CHECK("set_flags_kernel");
-                continue;
-            }
             if (wf) {
                 rc = wf_record(h, wf_id(h, 1, l, ck), gs);
                 if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 1, l, ck), s);
@@ -1184,28 +1141,9 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         bf16_t* dzb = wsb(ws, h->ws.dzbv[l]);
         float* dnext = l > 0 ? wsf(ws, h->ws.gout[l - 1]) : wsf(ws, h->ws.gx0);
         cudaStream_t gs = wf_gstream(h, st, l);
-        const bool persist = wf && h->wf_persist && env_int("CRNN_WF_PERSIST_BWD", 1);    // see run_forward_bf16
-        const unsigned nctas = (unsigned)(h->tcp.nslices * h->tcp.ntiles);
-        if (persist) {
-            tc::RecTcArgs a{};
-            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = 0; a.t_end = S;
-            a.gates = gates; a.hx = hx; a.cx = cx;
-            a.dy = wsf(ws, h->ws.gout[l]); a.dz = dz; a.dzb = dzb;
-            a.carry0 = wsf(ws, h->ws.carry0v[l]); a.carry1 = wsf(ws, h->ws.carry1v[l]);
-            a.barrier = ws_barrier(ws, 32 + l);
-            a.nchunks = C; a.in_flags = ws_flags(ws, FLAG_DYREADY, l); a.out_flags = ws_flags(ws, FLAG_BWD_DONE, l);
-            if (l == L - 1)                              // the projection gradients are complete: every chunk of dy is there
-                { set_flags_kernel<<<1, 32, 0, s>>>(ws_flags(ws, FLAG_DYREADY, l), C); CRNN_LAUNCH_CHECK("set_flags_kernel"); }
-            rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, s);
-            if (rc != CRNN_OK) return rc;
-        }
         for (int ck = C - 1; ck >= 0; --ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
-            if (persist) {                           // this layer's running kernel has finished the chunk on every CTA
-                wait_ge_kernel<<<1, 1, 0, gs>>>(ws_flags(ws, FLAG_BWD_DONE, l) + ck, nctas);
-                CRNN_LAUNCH_CHECK("wait_ge_kernel");
-            } else {
             if (wf && l < L - 1) {                   // layer l+1 has produced this chunk's output gradients
                 rc = wf_wait(h, wf_id(h, 3, l + 1, ck), s);
                 if (rc != CRNN_OK) return rc;
@@ -1224,7 +1162,6 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
                 if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 2, l, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }
-            }
             // input gradients of the chunk: dIn = dz * Wx^T (A = dz K-major, B = kernel rows 0..H as [N,K])
             if (!wf) prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
             const bf16_t* dzc = dzb + (int64_t)t0 * B * zw;
@@ -1240,9 +1177,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             }
             if (rc == CRNN_OK && drop) rc = drop_apply(h, call, l, dn, dn, nullptr, (int64_t)t0 * BH, (int64_t)rows * H, gs);
             if (rc != CRNN_OK) return rc;
-            if (persist) {                           // layer l-1's running kernel may start this chunk
-                if (l > 0) { set_flags_kernel<<<1, 32, 0, gs>>>(ws_flags(ws, FLAG_DYREADY, l - 1) + ck, 1); CRNN_LAUNCH_CHECK("set_flags_kernel"); }
-            } else if (wf) {
+            if (wf) {
                 rc = wf_record(h, wf_id(h, 3, l, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }

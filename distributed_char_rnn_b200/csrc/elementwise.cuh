@@ -102,23 +102,6 @@ __global__ void __launch_bounds__(256) dropout_apply_kernel(const float* __restr
     }
 }
 
-// Stream-ordered wait on a device counter another kernel advances (layer wavefront: the batch GEMMs of a chunk wait
-// for the persistent recurrence kernel that is still running to have finished that chunk).  One thread spins.
-__global__ void wait_ge_kernel(const unsigned* __restrict__ flag, unsigned target) {
-    unsigned v;
-    do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-        if (v < target) __nanosleep(500);
-    } while (v < target);
-}
-
-// The matching stream-ordered signal (a memset would do, but its driver-internal kernel may be loaded lazily, and a
-// module load while a persistent kernel is spinning on this very flag never returns).
-__global__ void set_flags_kernel(unsigned* __restrict__ flags, int n) {
-    for (int i = threadIdx.x; i < n; i += blockDim.x) flags[i] = 1u;
-    __threadfence();
-}
-
 // ---- softmax + sequence cross-entropy (model.py:77,80-85) ---------------------------------
 // One warp per row of logits [N, V] (row i = t*B + b).  In place: logits -> (softmax-onehot)/N.
 __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ logits, int B, int S, int V,

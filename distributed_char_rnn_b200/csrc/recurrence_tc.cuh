@@ -4,8 +4,7 @@
 // reverse-mode mirror (model.py:88-91): per time step only h_{t-1} * W_h (forward) or
 // dz_{t+1} * W_h^T (backward) remains once the x halves are hoisted into batch GEMMs.
 //
-// One cooperative launch per layer and direction (per sequence chunk, or for the whole sequence with chunk
-// flags, see RecTcArgs::nchunks).  CTA (slice, tile) owns hidden units [j0, j0+HC) for batch rows [b0, b0+BT).
+// One cooperative launch per layer, direction and sequence chunk.  CTA (slice, tile) owns hidden units [j0, j0+HC) for batch rows [b0, b0+BT).
 // Its slice of the recurrent weights is loaded by TMA ONCE into shared memory as a K-major, 128-byte-swizzled
 // UMMA operand and stays resident for all steps.  Per step and contraction:
 //   warp 0, one thread: waits (acquire polls) until every slice of the tile has released the previous step,
@@ -73,13 +72,6 @@ struct RecTcArgs {
     int split;                  // 1: every bf16 operand is a (hi, lo) pair (CRNN_PREC_BF16X3): hi*hi + lo*hi + hi*lo per K step
     long long hxb_lo, rsb_lo, dzb_lo;   // element offsets of the lo twins of hxb / rsb / dzb (0 when not split)
     int expt;                   // timing experiments only (CRNN_TC_EXPT; results are wrong when set): 1 no critical stores, 2 no math, 4 no deferred stores (fwd)
-    // One launch for the whole sequence while its inputs / consumers work chunk by chunk on other streams
-    // (layer wavefront): before the first step of chunk c the epilogue waits until in_flags[c] != 0 (the batch GEMM
-    // that produces the chunk's hoisted inputs has finished), and after the last step of chunk c every CTA adds 1 to
-    // out_flags[c] (all of its stores included).  nchunks == 0: no flags.
-    int nchunks;
-    const unsigned* in_flags;
-    unsigned* out_flags;
     int acq_poll;               // 1: the step barrier is polled with acquire loads (no fence after the poll loop)
     int defer;                  // 1: stores only this CTA reads later are issued after the step barrier's release
     int rotate;                 // 1: slices of a tile walk the K blocks from different starting stages, so they do not all
@@ -115,19 +107,6 @@ __device__ __forceinline__ float tanh_ex2(float x) { return 1.0f - __fdividef(2.
 #define fast_tanh(x) (FAST ? tanh_mufu(x) : tanh_ex2(x))
 #define fast_sigmoid(x) (FAST ? fmaf(0.5f, tanh_mufu(0.5f * (x)), 0.5f) : sigmoid_ex2(x))
 
-__host__ __device__ inline int rt_chunk_t0(int S, int C, int c) { return (int)((long long)S * c / C); }
-// epilogue thread 0 spins (acquire) on a flag another stream's work sets; the barrier orders everybody else behind it
-__device__ __forceinline__ void rt_wait_flag(const unsigned* flag) {
-    unsigned v;
-    do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-        if (v == 0) __nanosleep(200);
-    } while (v == 0);
-}
-__device__ __forceinline__ void rt_signal_flag(unsigned* flag) {
-    __threadfence();
-    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(flag) : "memory");
-}
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(RT_EPI_THREADS) : "memory"); }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
@@ -615,12 +594,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         const int epi_tid = (warp - 2) * 32 + lane;
         uint32_t zpeer[4] = {0, 0, 0, 0};            // the peers' accumulator staging areas (distributed shared memory)
         if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
-        int chunk = 0;                                // (flags only when the launch covers the whole sequence)
         for (int t = a.t_begin; t < a.t_end; ++t) {
-            if (a.nchunks > 0 && t == rt_chunk_t0(a.S, a.nchunks, chunk)) {       // the chunk's x-projection has been written
-                if (epi_tid == 0) rt_wait_flag(a.in_flags + chunk);
-                epi_bar_sync();
-            }
             const int64_t tB = (int64_t)t * B;
             float* gt = a.gates;
             const float* hprev = a.hx + (int64_t)t * BH;
@@ -774,11 +748,6 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 }
                 if (epi_tid == 0) RT_STAMP(13);
             }
-            if (a.nchunks > 0 && t + 1 == rt_chunk_t0(a.S, a.nchunks, chunk + 1)) {   // chunk complete on this CTA
-                epi_bar_sync();
-                if (epi_tid == 0) rt_signal_flag(a.out_flags + chunk);
-                ++chunk;
-            }
         }
     }
     __syncthreads();
@@ -902,12 +871,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 a.carry0[(int64_t)(b0 + r) * H + j0 + jj] = 0.f;
             }
         }
-        int chunk = a.nchunks - 1;
         for (int t = a.t_end - 1; t >= a.t_begin; --t) {
-            if (a.nchunks > 0 && t + 1 == rt_chunk_t0(a.S, a.nchunks, chunk + 1)) {   // the chunk's output gradients have been written
-                if (epi_tid == 0) rt_wait_flag(a.in_flags + chunk);
-                epi_bar_sync();
-            }
             const bool has_next = t + 1 < a.S;
             const int64_t tB = (int64_t)t * B;
             // Same split as the forward epilogue: only the bf16 dz rows other CTAs stream next are stored before the
@@ -1098,11 +1062,6 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                         stv<VEC>(a.carry0 + ob + e[qd].r * H + e[qd].jj, v4 + VEC * qd);
                     }
                 }
-            }
-            if (a.nchunks > 0 && t == rt_chunk_t0(a.S, a.nchunks, chunk)) {          // chunk complete on this CTA
-                epi_bar_sync();
-                if (epi_tid == 0) rt_signal_flag(a.out_flags + chunk);
-                --chunk;
             }
         }
     }

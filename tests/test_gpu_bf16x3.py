@@ -121,8 +121,8 @@ SHAPES = [
     ("gru", 64, 2, 5, 40, 17, {"CRNN_TC_SWAP": 1}), ("lstm", 32, 2, 6, 20, 11, {"CRNN_TC_SWAP": 1}),
     ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3}),
     ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 1}),
-    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4, "CRNN_WF_PERSIST": 0}),
-    ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_PERSIST": 1, "CRNN_WF_HOIST0": 1}),
+    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4}),
+    ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_HOIST0": 1}),
     ("gru", 256, 1, 5, 20, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 4}),
     ("rnn", 256, 2, 5, 70, 13, {"CRNN_TC_HC": 32, "CRNN_TC_KSPLIT": 2}),
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 0}),

@@ -117,12 +117,11 @@ BF16_SHAPES = [
     ("rnn", 48, 3, 6, 12, 13, {"CRNN_WAVEFRONT": 3, "CRNN_WAVEFRONT_CHUNKS": 2}),
     ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 1}),
     ("lstm", 64, 2, 5, 8, 9, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 5}),
-    # the same wavefront as one launch per chunk (events) instead of one launch per layer (device flags), and with
-    # layer 0's batch GEMMs hoisted out of it
-    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4, "CRNN_WF_PERSIST": 0}),
-    ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_PERSIST": 0}),
-    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4, "CRNN_WF_PERSIST": 1, "CRNN_WF_HOIST0": 1}),
-    ("rnn", 48, 3, 6, 12, 13, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_PERSIST": 0, "CRNN_WF_HOIST0": 1}),
+    # the same wavefront with layer 0's batch GEMMs hoisted out of it
+    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4}),
+    ("lstm", 32, 3, 7, 9, 11, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3}),
+    ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4, "CRNN_WF_HOIST0": 1}),
+    ("rnn", 48, 3, 6, 12, 13, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_HOIST0": 1}),
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16}), ("rnn", 96, 2, 6, 70, 13, {"CRNN_TC_HC": 16}),
     ("gru", 128, 1, 5, 300, 13, {"CRNN_TC_HC": 16, "CRNN_TC_TILES": 2}),
     # K split over a cluster of 2 / 4 CTAs, partial sums exchanged through distributed shared memory
