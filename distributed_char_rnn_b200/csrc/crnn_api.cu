@@ -57,6 +57,8 @@ struct RecPlanTc {
     int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
     int q_fwd, q_bwd;       // K parts per unit group (cluster size) of the forward / backward kernel
     int ring_fwd, ring_bwd; // TMA ring bytes
+    int gather;             // 1: direct exchange of the streamed rows (recurrence_tc.cuh: rt_gather) instead of TMA loads behind a step barrier
+    int g_rp_log2, g_ckb_log2;
     size_t smem_fwd, smem_bwd;
 };
 
@@ -86,6 +88,7 @@ struct crnn_handle {
     int split;            // 1: CRNN_PREC_BF16X3, every bf16 operand array is followed by its lo twin
     long long fb_calls;
     long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
+    unsigned* err_word;   // host-mapped word a kernel sets when one of its bounded waits expires
     int dbg_layer;        // the layer whose forward launches record stamps
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
     int fast_act;
@@ -286,6 +289,33 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
             one(&o->smem_fwd, &o->ring_fwd, o->q_fwd);
             one(&o->smem_bwd, &o->ring_bwd, o->q_bwd);
         }
+        // Direct exchange (CRNN_TC_GATHER=1, recurrence_tc.cuh: rt_validate / rt_probe): no step barrier; the streamed rows
+        // carry their own readiness (sentinel-filled slots, landed stages checked in shared memory).  Single-pass tiles,
+        // batch rows on M, no K split; stages of at most 16 KB per operand half and at most 4096 chunks.
+        // Measured on B200 (config 3, bf16, ms per step): barrier protocol 3.04; direct exchange 3.83-4.05 - the check of
+        // the landed rows by the epilogue threads costs ~4 k cycles per phase next to the other layer's kernel; with the
+        // check switched off (wrong results, timing only) 3.02, i.e. removing MEMBAR + flag + acquire poll from the chain
+        // buys ~1 k of ~10 k cycles per phase in the forward kernel and nothing over the whole step.  A kernel running
+        // alone gains 18 % (6.9 k vs 8.4-9.3 k cycles per phase).  Off by default.
+        o->gather = 0; o->g_rp_log2 = o->g_ckb_log2 = 0;
+        if (env_int("CRNN_TC_GATHER", 0) && o->npass == 1 && o->q_fwd == 1 && o->q_bwd == 1 && !o->swap_fwd && !o->swap_bwd) {
+            const int tile = tc::rt_tile_bytes(o->box_rows), nsp = 1 + h->split;
+            int rp = 5; while ((1 << rp) < BT) ++rp;
+            int ck = 0;
+            while ((2 << ck) <= nkb && nsp * (1 << rp) * (2 << ck) * 8 <= 4096 && (2 << ck) * tile <= 16384) ++ck;
+            { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) { ck = 0; while ((2 << ck) <= ck_env && (2 << ck) <= nkb && nsp * (1 << rp) * (2 << ck) * 8 <= 4096) ++ck; } }
+            if (nsp * (1 << rp) * (1 << ck) * 8 <= 4096) {
+                o->gather = 1; o->g_rp_log2 = rp; o->g_ckb_log2 = ck;
+                const int cap = env_int("CRNN_TC_RING_KB", 128) * 1024;
+                auto grow2 = [&](size_t* smem, int* ring) {
+                    const int spare = ((h->max_smem - (int)*smem) / 1024) * 1024;
+                    const int add = std::max(0, std::min(spare, cap - *ring));
+                    *ring += add; *smem += (size_t)add;
+                };
+                grow2(&o->smem_fwd, &o->ring_fwd);
+                grow2(&o->smem_bwd, &o->ring_bwd);
+            }
+        }
         return true;
     };
     // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
@@ -440,6 +470,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->okp = (cfg->output_keep_prob > 0.f && cfg->output_keep_prob < 1.f) ? cfg->output_keep_prob : 1.0f;
     h->drop_on = h->ikp < 1.0f || h->okp < 1.0f;
     h->fb_calls = 0;
+    h->err_word = nullptr;
     h->wf_W = 1; h->wf_C = 1;
     if (rc == CRNN_OK && h->tc) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
@@ -474,7 +505,11 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             }
         }
     }
-    if (rc != CRNN_OK) { for (cudaStream_t s_ : h->wf_streams) cudaStreamDestroy(s_); delete h; return rc; }
+    if (rc == CRNN_OK && h->tc) {
+        if (cudaHostAlloc((void**)&h->err_word, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); rc = set_err(CRNN_ERR_CUDA, "cudaHostAlloc failed"); }
+        else *h->err_word = 0u;
+    }
+    if (rc != CRNN_OK) { for (cudaStream_t s_ : h->wf_streams) cudaStreamDestroy(s_); if (h->err_word) cudaFreeHost(h->err_word); delete h; return rc; }
     build_workspace(h);
     *out = h;
     return CRNN_OK;
@@ -486,6 +521,7 @@ void crnn_destroy(crnn_handle* h) {
     for (cudaEvent_t e : h->kev) cudaEventDestroy(e);
     for (cudaEvent_t e : h->wf_events) if (e) cudaEventDestroy(e);
     for (cudaStream_t s : h->wf_streams) cudaStreamDestroy(s);
+    if (h->err_word) cudaFreeHost(h->err_word);
     delete h;
 }
 
@@ -742,6 +778,9 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         const int tile = tc::rt_tile_bytes(p.box_rows);
         while (a.ckb > 1 && (a.ring_bytes - tc::RT_MROWS_BYTES + tile) / (tile * a.ckb * (1 + split)) < env_int("CRNN_TC_MIN_STAGES", 2)) --a.ckb;
     }
+    a.gather = p.gather; a.g_rp_log2 = p.g_rp_log2; a.g_ckb_log2 = p.g_ckb_log2;
+    a.err = h->err_word;
+    if (a.gather) a.ckb = 1 << p.g_ckb_log2;
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb, split, a.ring_bytes);
     a.use3d = (H % 64 == 0 && env_int("CRNN_TC_3D", 1)) ? 1 : 0;
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
@@ -804,7 +843,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // config 3 but eight of them with ~190 KB of shared memory per CTA are not co-scheduled, which costs
     // the layer wavefront far more than that.
     const int cbar_max = env_int("CRNN_TC_CBAR", 8);
-    if (p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
+    if (!a.gather && p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
         csize = p.nslices;
         a.cbar = 1;
     }
@@ -1020,6 +1059,14 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         tc::cast_bf16_kernel<<<grid_for(BH, sc), 256, 0, s>>>(hin, H, B, H, hxb, H, lo.hxb);
         CRNN_LAUNCH_CHECK("cast_bf16_kernel");
         cudaStream_t gs = wf_gstream(h, st, l);
+        if (h->tcp.gather) {
+            // direct exchange: the slots of the FIRST chunk start as the sentinel (later chunks are filled by the launch before them)
+            const int64_t n0 = (int64_t)wf_t0(h, 1) * BH;
+            for (int half = 0; half <= h->split; ++half) {
+                CRNN_CUDA(cudaMemsetAsync(hxb + BH + half * lo.hxb, 0xFF, n0 * sizeof(bf16_t), s));
+                if (c.model == CRNN_MODEL_GRU) CRNN_CUDA(cudaMemsetAsync(wsb(ws, h->ws.rsb[l]) + half * lo.act, 0xFF, n0 * sizeof(bf16_t), s));
+            }
+        }
         for (int ck = 0; ck < C; ++ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
@@ -1056,6 +1103,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
             a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
             a.rsb = c.model == CRNN_MODEL_GRU ? wsb(ws, h->ws.rsb[l]) : nullptr;
+            a.fill_t0 = t1; a.fill_t1 = ck + 1 < C ? wf_t0(h, ck + 2) : t1;
             a.barrier = ws_barrier(ws, l * C + ck);
             if (!wf) prof_mark(h, st, CRNN_PHASE_REC_FWD);
             rc = launch_rec_tc_model(h, false, a, nullptr, nullptr, wsb(ws, h->ws.wr[l]), s);
@@ -1141,6 +1189,11 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         bf16_t* dzb = wsb(ws, h->ws.dzbv[l]);
         float* dnext = l > 0 ? wsf(ws, h->ws.gout[l - 1]) : wsf(ws, h->ws.gx0);
         cudaStream_t gs = wf_gstream(h, st, l);
+        if (h->tcp.gather) {                         // sentinel over the LAST chunk's dz slots (see run_forward_bf16)
+            const int64_t r0 = (int64_t)wf_t0(h, C - 1) * B * zw, n0 = (int64_t)(S - wf_t0(h, C - 1)) * B * zw;
+            for (int half = 0; half <= h->split; ++half)
+                CRNN_CUDA(cudaMemsetAsync(dzb + r0 + half * lo.dzb, 0xFF, n0 * sizeof(bf16_t), s));
+        }
         for (int ck = C - 1; ck >= 0; --ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
@@ -1153,6 +1206,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             a.gates = gates; a.hx = hx; a.cx = cx;
             a.dy = wsf(ws, h->ws.gout[l]); a.dz = dz; a.dzb = dzb;
             a.carry0 = wsf(ws, h->ws.carry0v[l]); a.carry1 = wsf(ws, h->ws.carry1v[l]);
+            a.fill_t0 = ck > 0 ? wf_t0(h, ck - 1) : t0; a.fill_t1 = t0;
             a.barrier = ws_barrier(ws, L * C + l * C + ck);
             if (!wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
             rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, s);
@@ -1235,6 +1289,8 @@ static int check_common(crnn_handle* h, const void* a, const void* b, const void
     CRNN_CUDA(cudaSetDevice(h->cfg.device));
     if (h->cfg.batch_size > 2 * 1024 * 1024) return set_err(CRNN_ERR_ARG, "batch too large");
     if (h->cfg.num_layers > 32) return set_err(CRNN_ERR_ARG, "at most 32 layers");
+    if (h->err_word && *reinterpret_cast<volatile unsigned*>(h->err_word))
+        return set_err(CRNN_ERR_CUDA, "a recurrence kernel of an earlier call gave up waiting for a peer slice's rows (results of that call are invalid)");
     return CRNN_OK;
 }
 

@@ -72,6 +72,15 @@ struct RecTcArgs {
     int split;                  // 1: every bf16 operand is a (hi, lo) pair (CRNN_PREC_BF16X3): hi*hi + lo*hi + hi*lo per K step
     long long hxb_lo, rsb_lo, dzb_lo;   // element offsets of the lo twins of hxb / rsb / dzb (0 when not split)
     int expt;                   // timing experiments only (CRNN_TC_EXPT; results are wrong when set): 1 no critical stores, 2 no math, 4 no deferred stores (fwd)
+    // Direct exchange (gather != 0): no step barrier at all.  The bf16 rows a phase streams are copied from global memory
+    // into the ring by the epilogue threads themselves, and every 16-bit half of the copied words is checked against a
+    // sentinel (0xFFFF, a NaN pattern no conversion produces) the slots were filled with before: a word is either still
+    // the sentinel or final, so data needs no flag, no fence and no poll of a counter - see rt_validate.
+    int gather;
+    int g_rp_log2;              // log2 of the tile's rows padded to a power of two (>= 32)
+    int g_ckb_log2;             // log2(ckb): K blocks per ring stage
+    int fill_t0, fill_t1;       // steps whose output slots this launch fills with the sentinel for the NEXT launch of the chain
+    unsigned* err;              // set to 1 when a wait ran into its bound (host-mapped; the host turns it into CRNN_ERR_CUDA)
     int acq_poll;               // 1: the step barrier is polled with acquire loads (no fence after the poll loop)
     int defer;                  // 1: stores only this CTA reads later are issued after the step barrier's release
     int rotate;                 // 1: slices of a tile walk the K blocks from different starting stages, so they do not all
@@ -119,9 +128,43 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
         if (dbgs && dbg_phase >= 20 && dbg_phase < 28) dbgs[(dbg_phase - 20) * 24 + (slot)] = clock64(); \
     } while (0)
 
+
+// ---- direct exchange of the streamed rows --------------------------------------------------------------------------
+// Producers store final bf16 words straight to L2 (.cg), consumers read them from L2 (.cg: never from this SM's L1, which
+// could hold a stale copy of the line) until no 16-bit half is the sentinel.  Each 32-bit word is written exactly once
+// between two fills.  (Measured: the same loads as ld.relaxed.gpu are issued one at a time - sixteen of them took 7 k
+// cycles, one L2 round trip each - while .cg loads pipeline.)
+constexpr int RT_GATHER_SLOTS = 16;            // 16-byte chunks one thread keeps in flight
+constexpr int RT_GATHER_SPINS = 1 << 22;       // re-reads of one chunk before the wait is declared dead (seconds)
+__device__ __forceinline__ uint4 ld_relaxed_gpu_v4(const void* p) {     // coherent at gpu scope (LDG.STRONG.GPU): always from L2
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+// First attempt: a weak load that does not allocate in L1.  Strong loads of one thread complete one at a time (measured:
+// sixteen took 7 k cycles, one L2 round trip each); these pipeline.  Should L1 ever serve one of them from a stale line,
+// the stale value can only be the sentinel (every word is written once per fill), and the retry below uses strong loads.
+__device__ __forceinline__ uint4 ld_weak_nol1_v4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_gpu_v2(void* p, uint32_t a, uint32_t b) {
+    asm volatile("st.global.cg.v2.b32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_gpu_b16(void* p, uint16_t a) {
+    asm volatile("st.global.cg.b16 [%0], %1;" ::"l"(p), "h"(a) : "memory");
+}
+__device__ __forceinline__ bool rt_has_sentinel(const uint4& v) {
+    return (__vcmpeq2(v.x, 0xFFFFFFFFu) | __vcmpeq2(v.y, 0xFFFFFFFFu) | __vcmpeq2(v.z, 0xFFFFFFFFu) | __vcmpeq2(v.w, 0xFFFFFFFFu)) != 0u;
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t saddr, const uint4& v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 struct RtSmem {
     uint8_t* wsa; uint8_t* wsb; uint8_t* ring; float* zs;
-    uint64_t *a_full, *a_empty, *z_full, *z_empty, *w_bar, *step_bar, *zs_ready, *zs_free;
+    uint64_t *a_full, *a_empty, *a_valid, *z_full, *z_empty, *w_bar, *step_bar, *zs_ready, *zs_free;
     uint32_t* tmem_slot;
     long long* dbg;          // 8 phases x 24 stamps
 };
@@ -135,7 +178,8 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     s.zs = reinterpret_cast<float*>(p); p += (size_t)((zs_floats + 3) & ~3) * 4;
     s.a_full = reinterpret_cast<uint64_t*>(p);
     s.a_empty = s.a_full + RT_MAX_STAGES;
-    s.z_full = s.a_empty + RT_MAX_STAGES;
+    s.a_valid = s.a_empty + RT_MAX_STAGES;
+    s.z_full = s.a_valid + RT_MAX_STAGES;
     s.z_empty = s.z_full + 1;
     s.w_bar = s.z_empty + 1;
     s.step_bar = s.w_bar + 1;
@@ -161,6 +205,147 @@ struct RtPipe {
         if (++st == (uint32_t)nst) { st = 0; ph ^= 1u; }
     }
 };
+
+// The streamed operand of one contraction, copied by the RT_EPI_THREADS epilogue threads (RecTcArgs::gather): rows
+// [row0, row0 + nrows) x columns [k0, k0 + nkb*64) of `src` (row pitch `ld` elements, lo twin `lo_ofs` elements
+// further when nsp == 2) go into the ring stage by stage, each K block as a K-major tile of 128-byte rows whose
+// 16-byte chunks are XOR-swizzled by (row & 7) - what a SWIZZLE_128B TMA load would have produced.  Chunk index
+// inside a stage: [half][row (padded to 2^rp_log2)][K block][chunk of 8 elements]; thread i owns chunks i, i + 256, ...
+// so a warp reads whole contiguous row segments and its shared-memory stores cover all banks.  The low 8 bits of a
+// chunk index are the thread's (column, K block, low row bits - fixed for the whole kernel), the high bits the slot's
+// (block-uniform), so per chunk only a handful of instructions remain.  Up to RT_GATHER_SLOTS chunks per thread are in
+// flight at once; a chunk is re-read until it holds no sentinel half.  Columns >= kvalid are written as zeros; rows
+// >= nrows are never written (the ring starts zeroed).
+__device__ __forceinline__ bool rt_word_has_sentinel(uint32_t w) {      // a 16-bit half of w is 0xFFFF
+    const uint32_t x = ~w;
+    return ((x - 0x00010001u) & w & 0x80008000u) != 0u;               // "has a zero halfword" on ~w
+}
+__device__ __forceinline__ bool rt_chunk_has_sentinel(const uint4& v) {
+    return rt_word_has_sentinel(v.x) | rt_word_has_sentinel(v.y) | rt_word_has_sentinel(v.z) | rt_word_has_sentinel(v.w);
+}
+// Everything about one phase's check that does not change from call to call inside a launch.
+struct RtGatherGeom {
+    uint32_t ring0, a_full0, a_valid0;   // shared-memory addresses: ring, first full / valid barrier
+    int nsp, tile, ckb_log2, rp_log2, nst, expt;
+    unsigned* err;
+};
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t saddr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr) : "memory");
+    return v;
+}
+// Direct exchange, consumer side.  The rows a phase streams are still moved by TMA (one instruction per ring stage; the
+// TMA unit reads L2 on its own path, so the copy does not queue behind the epilogue's loads and stores - a version that
+// copied with cp.async from the epilogue threads ran 2x slower next to the other layer's kernel for that reason), but
+// nothing orders those loads after the other slices' stores: no release, no flag, no fence.  Instead every slot was
+// filled with a sentinel (0xFFFF in each 16-bit half: a NaN pattern no float->bf16 conversion produces) before, every
+// word is written exactly once, and the RT_EPI_THREADS epilogue threads read the landed stage back from shared memory:
+// a 16-byte chunk with a sentinel half was loaded too early and is re-read from L2 with coherent loads until complete,
+// then patched in place.  Chunk index inside a stage: [half][row (padded to 2^rp_log2)][K block][chunk of 8 elements];
+// thread i owns chunks i, i + 256, ...  Rows >= nrows belong to other tiles and are not looked at (their products land
+// in accumulator rows nobody reads); columns >= kvalid were zero-filled by TMA.
+// `stph`: the caller's ring position (stage | phase bit << 16), returned advanced.
+__device__ __forceinline__ uint32_t rt_validate(const RtGatherGeom& G, uint32_t stph, const __nv_bfloat16* __restrict__ src, int64_t lo_ofs,
+                                                int64_t row0, int nrows, int ld, int k0, int kvalid, int nkb, int epi_tid, int lane,
+                                                long long* stamps) {
+    const int nsp = G.nsp, tile = G.tile, ckb_log2 = G.ckb_log2, rp_log2 = G.rp_log2, nst = G.nst;
+    uint32_t st = stph & 0xFFFFu, ph = stph >> 16;
+    const int hbit = nsp - 1;
+    const int L = hbit + rp_log2 + ckb_log2 + 3;             // log2(chunks per stage), L >= 8 (host)
+    const int ckb = 1 << ckb_log2;
+    const int qs = 1 << (L - 8);                             // chunks per stage and thread
+    const int nstages = (nkb + ckb - 1) >> ckb_log2;
+    // the thread's part of every chunk it owns: low 8 bits of the chunk index
+    const int c = epi_tid & 7, kbl = (epi_tid >> 3) & (ckb - 1), r_low = epi_tid >> (3 + ckb_log2);
+    const int kcol_t = kbl * 64 + c * 8;
+    const __nv_bfloat16* gsrc = src + (row0 + r_low) * (int64_t)ld + k0 + kcol_t;
+    const uint32_t s_thr = G.ring0 + (uint32_t)(kbl * tile + r_low * 128);
+    const uint32_t stage_bytes = (uint32_t)(ckb * tile * nsp), half_bytes = (uint32_t)(ckb * tile);
+    if (stamps && epi_tid == 0) stamps[19] = clock64();
+    long long nretry = 0;
+#pragma unroll 1
+    for (int sv = 0; sv < nstages; ++sv) {
+        {   // the stage's TMA loads have landed
+            const uint32_t bar = G.a_full0 + st * 8u;
+            uint32_t ok;
+            do {
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(ok) : "r"(bar), "r"(ph) : "memory");
+            } while (!ok);
+        }
+        if (stamps && epi_tid == 0 && sv == 0) stamps[20] = clock64();
+        const int kb0 = sv << ckb_log2;
+        const uint32_t sbase = s_thr + st * stage_bytes;
+        if ((kb0 + kbl) < nkb && (kb0 * 64 + kcol_t) < kvalid && !(G.expt & 8)) {
+#pragma unroll 2
+            for (int i = 0; i < qs; ++i) {
+                const int hi_bits = i << 8;                           // the slot's part of the chunk index
+                const int half = hbit ? (hi_bits >> (L - 1)) : 0;
+                const int rq = (hi_bits >> (ckb_log2 + 3)) & ((1 << rp_log2) - 1);
+                const int r = r_low + rq;
+                if (r >= nrows) continue;
+                const uint32_t sa = sbase + (half ? half_bytes : 0u) + (uint32_t)(rq * 128 + ((c ^ (r & 7)) << 4));
+                uint4 v = ld_shared_v4(sa);
+                if (!rt_chunk_has_sentinel(v)) continue;
+                const __nv_bfloat16* g = gsrc + (int64_t)rq * ld + (half ? lo_ofs : 0) + kb0 * 64;
+                int spins = 0;
+                do {
+                    v = ld_relaxed_gpu_v4(g);
+                    // bounded: a dead wait raises the host-visible error word, and every other wait of the launch then gives up too
+                    if ((++spins & 1023) == 0 && G.err && (spins > RT_GATHER_SPINS || *reinterpret_cast<volatile unsigned*>(G.err))) {
+                        *reinterpret_cast<volatile unsigned*>(G.err) = 1u;
+                        break;
+                    }
+                } while (rt_chunk_has_sentinel(v));
+                st_shared_v4(sa, v);
+                nretry += spins;
+            }
+        }
+        fence_proxy_async();                                  // patches -> visible to the tensor core's reads
+        __syncwarp();
+        if (lane == 0)                                        // one arrival per epilogue warp
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(G.a_valid0 + st * 8u) : "memory");
+        if (++st == (uint32_t)nst) { st = 0; ph ^= 1u; }
+        if (stamps && epi_tid == 0 && sv == 0) stamps[21] = clock64();
+    }
+    if (stamps && epi_tid == 0) { stamps[22] = clock64(); stamps[23] = nretry; }
+    return st | (ph << 16);
+}
+
+// Direct exchange, trigger of the TMA loads (warp 0, all lanes): wait until a word from the END of every slice's share of
+// the rows (last row, last two units; the lo twin when there is one - it is stored after the hi word) is no longer the
+// sentinel.  Only a hint that the rows are about to be complete - it keeps the number of chunks rt_validate has to patch
+// small; nothing depends on it for correctness.
+__device__ __forceinline__ void rt_probe(const __nv_bfloat16* __restrict__ src, int64_t lo_ofs, int64_t row_last, int ld, int col0, int HC,
+                                         int ncols, int nslices, int lane, unsigned* err) {
+    for (int sl = lane; sl < nslices; sl += 32) {
+        const int col = min(col0 + sl * HC + HC, ncols) - 2;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(src + lo_ofs + row_last * (int64_t)ld + col);
+        int spins = 0;
+        uint32_t v;
+        do {
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
+            if ((++spins & 1023) == 0 && err && (spins > RT_GATHER_SPINS || *reinterpret_cast<volatile unsigned*>(err))) {
+                *reinterpret_cast<volatile unsigned*>(err) = 1u;
+                break;
+            }
+        } while (rt_word_has_sentinel(v));
+    }
+    __syncwarp();
+}
+
+// Sentinel over the bf16 slots rows [row0, row0 + nrows) x columns [c0, c0 + ncols) of `dst` (ncols % 8 == 0, 16-byte aligned).
+__device__ __forceinline__ void rt_fill_sentinel(__nv_bfloat16* __restrict__ dst, int64_t lo_ofs, int64_t row0, int nrows, int ld,
+                                                 int c0, int ncols, int epi_tid) {
+    const int per_row = ncols >> 3;
+    const uint4 ff = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+    for (int i = epi_tid; i < nrows * per_row; i += RT_EPI_THREADS) {
+        const int r = i / per_row, c = i - r * per_row;
+        __nv_bfloat16* q = dst + (row0 + r) * (int64_t)ld + c0 + c * 8;
+        *reinterpret_cast<uint4*>(q) = ff;
+        if (lo_ofs) *reinterpret_cast<uint4*>(q + lo_ofs) = ff;
+    }
+}
 
 // One contraction Z[128 x NC] = A_tile[rows x K] * W_region^T, split across the three roles.
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
@@ -215,7 +400,7 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 // Executed by ALL lanes of the (converged) MMA warp with warp-uniform arguments; one elected lane issues.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
                                        int swap, int nrows16, int box_rows, int ckb, int nst, int m64,
-                                       long long* stamps = nullptr, int split = 0, int rot = 0) {
+                                       long long* stamps = nullptr, int split = 0, int rot = 0, int checked = 0) {
     const int tile = rt_tile_bytes(box_rows);
     const bool lane0 = (threadIdx.x & 31) == 0;
     // split: lo tiles sit ckb tiles after their hi tiles in the stage, the lo weight region right after the hi one
@@ -227,7 +412,7 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
     const uint32_t w0 = smem_u32(wbase);
     for (int kb0 = 0; kb0 < nkb; kb0 += ckb, p.advance(nst)) {
         const int st = (int)p.st;
-        mbar_wait(&s.a_full[st], p.ph);
+        mbar_wait(checked ? &s.a_valid[st] : &s.a_full[st], p.ph);     // direct exchange: the epilogue threads have checked the stage
         tc_fence_after();
         if (stamps && lane0) stamps[kb0 == 0 ? 11 : 12] = clock64();
         const int n = min(ckb, nkb - kb0);
@@ -415,20 +600,23 @@ __device__ __forceinline__ void stv(float* __restrict__ p, const float* src) {
     if (VEC == 4) *reinterpret_cast<float4*>(p) = make_float4(src[0], src[1], src[2], src[3]);
     else p[0] = src[0];
 }
-// adjacent bf16 (one 8-byte store for four), plus the lo twins when lo_ofs != 0 (see store_bf16_split)
+// adjacent bf16 (one 8-byte store for four), plus the lo twins when lo_ofs != 0 (see store_bf16_split).  These are the rows
+// other CTAs read while this kernel runs: relaxed gpu-scope stores (strong operations, written through to L2).
 template <int VEC>
 __device__ __forceinline__ void stv_bf16_split(__nv_bfloat16* __restrict__ p, int64_t lo_ofs, const float* v) {
-    if (VEC == 1) { store_bf16_split(p, lo_ofs, v[0]); return; }
+    if (VEC == 1) {
+        const __nv_bfloat16 hi = __float2bfloat16_rn(v[0]);
+        st_relaxed_gpu_b16(p, __bfloat16_as_ushort(hi));
+        if (lo_ofs) st_relaxed_gpu_b16(p + lo_ofs, __bfloat16_as_ushort(__float2bfloat16_rn(v[0] - __bfloat162float(hi))));
+        return;
+    }
     const __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[VEC > 1 ? 1 : 0]), h1 = __floats2bfloat162_rn(v[VEC > 2 ? 2 : 0], v[VEC > 3 ? 3 : 0]);
-    uint2 w;
-    w.x = *reinterpret_cast<const uint32_t*>(&h0); w.y = *reinterpret_cast<const uint32_t*>(&h1);
-    *reinterpret_cast<uint2*>(p) = w;
+    st_relaxed_gpu_v2(p, *reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
     if (lo_ofs) {
         const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
         const __nv_bfloat162 l0 = __floats2bfloat162_rn(v[0] - f0.x, v[VEC > 1 ? 1 : 0] - f0.y),
                              l1 = __floats2bfloat162_rn(v[VEC > 2 ? 2 : 0] - f1.x, v[VEC > 3 ? 3 : 0] - f1.y);
-        w.x = *reinterpret_cast<const uint32_t*>(&l0); w.y = *reinterpret_cast<const uint32_t*>(&l1);
-        *reinterpret_cast<uint2*>(p + lo_ofs) = w;
+        st_relaxed_gpu_v2(p + lo_ofs, *reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1));
     }
 }
 
@@ -528,7 +716,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); mbar_init(&s.a_valid[i], RT_EPI_WARPS); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
@@ -560,19 +748,25 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     if (MODEL == CRNN_MODEL_GRU)
                         tma_load_2d(s.wsb + (size_t)wblk * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
                 }
-            for (int t = a.t_begin; t < a.t_end; ++t) {
-                for (int ph = 0; ph < nphase; ++ph) {
+        }
+        for (int t = a.t_begin; t < a.t_end; ++t) {
+            for (int ph = 0; ph < nphase; ++ph) {
+                if (a.gather && phases_done > 0) {    // (the launch's first phase reads rows an earlier launch or the host wrote)
+                    const bool second = MODEL == CRNN_MODEL_GRU && ph == 1;
+                    rt_probe(second ? a.rsb : a.hxb, second ? a.rsb_lo : a.hxb_lo, (int64_t)t * B + b0 + bt - 1, H, 0, HC, H, a.nslices, lane, a.err);
+                }
+                if (lane == 0) {
                     const int dbg_phase = (int)phases_done;
                     RT_STAMP(0);
-                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+                    if (!a.gather && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     RT_STAMP(1);
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb,
                                    a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr, rot,
-                                   (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
+                                   (!a.gather && dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
                     RT_STAMP(2);
-                    ++phases_done;
                 }
+                ++phases_done;
             }
         }
     } else if (warp == 1) {
@@ -584,7 +778,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
-                               (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot);
+                               (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot, a.gather);
                     if (lane == 0) RT_STAMP(3);
                 }
         }
@@ -594,6 +788,15 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         const int epi_tid = (warp - 2) * 32 + lane;
         uint32_t zpeer[4] = {0, 0, 0, 0};            // the peers' accumulator staging areas (distributed shared memory)
         if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
+        if (a.gather) {
+            // the slots this CTA writes in the NEXT launch of the layer's chain (visible there by the kernel boundary)
+            for (int t = a.fill_t0; t < a.fill_t1; ++t) {
+                rt_fill_sentinel(a.hxb, a.hxb_lo, (int64_t)(t + 1) * B + b0, bt, H, j0, hcv, epi_tid);
+                if (MODEL == CRNN_MODEL_GRU) rt_fill_sentinel(a.rsb, a.rsb_lo, (int64_t)t * B + b0, bt, H, j0, hcv, epi_tid);
+            }
+        }
+        const RtGatherGeom gg{smem_u32(s.ring), smem_u32(s.a_full), smem_u32(s.a_valid), nsp, rt_tile_bytes(a.box_rows), a.g_ckb_log2, a.g_rp_log2, a.nst, a.expt, a.err};
+        uint32_t gpos = 0;                            // ring position of the gather (stage | phase bit << 16)
         for (int t = a.t_begin; t < a.t_end; ++t) {
             const int64_t tB = (int64_t)t * B;
             float* gt = a.gates;
@@ -605,6 +808,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 // registers across the step barrier: only the bf16 rows other CTAs stream next (hxb / rsb) are
                 // stored before the release, everything this CTA alone reads later (fp32 h, c, the gate stash for
                 // BPTT) is stored after it - the release waits for every store issued before it.
+                if (a.gather) {   // this phase's rows: h_{t-1} (slot t of hxb) or r*h of this step, as the other slices finish them
+                    const int gph = (t - a.t_begin) * nphase + ph;
+                    long long* gstamp = (dbgs && gph >= 20 && gph < 28) ? dbgs + (gph - 20) * 24 : nullptr;
+                    const bool second = MODEL == CRNN_MODEL_GRU && ph == 1;
+                    gpos = rt_validate(gg, gpos, second ? a.rsb : a.hxb, second ? a.rsb_lo : a.hxb_lo, tB + b0, bt, H, 0, H, nkb, epi_tid, lane, gstamp);
+                }
                 EpiIdx e[UB / VEC];
                 float x0[UB], x1[UB], x2[UB], x3[UB], ax[UB], hv[UB];
                 bool pending = false;
@@ -722,7 +931,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 }
                 const int dbg_phase = (t - a.t_begin) * nphase + ph;
                 if (epi_tid == 0) RT_STAMP(6);
-                if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+                if (a.gather) { /* the stored rows are their own signal */ }
+                else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
                 if (epi_tid == 0) RT_STAMP(7);
                 if (pending && !(a.expt & 4)) {   // the stores nobody else waits for
                     const int b0row = b0 + (a.npass - 1) * 128;                  // the deferred batch belongs to the last pass
@@ -800,7 +1010,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); }
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); mbar_init(&s.a_valid[i], RT_EPI_WARPS); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
@@ -829,22 +1039,29 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     for (int kb = 0; kb < nkb1; ++kb)
                         tma_load_2d(s.wsb + (size_t)(il ? kb * 2 + half : half * nkb1 + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
             }
-            for (int t = a.t_end - 1; t >= a.t_begin; --t) {
-                // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
-                if (t + 1 < a.S) {
-                    if (phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+        }
+        for (int t = a.t_end - 1; t >= a.t_begin; --t) {
+            // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
+            if (t + 1 < a.S) {
+                if (a.gather && phases_done > 0)
+                    rt_probe(a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0 + bt - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
+                if (lane == 0) {
+                    if (!a.gather && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb0,
                                    a.split ? &tmZ0l : nullptr, rot0);
                 }
-                ++phases_done;
-                if (MODEL == CRNN_MODEL_GRU) {
-                    if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll);
+            }
+            ++phases_done;
+            if (MODEL == CRNN_MODEL_GRU) {
+                if (a.gather) rt_probe(a.dzb + 2 * H, a.dzb_lo, (int64_t)t * B + b0 + bt - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
+                if (lane == 0) {
+                    if (!a.gather) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb1,
                                    a.split ? &tmZ1l : nullptr, rot1);
-                    ++phases_done;
                 }
+                ++phases_done;
             }
         }
     } else if (warp == 1) {
@@ -853,9 +1070,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0, a.gather);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1, a.gather);
             }
         }
     } else {
@@ -864,6 +1081,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         const int epi_tid = (warp - 2) * 32 + lane;
         uint32_t zpeer[4] = {0, 0, 0, 0};
         if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
+        if (a.gather) {
+            // the dz slots this CTA writes in the NEXT (earlier) launch of the layer's chain
+            for (int t = a.fill_t0; t < a.fill_t1; ++t)
+                for (int g = 0; g < GZ; ++g) rt_fill_sentinel(a.dzb, a.dzb_lo, (int64_t)t * B + b0, bt, (int)zw, g * H + j0, hcv, epi_tid);
+        }
+        const RtGatherGeom gg{smem_u32(s.ring), smem_u32(s.a_full), smem_u32(s.a_valid), nsp, rt_tile_bytes(a.box_rows), a.g_ckb_log2, a.g_rp_log2, a.nst, a.expt, a.err};
+        uint32_t gpos = 0;
         // zero the CTA-private carries (they persist in global memory across the launches of one sequence)
         if (MODEL != CRNN_MODEL_RNN && a.t_end == a.S) {
             for (int idx = epi_tid; idx < bt * hcv; idx += RT_EPI_THREADS) {
@@ -877,6 +1101,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             // Same split as the forward epilogue: only the bf16 dz rows other CTAs stream next are stored before the
             // step barrier's release; fp32 dz (read by the weight-gradient GEMMs' bias sums after the kernel) and the
             // carries (read back by the same thread) of the phase's last batch go out after it.
+            if (a.gather && has_next)   // dz_{t+1}, gate columns [0, G1*H), as the other slices finish them
+                gpos = rt_validate(gg, gpos, a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0, bt, (int)zw, 0, G1 * H, nkb0, epi_tid, lane, nullptr);
             EpiIdx e[UB / VEC];
             float v0[UB], v1[UB], v2[UB], v3[UB], v4[UB];
             bool pending = false;
@@ -977,7 +1203,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 epi_bar_sync();
                 if (has_next) RT_RELEASE_PARTIALS();
             }
-            if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+            if (a.gather) { /* the stored rows are their own signal */ }
+            else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
             if (pending) {
                 const int b0row = b0 + (a.npass - 1) * 128;
                 const int64_t ob = (int64_t)b0row * H + j0;
@@ -1000,6 +1227,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             }
             if (MODEL == CRNN_MODEL_GRU) {
                 pending = false;
+                if (a.gather)   // this step's candidate columns [2H, 3H) of dz
+                    gpos = rt_validate(gg, gpos, a.dzb + 2 * H, a.dzb_lo, tB + b0, bt, (int)zw, 0, H, nkb1, epi_tid, lane, nullptr);
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(128, bt - ps * 128);
                     const int nquads = nr * hq;
@@ -1051,7 +1280,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     epi_bar_sync();
                     RT_RELEASE_PARTIALS();
                 }
-                if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+                if (a.gather) { }
+                else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
                 if (pending) {
                     const int b0row = b0 + (a.npass - 1) * 128;
                     const int64_t ob = (int64_t)b0row * H + j0;

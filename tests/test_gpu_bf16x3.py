@@ -128,6 +128,9 @@ SHAPES = [
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 0}),
     ("gru", 80, 2, 6, 24, 13, {"CRNN_TC_3D": 0}),           # H % 64 != 0: 2-D tile loads
     ("gru", 64, 2, 6, 40, 13, {"CRNN_TC_HC": 16}),
+    # direct exchange of the streamed rows (sentinel-filled slots, no step barrier): opt-in
+    ("gru", 96, 2, 12, 70, 96, {"CRNN_TC_GATHER": 1}), ("lstm", 128, 2, 10, 50, 65, {"CRNN_TC_GATHER": 1}),
+    ("rnn", 160, 2, 9, 33, 40, {"CRNN_TC_GATHER": 1}), ("gru", 512, 2, 12, 64, 96, {"CRNN_TC_GATHER": 1}),
     ("gru", 512, 2, 12, 64, 96, {}),                        # config-3 layers, a short sequence
 ]
 

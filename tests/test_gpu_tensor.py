@@ -123,6 +123,9 @@ BF16_SHAPES = [
     ("gru", 64, 2, 8, 20, 17, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 4, "CRNN_WF_HOIST0": 1}),
     ("rnn", 48, 3, 6, 12, 13, {"CRNN_WAVEFRONT": 2, "CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WF_HOIST0": 1}),
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16}), ("rnn", 96, 2, 6, 70, 13, {"CRNN_TC_HC": 16}),
+    # direct exchange of the streamed rows (opt-in)
+    ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_GATHER": 1}), ("gru", 64, 2, 8, 20, 17, {"CRNN_TC_GATHER": 1, "CRNN_WAVEFRONT_CHUNKS": 4}),
+    ("rnn", 96, 2, 6, 70, 13, {"CRNN_TC_GATHER": 1}),
     ("gru", 128, 1, 5, 300, 13, {"CRNN_TC_HC": 16, "CRNN_TC_TILES": 2}),
     # K split over a cluster of 2 / 4 CTAs, partial sums exchanged through distributed shared memory
     ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 2}),
