@@ -50,6 +50,9 @@ struct WsPlan {
     size_t pbf, wsmb, x0b, dlb, gx0;
     std::vector<size_t> wr, hxb, rsb;
     std::vector<size_t> dzv, dzbv, gout, carry0v, carry1v;   // per layer: layers run concurrently (wavefront)
+    std::vector<size_t> csum;        // per layer (+ one for softmax_b): row-block partials of the bias-gradient column sums
+    size_t es_part, es_sq;           // ordered embedding scatter: per-segment tables [nseg][V][H], partial sums of squares
+    int es_nseg, es_tps;             // segments / tokens per segment (0: the table does not fit shared memory -> atomics)
     size_t total;
 };
 
@@ -66,8 +69,14 @@ struct RecPlanTc {
 
 using namespace crnn;
 
+// Launch-time switches, read from the environment ONCE per handle (crnn_create): a step launches ~100 kernels.
+struct LaunchEnv {
+    int m64, dbg, dbg_layer, one_stage, ckb, rotate, min_stages, use3d, ub8, defer, acq_poll, expt, vec4, cbar, hoist0;
+};
+
 struct crnn_handle {
     crnn_config cfg;
+    LaunchEnv env;
     int G;            // gate blocks in the cell kernel(s): lstm 4, gru 3 (2+1), rnn 1
     int GS;           // gate-stash width / H
     int GZ;           // pre-activation-gradient width / H
@@ -416,6 +425,19 @@ static void build_workspace(crnn_handle* h) {
         w.gx0 = take(S * B * H);
         w.dlb = take2(S * B * h->Vp);
     }
+    // bias-gradient column sums, combined in row-block order (one region per layer: layers overlap; the last for softmax_b)
+    for (int l = 0; l <= L; ++l) w.csum.push_back(take(colsum_scratch_floats(S * B, l < L ? h->GZ * H : V)));
+    // ordered embedding scatter: token segments of >= 128 rows, at most 32 MB of per-segment tables
+    w.es_nseg = 0; w.es_tps = 0; w.es_part = w.es_sq = 0;
+    if ((int64_t)es_smem_bytes((int)V) + 1024 <= h->max_smem && H % 4 == 0) {
+        // segments: about two CTAs per SM over all column chunks, at least 128 rows each, at most 32 MB of tables
+        const int64_t N = S * B, tab = V * H * 4, nchunk = ceil_div64(H, ES_COLS);
+        int64_t nseg = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(N / 128, (32LL << 20) / tab), std::max<int64_t>(1, 2 * h->sm_count / nchunk)));
+        w.es_tps = (int)ceil_div64(N, nseg);
+        w.es_nseg = (int)ceil_div64(N, w.es_tps);
+        w.es_part = take((int64_t)w.es_nseg * V * H);
+        w.es_sq = take(2 * (int64_t)w.es_nseg * ceil_div64(H, ES_COLS));
+    }
     w.total = off;
 }
 
@@ -471,6 +493,10 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->drop_on = h->ikp < 1.0f || h->okp < 1.0f;
     h->fb_calls = 0;
     h->err_word = nullptr;
+    h->env = LaunchEnv{env_int("CRNN_TC_M64", 1), env_int("CRNN_TC_DEBUG", 0), env_int("CRNN_TC_DEBUG_LAYER", 0), env_int("CRNN_TC_ONE_STAGE", 1),
+                       env_int("CRNN_TC_CKB", 0), env_int("CRNN_TC_ROTATE", 0), env_int("CRNN_TC_MIN_STAGES", 2), env_int("CRNN_TC_3D", 1),
+                       env_int("CRNN_TC_UB8", 1), env_int("CRNN_TC_DEFER", 1), env_int("CRNN_TC_ACQ_POLL", 1), env_int("CRNN_TC_EXPT", 0),
+                       env_int("CRNN_TC_VEC4", -1), env_int("CRNN_TC_CBAR", 8), env_int("CRNN_WF_HOIST0", 0)};
     h->wf_W = 1; h->wf_C = 1;
     if (rc == CRNN_OK && h->tc) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
@@ -630,6 +656,39 @@ static int grid_for(int64_t n_threads_needed, int sm_count) {
     return (int)std::max<int64_t>(1, std::min<int64_t>(blocks, (int64_t)sm_count * 8));
 }
 
+static inline double* ws_loss_part(void* ws) { return reinterpret_cast<double*>((char*)ws + 8192); }   // one slot per softmax block (<= 8 * SMs)
+
+// Embedding gradient (scatter-add of the slices) + sum of squares of the slices + the two trailing scalars.
+static int scatter_and_finalize(crnn_handle* h, const int32_t* x, int64_t ld, const float* dX, float* grads, void* ws,
+                                int nloss, cudaStream_t st) {
+    const crnn_config& c = h->cfg;
+    const int H = c.rnn_size, V = c.vocab_size, S = c.seq_length, B = c.batch_size;
+    const int64_t SB = (int64_t)S * B;
+    prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
+    if (h->ws.es_nseg > 0) {
+        const int nchunk = ceil_div(H, ES_COLS);
+        const int smem = (int)es_smem_bytes(V);
+        static bool attr_done[64] = {};
+        if (!attr_done[c.device & 63]) {
+            CRNN_CUDA(cudaFuncSetAttribute(embed_scatter_part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem - 1024));
+            attr_done[c.device & 63] = true;
+        }
+        float* part = wsf(ws, h->ws.es_part);
+        double* sqp = reinterpret_cast<double*>((char*)ws + h->ws.es_sq);
+        embed_scatter_part_kernel<<<dim3(nchunk, h->ws.es_nseg), ES_COLS, smem, st>>>(V, H, x, ld, B, S, dX, h->ws.es_tps, part, sqp);
+        CRNN_LAUNCH_CHECK("embed_scatter_part_kernel");
+        embed_scatter_reduce_kernel<<<grid_for((int64_t)V * H, h->sm_count), 256, 0, st>>>(grads + h->emb_off, (int64_t)V * H, h->ws.es_nseg, part, sqp,
+                                                                                           h->ws.es_nseg * nchunk, ws_sq(ws));
+        CRNN_LAUNCH_CHECK("embed_scatter_reduce_kernel");
+    } else {
+        embed_scatter_kernel<<<grid_for(SB * H, h->sm_count), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, dX, ws_sq(ws));
+        CRNN_LAUNCH_CHECK("embed_scatter_kernel");
+    }
+    finalize_scalars_kernel<<<1, 256, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P, ws_loss_part(ws), nloss);
+    CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
+    return CRNN_OK;
+}
+
 // ---- dropout sites ---------------------------------------------------------------------------
 // site l < L: what cell l reads = (embedding mask | output mask of cell l-1) x input mask of cell l;
 // site L: the top cell's output as the projection reads it.
@@ -751,8 +810,8 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.fast_act = h->fast_act;
     a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
     a.swap = backward ? p.swap_bwd : p.swap_fwd;
-    a.m64 = (!a.swap && p.npass == 1 && p.BT <= 64 && env_int("CRNN_TC_M64", 1)) ? 1 : 0;
-    a.dbg = (!backward && env_int("CRNN_TC_DEBUG", 0) && h->dbg_layer == env_int("CRNN_TC_DEBUG_LAYER", 0)) ? h->dbg_ptr : nullptr;
+    a.m64 = (!a.swap && p.npass == 1 && p.BT <= 64 && h->env.m64) ? 1 : 0;
+    a.dbg = (!backward && h->env.dbg && h->dbg_layer == h->env.dbg_layer) ? h->dbg_ptr : nullptr;
     CUtensorMap t0, t1, w0, w1, t0l, t1l, w0l, w1l;
     int rc;
     const int split = h->split;
@@ -769,20 +828,20 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.ring_bytes = backward ? p.ring_bwd : p.ring_fwd;
     {   // the whole H extent (of this CTA's K part) as one stage when the ring holds it
         const int nkb_h = ceil_div(H, 64) / Q, tile = tc::rt_tile_bytes(p.box_rows);
-        if (env_int("CRNN_TC_ONE_STAGE", 1) && p.npass == 1 && nkb_h * tile * (1 + split) + tc::RT_MROWS_BYTES - tile <= a.ring_bytes) a.ckb = nkb_h;
+        if (h->env.one_stage && p.npass == 1 && nkb_h * tile * (1 + split) + tc::RT_MROWS_BYTES - tile <= a.ring_bytes) a.ckb = nkb_h;
     }
-    { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) a.ckb = std::min(ck_env, ceil_div(H, 64)); }
-    a.rotate = env_int("CRNN_TC_ROTATE", 0);
+    { const int ck_env = h->env.ckb; if (ck_env > 0) a.ckb = std::min(ck_env, ceil_div(H, 64)); }
+    a.rotate = h->env.rotate;
     a.ring_bytes = backward ? p.ring_bwd : p.ring_fwd;
     {   // at least two stages must fit in the ring
         const int tile = tc::rt_tile_bytes(p.box_rows);
-        while (a.ckb > 1 && (a.ring_bytes - tc::RT_MROWS_BYTES + tile) / (tile * a.ckb * (1 + split)) < env_int("CRNN_TC_MIN_STAGES", 2)) --a.ckb;
+        while (a.ckb > 1 && (a.ring_bytes - tc::RT_MROWS_BYTES + tile) / (tile * a.ckb * (1 + split)) < h->env.min_stages) --a.ckb;
     }
     a.gather = p.gather; a.g_rp_log2 = p.g_rp_log2; a.g_ckb_log2 = p.g_ckb_log2;
     a.err = h->err_word;
     if (a.gather) a.ckb = 1 << p.g_ckb_log2;
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb, split, a.ring_bytes);
-    a.use3d = (H % 64 == 0 && env_int("CRNN_TC_3D", 1)) ? 1 : 0;
+    a.use3d = (H % 64 == 0 && h->env.use3d) ? 1 : 0;
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
         if (a.use3d) return tc::make_tmap_bf16_kblocks(m, base, rows, cols, ld, p.box_rows, a.ckb);
         return tc::make_tmap_bf16(m, base, rows, cols, ld, p.box_rows);
@@ -817,13 +876,13 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // elements per epilogue thread per batch: one batch per 128-row pass when 8 per thread cover it, so every global
     // load of the pass is in flight before the accumulator arrives
     const int per_pass = std::min(128, p.BT) * p.HC;
-    const bool ub8 = per_pass > tc::RT_EPI_THREADS * 4 && env_int("CRNN_TC_UB8", 1);
-    a.defer = env_int("CRNN_TC_DEFER", 1);
-    a.acq_poll = env_int("CRNN_TC_ACQ_POLL", 1);
-    a.expt = env_int("CRNN_TC_EXPT", 0);
+    const bool ub8 = per_pass > tc::RT_EPI_THREADS * 4 && h->env.ub8;
+    a.defer = h->env.defer;
+    a.acq_poll = h->env.acq_poll;
+    a.expt = h->env.expt;
     // K-split launches read their partial sums from distributed shared memory; there consecutive lanes on consecutive
     // units (scalar epilogue) beat quads (config 4 BPTT 5.4 vs 6.6 ms, split-precision config 3 BPTT 2.9 vs 3.6 ms)
-    const bool vec4 = env_int("CRNN_TC_VEC4", Q > 1 ? 0 : 1) != 0;
+    const bool vec4 = (h->env.vec4 >= 0 ? h->env.vec4 : (Q > 1 ? 0 : 1)) != 0;
     typedef void (*RecFn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs);
     RecFn fn;
 #define CRNN_PICK(KERNEL, F)                                                                                   \
@@ -833,7 +892,15 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     else             fn = backward ? CRNN_PICK(rec_bwd_tc_kernel, false) : CRNN_PICK(rec_fwd_tc_kernel, false);
 #undef CRNN_PICK
     const size_t smem = backward ? p.smem_bwd : p.smem_fwd;
-    CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {   // the attribute is per function and device; set it again only when the size changes
+        static std::unordered_map<uint64_t, int> smem_set;
+        const uint64_t key = (uint64_t)(uintptr_t)fn ^ ((uint64_t)h->cfg.device << 56);
+        auto it = smem_set.find(key);
+        if (it == smem_set.end() || it->second != (int)smem) {
+            CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            smem_set[key] = (int)smem;
+        }
+    }
     int csize = 1;
     a.cbar = 0;
     // Cluster barrier: when ALL slices of a batch tile fit in one cluster, the steps are ordered by remote
@@ -842,7 +909,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // cluster sizes (config 1: 4 slices, -2 %); 16-CTA clusters (CRNN_TC_CBAR=16) gain 4 % per kernel on
     // config 3 but eight of them with ~190 KB of shared memory per CTA are not co-scheduled, which costs
     // the layer wavefront far more than that.
-    const int cbar_max = env_int("CRNN_TC_CBAR", 8);
+    const int cbar_max = h->env.cbar;
     if (!a.gather && p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
         csize = p.nslices;
         a.cbar = 1;
@@ -1018,7 +1085,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
     // layer 0's input-gradient GEMM as one after the BPTT join), so the SMs left beside the recurrence kernels serve only
     // the chunk GEMMs on the layers' critical path.  Measured on config 3: the recurrence spans shrink (2.14 -> 2.09 and
     // 2.65 -> 2.58 ms, split precision) but the two GEMMs are then serial, 5.03 -> 5.19 ms per step: off by default.
-    const bool hoist0 = wf && env_int("CRNN_WF_HOIST0", 0);
+    const bool hoist0 = wf && h->env.hoist0;
     if (hoist0) {
         LayerParams lp = layer_params(h, params, 0);
         const bf16_t* inb0 = x0b;
@@ -1158,13 +1225,14 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
     const LoOfs lo = lo_offsets(h);
     const int64_t top_lo = drop ? lo.act : lo.hxb;
-    softmax_xent_kernel<<<grid_for(SB * 32, sc), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp, lo.dlb);
+    const int nloss = grid_for(SB * 32, sc);
+    softmax_xent_kernel<<<nloss, 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp, lo.dlb, ws_loss_part(ws));
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
     const bf16_t* topb = drop ? wsb(ws, h->ws.topdb) : wsb(ws, h->ws.hxb[L - 1]) + BH;
     prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
     // d softmax_w [H,V] = out^T * dlogits ; d softmax_b = colsum ; d out = dlogits * softmax_w^T
     rc = gemm_tc(h, H, V, (int)SB, topb, H, 1, top_lo, dlb, Vp, 1, lo.dlb, grads + h->tensors[0].offset, V, nullptr, 1, st);
-    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
+    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st, wsf(ws, h->ws.csum[L]));
     if (rc == CRNN_OK) rc = gemm_tc(h, (int)SB, H, V, dlb, Vp, 0, lo.dlb, wsb(ws, h->ws.wsmb), Vp, 0, lo.wsm, wsf(ws, h->ws.gout[L - 1]), H, nullptr, 0, st);
     if (rc == CRNN_OK && drop) rc = drop_apply(h, call, L, wsf(ws, h->ws.gout[L - 1]), wsf(ws, h->ws.gout[L - 1]), nullptr, 0, SB * H, st);
     if (rc != CRNN_OK) return rc;
@@ -1172,7 +1240,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     // BPTT, top layer first.  Wavefront: layer l works on chunk c (late steps first) as soon as layer
     // l+1 has turned that chunk's dz into input gradients; "rec_bwd" then times the whole fork..join
     // span (recurrences + interleaved input-gradient GEMMs), weight gradients included at its tail.
-    const bool hoist0 = wf && env_int("CRNN_WF_HOIST0", 0);     // see run_forward_bf16
+    const bool hoist0 = wf && h->env.hoist0;     // see run_forward_bf16
     if (wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
     rc = wf_fork(h, st, 1 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
@@ -1246,15 +1314,15 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             const bf16_t* rsb = wsb(ws, h->ws.rsb[l]);
             rc = gemm_tc(h, H, 2 * H, (int)SB, inb, H, 1, in_lo, dzb, zw, 1, lo.dzb, gW, 2 * H, nullptr, 1, s);
             if (rc == CRNN_OK) rc = gemm_tc(h, H, 2 * H, (int)SB, hxb, H, 1, lo.hxb, dzb, zw, 1, lo.dzb, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, s);
-            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, s);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, s, wsf(ws, h->ws.csum[l]));
             if (rc == CRNN_OK) rc = gemm_tc(h, H, H, (int)SB, inb, H, 1, in_lo, dzb + 2 * H, zw, 1, lo.dzb, gWc, H, nullptr, 1, s);
             if (rc == CRNN_OK) rc = gemm_tc(h, H, H, (int)SB, rsb, H, 1, lo.act, dzb + 2 * H, zw, 1, lo.dzb, gWc + (int64_t)H * H, H, nullptr, 1, s);
-            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, s);
+            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, s, wsf(ws, h->ws.csum[l]));
         } else {
             const int GH = h->G * H;
             rc = gemm_tc(h, H, GH, (int)SB, inb, H, 1, in_lo, dzb, zw, 1, lo.dzb, gW, GH, nullptr, 1, s);
             if (rc == CRNN_OK) rc = gemm_tc(h, H, GH, (int)SB, hxb, H, 1, lo.hxb, dzb, zw, 1, lo.dzb, gW + (int64_t)H * GH, GH, nullptr, 1, s);
-            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, s);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, s, wsf(ws, h->ws.csum[l]));
         }
         if (rc != CRNN_OK) return rc;
     }
@@ -1274,11 +1342,8 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         if (rc == CRNN_OK && drop) rc = drop_apply(h, call, 0, dn, dn, nullptr, 0, SB * H, st);
         if (rc != CRNN_OK) return rc;
     }
-    prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
-    embed_scatter_kernel<<<grid_for(SB * H, sc), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, wsf(ws, h->ws.gx0), ws_sq(ws));
-    CRNN_LAUNCH_CHECK("embed_scatter_kernel");
-    finalize_scalars_kernel<<<1, 32, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P);
-    CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
+    rc = scatter_and_finalize(h, x, ld, wsf(ws, h->ws.gx0), grads, ws, nloss, st);
+    if (rc != CRNN_OK) return rc;
     prof_mark(h, st, -1);
     return CRNN_OK;
 }
@@ -1321,7 +1386,8 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
 
     // loss + dlogits in place, then the three projection-layer gradients
     float* logits = wsf(ws, h->ws.logits);
-    softmax_xent_kernel<<<grid_for(SB * 32, h->sm_count), 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), nullptr, 0);
+    const int nloss = grid_for(SB * 32, h->sm_count);
+    softmax_xent_kernel<<<nloss, 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), nullptr, 0, 0, ws_loss_part(ws));
     CRNN_LAUNCH_CHECK("softmax_xent_kernel");
     const float* top = drop ? wsf(ws, h->ws.topd) : wsf(ws, h->ws.hx[L - 1]) + BH;
     const float* Wsm = params + h->tensors[0].offset;
@@ -1329,7 +1395,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
     float* dyb = wsf(ws, h->ws.dyb);
     prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
     rc = gemm_f32(1, 0, H, V, (int)SB, top, H, logits, V, grads + h->tensors[0].offset, V, nullptr, 1, st, h->sm_count);
-    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st);
+    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st, wsf(ws, h->ws.csum[L]));
     if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, V, logits, V, Wsm, V, dya, H, nullptr, 0, st, h->sm_count);
     if (rc == CRNN_OK && drop) rc = drop_apply(h, call, L, dya, dya, nullptr, 0, SB * H, st);   // back through the output mask
     if (rc != CRNN_OK) return rc;
@@ -1361,11 +1427,11 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
             // gates kernel [2H,2H]: rows 0..H from inputs, rows H..2H from h_{t-1}
             rc = gemm_f32(1, 0, H, 2 * H, (int)SB, in, H, dz, zw, gW, 2 * H, nullptr, 1, st, sc);
             if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, 2 * H, (int)SB, hx, H, dz, zw, gW + (int64_t)H * 2 * H, 2 * H, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, st);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, 2 * H, gb, st, wsf(ws, h->ws.csum[l]));
             // candidate kernel [2H,H]: rows H..2H see r*h_{t-1}
             if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, H, (int)SB, in, H, dz + 2 * H, zw, gWc, H, nullptr, 1, st, sc);
             if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, H, (int)SB, gates + 3 * H, gw, dz + 2 * H, zw, gWc + (int64_t)H * H, H, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, st);
+            if (rc == CRNN_OK) rc = colsum_f32(dz + 2 * H, zw, (int)SB, H, gbc, st, wsf(ws, h->ws.csum[l]));
             prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
             if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, 2 * H, dz, zw, lp.W, 2 * H, dnext, H, nullptr, 0, st, sc);
             if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, H, dz + 2 * H, zw, lp.Wc, H, dnext, H, nullptr, 1, st, sc);
@@ -1373,7 +1439,7 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
             const int GH = h->G * H;
             rc = gemm_f32(1, 0, H, GH, (int)SB, in, H, dz, zw, gW, GH, nullptr, 1, st, sc);
             if (rc == CRNN_OK) rc = gemm_f32(1, 0, H, GH, (int)SB, hx, H, dz, zw, gW + (int64_t)H * GH, GH, nullptr, 1, st, sc);
-            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, st);
+            if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, st, wsf(ws, h->ws.csum[l]));
             prof_mark(h, st, CRNN_PHASE_INPUT_GRADS);
             if (rc == CRNN_OK) rc = gemm_f32(0, 1, (int)SB, H, GH, dz, zw, lp.W, GH, dnext, H, nullptr, 0, st, sc);
         }
@@ -1382,11 +1448,8 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
         std::swap(dcur, dnext);
     }
     // dcur = dX [S,B,H] = the IndexedSlices values of the embedding gradient
-    prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
-    embed_scatter_kernel<<<grid_for(SB * H, h->sm_count), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, dcur, ws_sq(ws));
-    CRNN_LAUNCH_CHECK("embed_scatter_kernel");
-    finalize_scalars_kernel<<<1, 32, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P);
-    CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
+    rc = scatter_and_finalize(h, x, ld, dcur, grads, ws, nloss, st);
+    if (rc != CRNN_OK) return rc;
     prof_mark(h, st, -1);
     return CRNN_OK;
 }

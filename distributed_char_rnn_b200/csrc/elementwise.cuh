@@ -49,6 +49,8 @@ __global__ void __launch_bounds__(256) embed_gather_kernel(const float* __restri
 }
 
 // dtable[x[b,t],:] += dout[t,b,:]  (IndexedSlices -> dense) and sqnorm += sum dout^2.
+// Atomic form: used by the single-operator entry point (no workspace) and for vocabularies whose rows do not fit the
+// shared-memory table of the ordered form below.  The summation order of the atomics is not fixed.
 __global__ void __launch_bounds__(256) embed_scatter_kernel(float* __restrict__ dtable, int V, int H,
                                                             const int32_t* __restrict__ x, int64_t ldx,
                                                             int B, int S, const float* __restrict__ dout,
@@ -68,6 +70,110 @@ __global__ void __launch_bounds__(256) embed_scatter_kernel(float* __restrict__ 
     }
     double tot = block_sum_d(ss, sh);
     if (threadIdx.x == 0 && sqnorm) atomicAdd(sqnorm, tot);
+}
+
+// Ordered form (the training step): no atomics, the same bits on every run and on every replica.
+// Pass 1, CTA (column chunk, token segment): a [V][128] table in shared memory; the segment's rows (time-major order
+// t*B + b) are added one after the other, thread c owning column c of the chunk - a fixed order, no conflicts, the
+// hot rows never leave the SM.  The rows stream through a cp.async ring (ES_STAGES x 32 rows x 128 columns), so the
+// serial part of the loop is the shared-memory read-add-write of one table entry (~35 cycles per row) and not a DRAM
+// round trip.  The table goes to part[seg][V][H]; the chunk's share of sum dout^2 to sqpart.
+// Pass 2: dtable[v][c] = sum over segments in order; block 0 also sums sqpart in order into *sqnorm.
+constexpr int ES_COLS = 128;
+constexpr int ES_ROWS = 32;          // rows per ring stage
+constexpr int ES_STAGES = 4;
+inline size_t es_smem_bytes(int V) { return (size_t)V * ES_COLS * 4 + (size_t)ES_STAGES * ES_ROWS * ES_COLS * 4; }
+__global__ void __launch_bounds__(ES_COLS) embed_scatter_part_kernel(int V, int H, const int32_t* __restrict__ x, int64_t ldx, int B, int S,
+                                                                     const float* __restrict__ dout, int tokens_per_seg,
+                                                                     float* __restrict__ part, double* __restrict__ sqpart) {
+    extern __shared__ __align__(16) float es_smem[];
+    float* es_tab = es_smem;                          // [V][ES_COLS]
+    float* ring = es_smem + V * ES_COLS;              // [ES_STAGES][ES_ROWS][ES_COLS]
+    __shared__ double sh[32];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int c0 = blockIdx.x * ES_COLS;
+    const int c = c0 + tid;
+    const bool live = c < H;
+    const int64_t N = (int64_t)S * B;
+    const int64_t r0 = (int64_t)blockIdx.y * tokens_per_seg, r1 = min(N, r0 + tokens_per_seg);
+    const int nrows = (int)(r1 - r0), nstage = (nrows + ES_ROWS - 1) / ES_ROWS;
+    for (int i = tid; i < V * ES_COLS; i += ES_COLS) es_tab[i] = 0.f;
+    // copy role: thread -> (row in stage = tid / 32 + 4k, 16-byte piece = tid % 32); H % 4 == 0 (host)
+    auto issue = [&](int sidx) {
+        if (sidx < nstage) {
+            float* dst = ring + (sidx % ES_STAGES) * (ES_ROWS * ES_COLS);
+#pragma unroll
+            for (int k = 0; k < ES_ROWS / 4; ++k) {
+                const int rr = (tid >> 5) + 4 * k;
+                const int64_t row = r0 + (int64_t)sidx * ES_ROWS + rr;
+                const int col = c0 + 4 * lane;
+                if (row < r1 && col < H) {
+                    const unsigned sa = (unsigned)__cvta_generic_to_shared(dst + rr * ES_COLS + 4 * lane);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(dout + row * H + col) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int i = 0; i < ES_STAGES - 1; ++i) issue(i);
+    double ss = 0.0;
+    auto load_id = [&](int sidx) -> int {             // a stage's ids: lane l holds row l's
+        const int64_t myrow = r0 + (int64_t)sidx * ES_ROWS + lane;
+        if (myrow >= r1) return 0;
+        const int t = (int)(myrow / B), b = (int)(myrow % B);
+        return min(max(__ldg(x + (int64_t)b * ldx + t), 0), V - 1);
+    };
+    int nextid = load_id(0);
+    for (int sidx = 0; sidx < nstage; ++sidx) {
+        issue(sidx + ES_STAGES - 1);                  // (overwrites the stage consumed in the previous iteration)
+        const int myid = nextid;
+        nextid = load_id(sidx + 1);                   // in flight while this stage is consumed
+        asm volatile("cp.async.wait_group %0;" ::"n"(ES_STAGES - 1) : "memory");
+        __syncthreads();                              // every thread's pieces of the stage have landed
+        const float* src = ring + (sidx % ES_STAGES) * (ES_ROWS * ES_COLS) + tid;
+        const int nr = min(ES_ROWS, nrows - sidx * ES_ROWS);
+#pragma unroll 4
+        for (int rr = 0; rr < nr; ++rr) {             // (all lanes take part in the shuffle, also those past column H)
+            const int id = __shfl_sync(0xffffffffu, myid, rr);
+            if (live) {
+                const float g = src[rr * ES_COLS];
+                es_tab[id * ES_COLS + tid] += g;
+                ss += (double)g * (double)g;
+            }
+        }
+        __syncthreads();                              // the stage may be overwritten
+    }
+    if (live) {
+        float* dst = part + ((int64_t)blockIdx.y * V) * H + c;
+        for (int v = 0; v < V; ++v) dst[(int64_t)v * H] = es_tab[v * ES_COLS + tid];
+    }
+    const double tot = block_sum_d(ss, sh);
+    if (tid == 0) sqpart[blockIdx.y * gridDim.x + blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(256) embed_scatter_reduce_kernel(float* __restrict__ dtable, int64_t VH, int nseg,
+                                                                   const float* __restrict__ part, const double* __restrict__ sqpart,
+                                                                   int nsq, double* __restrict__ sqnorm) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < VH; i += (int64_t)gridDim.x * blockDim.x) {
+        float acc = 0.f;
+        int sg = 0;
+        for (; sg + 8 <= nseg; sg += 8) {             // eight loads in flight, added in segment order
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = __ldg(part + (int64_t)(sg + k) * VH + i);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc += v[k];
+        }
+        for (; sg < nseg; ++sg) acc += __ldg(part + (int64_t)sg * VH + i);
+        dtable[i] = acc;
+    }
+    if (blockIdx.x == 0 && sqnorm) {                  // fixed order: strided per thread, then the block's fixed tree
+        __shared__ double sh[32];
+        double t = 0.0;
+        for (int i = threadIdx.x; i < nsq; i += blockDim.x) t += sqpart[i];
+        t = block_sum_d(t, sh);
+        if (threadIdx.x == 0) *sqnorm = t;
+    }
 }
 
 // ---- dropout (model.py:31-34,58-59; train.py:58-61) ----------------------------------------
@@ -108,7 +214,7 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ l
                                                            const int32_t* __restrict__ y, int64_t ldy,
                                                            double* __restrict__ loss_sum,
                                                            __nv_bfloat16* __restrict__ dl_bf16, int64_t ld_bf16,
-                                                           int64_t lo_ofs = 0) {
+                                                           int64_t lo_ofs = 0, double* __restrict__ loss_part = nullptr) {
     __shared__ double sh[32];
     const int lane = threadIdx.x & 31;
     const int64_t N = (int64_t)B * S;
@@ -139,7 +245,9 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(float* __restrict__ l
         if (lane == 0) local += (double)(lse - zl);
     }
     double tot = block_sum_d(local, sh);
-    if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, tot);
+    // the training step hands in one slot per block and sums them in block order (finalize_scalars_kernel): same bits every run
+    if (threadIdx.x == 0 && loss_part) loss_part[blockIdx.x] = tot;
+    else if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, tot);
 }
 
 // probs[b*S+t,:] = softmax(logits_tb[t*B+b,:]); also writes the re-ordered logits.
@@ -168,10 +276,15 @@ __global__ void __launch_bounds__(256) logits_out_kernel(const float* __restrict
 
 // grads[P] = sum |dX|^2 ; grads[P+1] = cost = loss_sum / (B*S)
 __global__ void finalize_scalars_kernel(const double* __restrict__ sq, const double* __restrict__ loss_sum,
-                                        double n, float* __restrict__ tail) {
+                                        double n, float* __restrict__ tail, const double* __restrict__ loss_part = nullptr,
+                                        int nloss = 0) {
+    __shared__ double sh[32];
+    double l = 0.0;                                   // fixed order: strided per thread, then the block's fixed tree
+    for (int i = threadIdx.x; i < nloss; i += blockDim.x) l += loss_part[i];
+    l = block_sum_d(l, sh);
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         tail[0] = (float)(*sq);
-        tail[1] = (float)(*loss_sum / n);
+        tail[1] = (float)((l + *loss_sum) / n);
     }
 }
 

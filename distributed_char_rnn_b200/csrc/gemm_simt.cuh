@@ -133,9 +133,11 @@ inline int gemm_f32(int ta, int tb, int M, int N, int K, const float* A, int64_t
     return CRNN_OK;
 }
 
-// Column sums: out[c] (+)= sum_r X[r*ld + c]   (bias gradients: db = sum over (t,b) of dz).
+// Column sums: out[c] += sum_r X[r*ld + c]   (bias gradients: db = sum over (t,b) of dz).
+// `part` == nullptr: row blocks are combined with atomics (order not fixed).  With a scratch array of
+// gridDim.y * C floats the row blocks' sums are stored and added in block order by colsum_finish_kernel.
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int64_t ld, int R, int C,
-                                                     float* __restrict__ out, int rows_per_block) {
+                                                     float* __restrict__ out, int rows_per_block, float* __restrict__ part) {
     __shared__ float sh[8][33];
     int c = blockIdx.x * 32 + (threadIdx.x & 31);
     int ry = threadIdx.x >> 5;
@@ -150,16 +152,29 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X
         float t = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x & 31];
-        atomicAdd(out + c, t);
+        if (part) part[(int64_t)blockIdx.y * C + c] = t;
+        else atomicAdd(out + c, t);
     }
 }
+__global__ void __launch_bounds__(256) colsum_finish_kernel(const float* __restrict__ part, int nblk, int C, float* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float t = 0.f;
+    for (int i = 0; i < nblk; ++i) t += part[(int64_t)i * C + c];
+    out[c] += t;
+}
 
-inline int colsum_f32(const float* X, int64_t ld, int R, int C, float* out, cudaStream_t st) {
+inline int64_t colsum_scratch_floats(int64_t R, int64_t C) { return ceil_div64(R, 1024) * C; }
+inline int colsum_f32(const float* X, int64_t ld, int R, int C, float* out, cudaStream_t st, float* part = nullptr) {
     if (R <= 0 || C <= 0) return CRNN_OK;
     int rows_per_block = 1024;
     dim3 grid(ceil_div(C, 32), ceil_div(R, rows_per_block));
-    colsum_kernel<<<grid, 256, 0, st>>>(X, ld, R, C, out, rows_per_block);
+    colsum_kernel<<<grid, 256, 0, st>>>(X, ld, R, C, out, rows_per_block, grid.y > 1 ? part : nullptr);
     CRNN_LAUNCH_CHECK("colsum_kernel");
+    if (part && grid.y > 1) {
+        colsum_finish_kernel<<<ceil_div(C, 256), 256, 0, st>>>(part, (int)grid.y, C, out);
+        CRNN_LAUNCH_CHECK("colsum_finish_kernel");
+    }
     return CRNN_OK;
 }
 

@@ -6,6 +6,8 @@
 // a_format [7,10), b_format [10,13), a_major 15, b_major 16, N>>3 [17,23), M>>4 [24,29)).
 #pragma once
 #include <cuda.h>
+#include <mutex>
+#include <unordered_map>
 #include "common.cuh"
 
 namespace crnn {
@@ -214,60 +216,81 @@ inline EncodeTiledFn encode_fn() {
     return fn;
 }
 
+// Encoded tensor maps are cached: a training step re-uses the same few dozen (buffer, shape, box) combinations every
+// step (the workspace pointers do not change), and cuTensorMapEncodeTiled costs about a microsecond a piece - with
+// ~800 of them per step the host, not the GPU, bounded the small configurations.
+struct TmapKey {
+    int kind; const void* base; int64_t rows, cols, ld; int box_rows, box_kb;
+    bool operator==(const TmapKey& o) const {
+        return kind == o.kind && base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows && box_kb == o.box_kb;
+    }
+};
+struct TmapKeyHash {
+    size_t operator()(const TmapKey& k) const {
+        uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
+        h ^= (uint64_t)k.rows * 0xC2B2AE3D27D4EB4Full + (uint64_t)k.cols * 0x165667B19E3779F9ull + (uint64_t)k.ld * 0xD6E8FEB86659FD93ull;
+        h ^= ((uint64_t)k.kind << 56) ^ ((uint64_t)k.box_rows << 32) ^ (uint64_t)k.box_kb;
+        return (size_t)(h ^ (h >> 29));
+    }
+};
+inline int tmap_cached(CUtensorMap* out, const TmapKey& key, int (*encode)(CUtensorMap*, const TmapKey&)) {
+    static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+    static std::mutex mu;
+    {
+        std::lock_guard<std::mutex> g(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) { *out = it->second; return CRNN_OK; }
+    }
+    const int rc = encode(out, key);
+    if (rc != CRNN_OK) return rc;
+    std::lock_guard<std::mutex> g(mu);
+    if (cache.size() > 8192) cache.clear();
+    cache.emplace(key, *out);
+    return CRNN_OK;
+}
+
+inline int encode_tmap(CUtensorMap* out, const TmapKey& k) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    const int esz = k.kind == 1 ? 4 : 2;
+    if ((k.ld * esz) % 16 != 0 || ((uintptr_t)k.base & 15) != 0)
+        return set_err(CRNN_ERR_ARG, "tensor map needs a 16-byte aligned base and row pitch (ld %lld)", (long long)k.ld);
+    CUresult r;
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    if (k.kind == 2) {         // bf16 [kblock][row][64]
+        if (k.cols % 64 != 0) return set_err(CRNN_ERR_ARG, "k-block tensor map needs cols %% 64 == 0");
+        cuuint64_t gdim[3] = {64u, (cuuint64_t)k.rows, (cuuint64_t)(k.cols / 64)};
+        cuuint64_t gstr[2] = {(cuuint64_t)k.ld * 2, 128u};
+        cuuint32_t box[3] = {64u, (cuuint32_t)k.box_rows, (cuuint32_t)k.box_kb};
+        r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(k.base), gdim, gstr, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        cuuint64_t gdim[2] = {(cuuint64_t)k.cols, (cuuint64_t)k.rows};
+        cuuint64_t gstr[1] = {(cuuint64_t)k.ld * esz};
+        cuuint32_t box[2] = {k.kind == 1 ? 32u : 64u, (cuuint32_t)k.box_rows};
+        r = fn(out, k.kind == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(k.base), gdim, gstr, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    if (r != CUDA_SUCCESS) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d, kind %d)", (int)r, k.kind);
+    return CRNN_OK;
+}
+
 // Row-major bf16 matrix [rows, cols] with leading dimension ld (elements); box = [box_rows, 64 cols]
 // (64 bf16 = 128 B = one SWIZZLE_128B row).  Out-of-bounds elements read as zero.
 inline int make_tmap_bf16(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-    if ((ld * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0)
-        return set_err(CRNN_ERR_ARG, "bf16 operand needs a 16-byte aligned base and row pitch (ld %lld)", (long long)ld);
-    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
-    return CRNN_OK;
+    return tmap_cached(out, TmapKey{0, base, rows, cols, ld, box_rows, 0}, encode_tmap);
 }
-
 // Row-major fp32 matrix [rows, cols] (leading dimension ld): box = [box_rows, 32 cols] = 128-byte rows.
 inline int make_tmap_f32(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-    if ((ld * 4) % 16 != 0 || ((uintptr_t)base & 15) != 0)
-        return set_err(CRNN_ERR_ARG, "fp32 tensor map needs a 16-byte aligned base and row pitch");
-    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t gstr[1] = {(cuuint64_t)ld * 4};
-    cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled (fp32) failed (%d)", (int)r);
-    return CRNN_OK;
+    return tmap_cached(out, TmapKey{1, base, rows, cols, ld, box_rows, 0}, encode_tmap);
 }
-
 // The same row-major bf16 matrix seen as [kblock][row][64]: dims (64 k, rows, cols/64 k-blocks) with
 // strides (row pitch, 128 B).  One box {64, box_rows, box_kb} lands in shared memory as box_kb
 // consecutive K-major swizzled tiles of box_rows x 128 B - several K tiles per TMA instruction.
 // Requires cols % 64 == 0 (a partial last k-block would alias the next row instead of reading zero).
 inline int make_tmap_bf16_kblocks(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t ld,
                                   int box_rows, int box_kb) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-    if (cols % 64 != 0 || (ld * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0)
-        return set_err(CRNN_ERR_ARG, "k-block tensor map needs cols %% 64 == 0 and 16-byte aligned rows");
-    cuuint64_t gdim[3] = {64u, (cuuint64_t)rows, (cuuint64_t)(cols / 64)};
-    cuuint64_t gstr[2] = {(cuuint64_t)ld * 2, 128u};
-    cuuint32_t box[3] = {64u, (cuuint32_t)box_rows, (cuuint32_t)box_kb};
-    cuuint32_t estr[3] = {1u, 1u, 1u};
-    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return set_err(CRNN_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed (%d)", (int)r);
-    return CRNN_OK;
+    return tmap_cached(out, TmapKey{2, base, rows, cols, ld, box_rows, box_kb}, encode_tmap);
 }
 
 }  // namespace tc
