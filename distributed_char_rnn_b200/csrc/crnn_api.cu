@@ -7,6 +7,7 @@
 #include "elementwise.cuh"
 #include "gemm_tc.cuh"
 #include "recurrence_tc.cuh"
+#include "proj_xent_tc.cuh"
 
 #include <stdarg.h>
 #include <stdlib.h>
@@ -71,7 +72,7 @@ using namespace crnn;
 
 // Launch-time switches, read from the environment ONCE per handle (crnn_create): a step launches ~100 kernels.
 struct LaunchEnv {
-    int m64, dbg, dbg_layer, one_stage, ckb, rotate, min_stages, use3d, ub8, defer, acq_poll, expt, vec4, cbar, hoist0;
+    int m64, dbg, dbg_layer, one_stage, ckb, rotate, min_stages, use3d, ub8, defer, acq_poll, expt, vec4, cbar, hoist0, fuse_proj;
 };
 
 struct crnn_handle {
@@ -426,7 +427,8 @@ static void build_workspace(crnn_handle* h) {
         w.dlb = take2(S * B * h->Vp);
     }
     // bias-gradient column sums, combined in row-block order (one region per layer: layers overlap; the last for softmax_b)
-    for (int l = 0; l <= L; ++l) w.csum.push_back(take(colsum_scratch_floats(S * B, l < L ? h->GZ * H : V)));
+    // (the last region also holds the fused projection kernel's per-CTA column sums: one row per 128 rows)
+    for (int l = 0; l <= L; ++l) w.csum.push_back(take(l < L ? colsum_scratch_floats(S * B, h->GZ * H) : ceil_div64(S * B, 128) * V));
     // ordered embedding scatter: token segments of >= 128 rows, at most 32 MB of per-segment tables
     w.es_nseg = 0; w.es_tps = 0; w.es_part = w.es_sq = 0;
     if ((int64_t)es_smem_bytes((int)V) + 1024 <= h->max_smem && H % 4 == 0) {
@@ -496,7 +498,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->env = LaunchEnv{env_int("CRNN_TC_M64", 1), env_int("CRNN_TC_DEBUG", 0), env_int("CRNN_TC_DEBUG_LAYER", 0), env_int("CRNN_TC_ONE_STAGE", 1),
                        env_int("CRNN_TC_CKB", 0), env_int("CRNN_TC_ROTATE", 0), env_int("CRNN_TC_MIN_STAGES", 2), env_int("CRNN_TC_3D", 1),
                        env_int("CRNN_TC_UB8", 1), env_int("CRNN_TC_DEFER", 1), env_int("CRNN_TC_ACQ_POLL", 1), env_int("CRNN_TC_EXPT", 0),
-                       env_int("CRNN_TC_VEC4", -1), env_int("CRNN_TC_CBAR", 8), env_int("CRNN_WF_HOIST0", 0)};
+                       env_int("CRNN_TC_VEC4", -1), env_int("CRNN_TC_CBAR", 8), env_int("CRNN_WF_HOIST0", 0), env_int("CRNN_FUSE_PROJ", 1)};
     h->wf_W = 1; h->wf_C = 1;
     if (rc == CRNN_OK && h->tc) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
@@ -1055,8 +1057,11 @@ static int gemm_tc(const crnn_handle* h, int M, int N, int K, const bf16_t* A, i
                             h->split ? A + a_lo : nullptr, h->split ? B + b_lo : nullptr);
 }
 
+// y != nullptr (training): the projection is fused with softmax + cross-entropy and *fused_blocks receives the number of
+// loss / column-sum partials it wrote (0: vocabulary too large for the fused kernel, fp32 logits are in the workspace).
 static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const float* state_in, float* state_out,
-                            const float* params, void* ws, cudaStream_t st, long long drop_call = -1) {
+                            const float* params, void* ws, cudaStream_t st, long long drop_call = -1,
+                            const int32_t* y = nullptr, int* fused_blocks = nullptr) {
     const crnn_config& c = h->cfg;
     const bool drop = h->drop_on && drop_call >= 0;
     const int H = c.rnn_size, V = c.vocab_size, L = c.num_layers, S = c.seq_length, B = c.batch_size;
@@ -1198,8 +1203,21 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
         topb = wsb(ws, h->ws.topdb);
     }
     prof_mark(h, st, CRNN_PHASE_LOGITS_GEMM);
-    rc = gemm_tc(h, (int)SB, V, H, topb, H, 0, drop ? lo.act : lo.hxb, wsb(ws, h->ws.wsmb), h->Vp, 1, lo.wsm, wsf(ws, h->ws.logits), V,
-                 params + h->tensors[1].offset, 0, st);
+    const int64_t top_lo = drop ? lo.act : lo.hxb;
+    if (fused_blocks) *fused_blocks = 0;
+    rc = CRNN_ERR_UNSUP;
+    if (h->env.fuse_proj && ceil_div64(SB, 128) <= 2048) {
+        // fused projection + softmax + cross-entropy (training) / projection with fp32 logits out (forward only)
+        int nblk = 0;
+        rc = tc::proj_xent_tc((int)SB, V, h->Vp, H, B, S, topb, h->split ? topb + top_lo : nullptr, wsb(ws, h->ws.wsmb),
+                              h->split ? wsb(ws, h->ws.wsmb) + lo.wsm : nullptr, params + h->tensors[1].offset, y, ldx,
+                              y ? wsb(ws, h->ws.dlb) : nullptr, y ? lo.dlb : 0, y ? ws_loss_part(ws) : nullptr, y ? wsf(ws, h->ws.csum[L]) : nullptr,
+                              y ? nullptr : wsf(ws, h->ws.logits), st, &nblk);
+        if (rc == CRNN_OK && fused_blocks) *fused_blocks = nblk;
+    }
+    if (rc == CRNN_ERR_UNSUP)
+        rc = gemm_tc(h, (int)SB, V, H, topb, H, 0, top_lo, wsb(ws, h->ws.wsmb), h->Vp, 1, lo.wsm, wsf(ws, h->ws.logits), V,
+                     params + h->tensors[1].offset, 0, st);
     prof_mark(h, st, CRNN_PHASE_MISC);
     return rc;
 }
@@ -1217,7 +1235,8 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
-    int rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st, call);
+    int fused = 0;
+    int rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st, call, y, &fused);
     if (rc != CRNN_OK) return rc;
     const bf16_t* pbf = wsb(ws, h->ws.pbf);
     float* logits = wsf(ws, h->ws.logits);
@@ -1225,14 +1244,20 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     prof_mark(h, st, CRNN_PHASE_SOFTMAX_XENT);
     const LoOfs lo = lo_offsets(h);
     const int64_t top_lo = drop ? lo.act : lo.hxb;
-    const int nloss = grid_for(SB * 32, sc);
-    softmax_xent_kernel<<<nloss, 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp, lo.dlb, ws_loss_part(ws));
-    CRNN_LAUNCH_CHECK("softmax_xent_kernel");
+    int nloss = fused;
+    if (!fused) {
+        nloss = grid_for(SB * 32, sc);
+        softmax_xent_kernel<<<nloss, 256, 0, st>>>(logits, B, S, V, y, ld, ws_loss(ws), dlb, Vp, lo.dlb, ws_loss_part(ws));
+        CRNN_LAUNCH_CHECK("softmax_xent_kernel");
+    }
     const bf16_t* topb = drop ? wsb(ws, h->ws.topdb) : wsb(ws, h->ws.hxb[L - 1]) + BH;
     prof_mark(h, st, CRNN_PHASE_PROJ_GRADS);
     // d softmax_w [H,V] = out^T * dlogits ; d softmax_b = colsum ; d out = dlogits * softmax_w^T
     rc = gemm_tc(h, H, V, (int)SB, topb, H, 1, top_lo, dlb, Vp, 1, lo.dlb, grads + h->tensors[0].offset, V, nullptr, 1, st);
-    if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st, wsf(ws, h->ws.csum[L]));
+    if (rc == CRNN_OK && fused) {                    // the fused kernel left one row of column sums per CTA: add them in CTA order
+        colsum_finish_kernel<<<ceil_div(V, 256), 256, 0, st>>>(wsf(ws, h->ws.csum[L]), fused, V, grads + h->tensors[1].offset);
+        CRNN_LAUNCH_CHECK("colsum_finish_kernel");
+    } else if (rc == CRNN_OK) rc = colsum_f32(logits, V, (int)SB, V, grads + h->tensors[1].offset, st, wsf(ws, h->ws.csum[L]));
     if (rc == CRNN_OK) rc = gemm_tc(h, (int)SB, H, V, dlb, Vp, 0, lo.dlb, wsb(ws, h->ws.wsmb), Vp, 0, lo.wsm, wsf(ws, h->ws.gout[L - 1]), H, nullptr, 0, st);
     if (rc == CRNN_OK && drop) rc = drop_apply(h, call, L, wsf(ws, h->ws.gout[L - 1]), wsf(ws, h->ws.gout[L - 1]), nullptr, 0, SB * H, st);
     if (rc != CRNN_OK) return rc;
