@@ -38,6 +38,7 @@ SIGNATURES = {
     "crnn_state_size": (c_i64, [c_vp]),
     "crnn_workspace_bytes": (c_i64, [c_vp]),
     "crnn_forward_backward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "crnn_set_bucket_event": (c_i32, [c_vp, c_i32, c_vp]),
     "crnn_clip_adam": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_i64, c_f32, c_vp, c_vp, c_vp]),
     "crnn_clip_adam_noalloc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_i64, c_f32, c_vp, c_vp]),
     "crnn_train_step": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_i64,

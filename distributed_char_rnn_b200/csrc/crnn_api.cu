@@ -99,6 +99,8 @@ struct crnn_handle {
     long long fb_calls;
     long long* dbg_ptr;   // scratch tail for CRNN_TC_DEBUG stamps (set per call)
     unsigned* err_word;   // host-mapped word a kernel sets when one of its bounded waits expires
+    cudaEvent_t bucket_event;   // caller's event, recorded when cells >= bucket_layer have their final gradients (nullptr: off)
+    int bucket_layer;
     int dbg_layer;        // the layer whose forward launches record stamps
     int Vp;           // vocab size padded to 8 (bf16 row pitch of the projection operands)
     int fast_act;
@@ -495,6 +497,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     h->drop_on = h->ikp < 1.0f || h->okp < 1.0f;
     h->fb_calls = 0;
     h->err_word = nullptr;
+    h->bucket_event = nullptr; h->bucket_layer = 0;
     h->env = LaunchEnv{env_int("CRNN_TC_M64", 1), env_int("CRNN_TC_DEBUG", 0), env_int("CRNN_TC_DEBUG_LAYER", 0), env_int("CRNN_TC_ONE_STAGE", 1),
                        env_int("CRNN_TC_CKB", 0), env_int("CRNN_TC_ROTATE", 0), env_int("CRNN_TC_MIN_STAGES", 2), env_int("CRNN_TC_3D", 1),
                        env_int("CRNN_TC_UB8", 1), env_int("CRNN_TC_DEFER", 1), env_int("CRNN_TC_ACQ_POLL", 1), env_int("CRNN_TC_EXPT", 0),
@@ -1350,6 +1353,20 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             if (rc == CRNN_OK) rc = colsum_f32(dz, zw, (int)SB, GH, gb, s, wsf(ws, h->ws.csum[l]));
         }
         if (rc != CRNN_OK) return rc;
+        if (h->bucket_event && l >= h->bucket_layer) {
+            // crnn_set_bucket_event: cells bucket_layer .. L-1 are final once each of their streams has got this far
+            const int slot = 4 * L * C + 64;
+            if (l > h->bucket_layer) {
+                rc = wf_record(h, slot + l, s);
+                if (rc != CRNN_OK) return rc;
+            } else {
+                for (int lu = l + 1; lu < L; ++lu) {
+                    rc = wf_wait(h, slot + lu, s);
+                    if (rc != CRNN_OK) return rc;
+                }
+                CRNN_CUDA(cudaEventRecord(h->bucket_event, s));
+            }
+        }
     }
     rc = wf_join(h, st, 2 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
@@ -1470,12 +1487,21 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
         }
         if (rc == CRNN_OK && drop) rc = drop_apply(h, call, l, dnext, dnext, nullptr, 0, SB * H, st);   // back through this cell's input masks
         if (rc != CRNN_OK) return rc;
+        if (h->bucket_event && l == h->bucket_layer) CRNN_CUDA(cudaEventRecord(h->bucket_event, st));   // cells l .. L-1 are final
         std::swap(dcur, dnext);
     }
     // dcur = dX [S,B,H] = the IndexedSlices values of the embedding gradient
     rc = scatter_and_finalize(h, x, ld, dcur, grads, ws, nloss, st);
     if (rc != CRNN_OK) return rc;
     prof_mark(h, st, -1);
+    return CRNN_OK;
+}
+
+int crnn_set_bucket_event(crnn_handle* h, int32_t first_layer, void* event) {
+    if (!h) return set_err(CRNN_ERR_ARG, "null handle");
+    if (event && (first_layer < 0 || first_layer >= h->cfg.num_layers)) return set_err(CRNN_ERR_ARG, "first_layer must be in [0, num_layers)");
+    h->bucket_event = (cudaEvent_t)event;
+    h->bucket_layer = first_layer;
     return CRNN_OK;
 }
 

@@ -15,11 +15,12 @@ single ``all_reduce`` before the fused clip+Adam kernel runs identically on ever
 """
 import ctypes
 import math
+import os
 
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, parallel
 from ._lib import CrnnConfig, GRAD_TAIL, MODEL_IDS, PREC_IDS, check, ptr
 
 
@@ -57,7 +58,11 @@ class Model(object):
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
 
-        self.dropout_seed = int(np.random.SeedSequence(seed).generate_state(1)[0] & 0x7FFFFFFF) if (ikp < 1 or okp < 1) else 0
+        # every replica draws its own masks for its own shard (the reference's workers do: independent TF RNGs); the
+        # variable initialiser below stays on `seed` alone, so all replicas start from the same weights
+        rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
+        entropy = None if seed is None else [int(seed), int(rank)]
+        self.dropout_seed = int(np.random.SeedSequence(entropy).generate_state(1)[0] & 0x7FFFFFFF) if (ikp < 1 or okp < 1) else 0
         # "auto": the fp32-grade tensor-core mode where the shape allows it (rnn_size % 16 == 0 and the hi + lo
         # recurrent slices fit in shared memory), else the fp32 FFMA kernels - both CUDA, both at the 1e-4 parity bar.
         candidates = ["bf16x3", "fp32"] if precision == "auto" else [precision]
@@ -95,6 +100,19 @@ class Model(object):
         self._xy_host = torch.empty((2, B, S), dtype=torch.int32).pin_memory()
         self._xy_dev = torch.empty((2, B, S), dtype=torch.int32, device=dev)
         self._loss_host = torch.empty(1, dtype=f32).pin_memory()
+        self._xy_busy = None                    # event: the device copy of the pinned ids has been issued and not yet awaited
+        # Gradient exchange of the replicas in two buckets (CRNN_AR_OVERLAP=1): the top cells' bucket goes out while BPTT is
+        # still in the lower layers.  Measured on B200, config 3: it LOSES - 2 GPUs 4.70 -> 4.74 ms per step, 8 GPUs 4.75 ->
+        # 4.80 ms (twice each) - the NCCL kernel takes SMs and L2 bandwidth from the latency-bound recurrence kernels it
+        # runs beside, which costs more than the ~0.06 ms of exchange it hides.  Off by default: one all-reduce after BPTT.
+        self._ar_offset = self._ar_stream = self._ar_event = None
+        if self.world > 1 and training and int(os.environ.get("CRNN_AR_OVERLAP", "0")):
+            first, off1 = parallel.bucket_split(self.layout, args.num_layers)
+            if off1 is not None:
+                self._ar_offset, self._ar_stream = off1, torch.cuda.Stream(device=dev)
+                self._ar_event = torch.cuda.Event()
+                self._ar_event.record()         # (creates the CUDA event whose handle the library records)
+                check(self._lib.crnn_set_bucket_event(h, first, ctypes.c_void_p(self._ar_event.cuda_event)))
         self.input_data, self.targets = self._xy_host[0], self._xy_host[1]
         self.cell = _Cell(self)
         self.lr = 0.0                          # model.py:87
@@ -189,12 +207,18 @@ class Model(object):
             xd = x if x.dtype == torch.int32 else x.to(torch.int32)
             yd = None if y is None else (y if y.dtype == torch.int32 else y.to(torch.int32))
             return xd, yd, 0
+        if self._xy_busy is not None:           # the previous step's copy may still be reading the pinned buffer
+            self._xy_busy.synchronize()
+        else:
+            self._xy_busy = torch.cuda.Event()
         self._xy_host[0].copy_(torch.as_tensor(np.asarray(x)))
         if y is not None:
             self._xy_host[1].copy_(torch.as_tensor(np.asarray(y)))
             self._xy_dev.copy_(self._xy_host, non_blocking=True)
+            self._xy_busy.record()
             return self._xy_dev[0], self._xy_dev[1], self._xy_host.numel() * 4
         self._xy_dev[0].copy_(self._xy_host[0], non_blocking=True)
+        self._xy_busy.record()
         return self._xy_dev[0], None, self._xy_host[0].numel() * 4
 
     @staticmethod
@@ -227,7 +251,10 @@ class Model(object):
             check(self._lib.crnn_forward_backward(self._h, ptr(xd), ptr(yd), self._ld(xd), ptr(self._state),
                                                   ptr(self._state), ptr(self.params), ptr(self.grads),
                                                   ptr(self.workspace), st))
-            torch.distributed.all_reduce(self.grads, group=self.pg)      # the ONE exchange per step
+            if self._ar_offset is None:
+                parallel.allreduce_flat(self.grads, self.pg)             # the ONE exchange per step
+            else:                                                        # ... cut in two so its first half hides behind BPTT's tail
+                parallel.exchange_buckets(self.grads, self._ar_offset, self.P, self.pg, self._ar_stream, self._ar_event)
             check(self._lib.crnn_clip_adam(self._h, ptr(self.params), ptr(self.grads), ptr(self.adam_m),
                                            ptr(self.adam_v), self.lr, a.grad_clip, self.global_step,
                                            1.0 / self.world, ptr(self._gnorm), ptr(self.workspace), st))

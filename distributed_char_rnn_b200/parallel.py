@@ -84,6 +84,46 @@ def allreduce_flat(flat_tensor, group=None):
     return flat_tensor
 
 
+def bucket_split(layout, num_layers):
+    """``(first_layer, offset)`` of the EARLY bucket of the gradient exchange: the cells ``first_layer .. L-1`` (the top
+    half of the stack) are a contiguous tail ``[offset, P)`` of the flat buffer and are final well before BPTT has
+    reached the bottom layers.  ``layout`` rows are ``(name, offset, ...)``.  One layer: no early bucket (``(0, None)``)."""
+    if num_layers < 2:
+        return 0, None
+    first = num_layers - max(1, num_layers // 2)
+    key = "cell_%d/" % first
+    for row in layout:
+        if key in row[0]:
+            return first, int(row[1])
+    raise KeyError(key)
+
+
+def exchange_buckets(flat, offset, P, group=None, early_stream=None, early_event=None):
+    """Sum all-reduce of the flat gradient buffer ``[P + 2]`` in two buckets: ``[offset, P)`` (the top cells, issued on
+    ``early_stream`` as soon as ``early_event`` - recorded by the library inside BPTT, ``crnn_set_bucket_event`` - has
+    fired) and the rest ``[0, offset) + [P, P+2)`` on the current stream.  The caller's stream then waits for the
+    early bucket.  Without a stream / event (CPU, gloo) both buckets simply follow each other."""
+    import torch
+    import torch.distributed as dist
+    early, rest, tail = flat[offset:P], flat[:offset], flat[P:]
+    if early_stream is not None:
+        early_stream.wait_event(early_event)
+        with torch.cuda.stream(early_stream):
+            dist.all_reduce(early, op=dist.ReduceOp.SUM, group=group)
+    else:
+        dist.all_reduce(early, op=dist.ReduceOp.SUM, group=group)
+    if flat.is_cuda:                             # NCCL: the two pieces travel in one grouped launch
+        with dist._coalescing_manager(group=group, device=flat.device):
+            dist.all_reduce(rest, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(tail, op=dist.ReduceOp.SUM, group=group)
+    else:
+        dist.all_reduce(rest, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(tail, op=dist.ReduceOp.SUM, group=group)
+    if early_stream is not None:
+        torch.cuda.current_stream(flat.device).wait_stream(early_stream)
+    return flat
+
+
 def global_norm_from_flat(flat, layout, P, mult):
     """What ``crnn_clip_adam`` computes: dense tensors by their own squares, the embedding by
     the slices' sum of squares carried in ``flat[P]`` (``tf.global_norm`` on IndexedSlices)."""

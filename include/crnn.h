@@ -113,6 +113,14 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* d_x, const int32_t* d_y
                           const float* d_state_in, float* d_state_out,
                           const float* d_params, float* d_grads, void* d_workspace, void* stream);
 
+/* Overlap of the replicas' gradient exchange with BPTT's tail (replaces the per-variable gRPC pushes of the reference's
+ * workers, train.py:126-133: there each gradient travels as soon as its op has run).  `event` is a caller-owned
+ * cudaEvent_t (NULL: off).  Every later crnn_forward_backward records it, on the library's own stream, at the point
+ * where the gradients of cells first_layer .. num_layers-1 (a contiguous tail of the flat buffer, see
+ * crnn_param_layout) are final - for the top layers that is well before the call's work ends - so the caller can
+ * start all-reducing that bucket on a side stream while the lower layers are still in BPTT.                         */
+int crnn_set_bucket_event(crnn_handle* h, int32_t first_layer, void* event);
+
 /* clip_by_global_norm + AdamOptimizer.apply_gradients (model.py:91-98).  `step` is the
  * 1-based Adam step t (beta powers beta^t); grads are read as grad_mult * d_grads
  * (grad_mult = 1/world after a sum all-reduce, 1 for a single process).

@@ -34,7 +34,12 @@ def _worker(rank, world, port, model, out_dir):
     fb = O.forward_backward(cfg, params, x, y, O.zero_state(cfg, np.float64), np.float64)
     lay, P = PL.flat_layout(model, H, L, V)
     flat = torch.from_numpy(PL.pack(fb["grads"], lay, P, tail=(fb["emb_slices_sqnorm"], fb["loss"])).astype(np.float64))
+    first, off1 = PL.bucket_split(lay, L)
+    assert first == 1 and lay[[n for n, _, _ in lay].index("rnnlm/multi_rnn_cell/cell_1/" + lay[-2][0].split("cell_1/")[1])][1] >= off1
+    two = flat.clone()
     PL.allreduce_flat(flat)
+    PL.exchange_buckets(two, off1, P)                             # the same exchange cut in two buckets (+ the tail)
+    assert torch.equal(two, flat)
     flat = flat.numpy()
     mult = 1.0 / world
     gn = PL.global_norm_from_flat(flat, lay, P, mult)
@@ -60,6 +65,20 @@ def test_two_replicas_equal_one_process_on_stacked_batch(tmp_path, model):
     assert abs(float(r[0]["loss"]) - fb["loss"]) < 1e-6 * fb["loss"]
     assert abs(float(r[0]["gn"]) - O.global_norm(cfg, fb)) < 1e-6 * float(r[0]["gn"])   # incl. the un-deduplicated slices term
     assert float(r[0]["gn"]) > 0.05
+
+
+def test_bucket_split_is_a_contiguous_tail():
+    for model, L in (("lstm", 2), ("gru", 3), ("rnn", 4), ("lstm", 1)):
+        lay, P = PL.flat_layout(model, 16, L, 9)
+        first, off = PL.bucket_split(lay, L)
+        if L == 1:
+            assert off is None
+            continue
+        assert first == L - max(1, L // 2)
+        early = [n for n, o, _ in lay if o >= off]
+        assert early and all("cell_%d/" % l in n for n in early for l in [int(n.split("cell_")[1].split("/")[0])] if l >= first)
+        assert all(int(n.split("cell_")[1].split("/")[0]) >= first for n in early)
+        assert all(("cell_" not in n) or int(n.split("cell_")[1].split("/")[0]) < first for n, o, _ in lay if o < off)
 
 
 def test_reference_shards_give_each_rank_223_batches(tmp_path):
