@@ -61,6 +61,7 @@ struct RecPlanTc {
     int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
     int q_fwd, q_bwd;       // K parts per unit group (cluster size) of the forward / backward kernel
     int ring_fwd, ring_bwd; // TMA ring bytes
+    int pr, sub;            // rows per pass; 1: the passes of a tile are independent chains (RecTcArgs::sub)
     int gather;             // 1: direct exchange of the streamed rows (recurrence_tc.cuh: rt_gather) instead of TMA loads behind a step barrier
     int g_rp_log2, g_ckb_log2;
     size_t smem_fwd, smem_bwd;
@@ -237,7 +238,7 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         o->HC = HC; o->BT = BT; o->nslices = nslices; o->ntiles = ceil_div(B, BT);
         o->npass = ceil_div(BT, 128);
         o->box_rows = o->npass > 1 ? 128 : std::min(128, (BT + 7) & ~7);
-        const int rows = std::min(128, BT);
+        int rows = std::min(128, BT);
         // MMA orientation: cost ~ N with M fixed at 128, so put the smaller of (gate columns, rows) on N
         const int rows16 = (rows + 15) & ~15;
         const int sw_env = env_int("CRNN_TC_SWAP", -1);
@@ -271,6 +272,22 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         const int q_env = env_int("CRNN_TC_KSPLIT", -1);       // -1 auto, 0/1 off, 2/4 forced
         o->q_fwd = q_env == 0 || q_env == 1 ? 1 : pick_q(g1, std::max(q_env, 0));
         o->q_bwd = q_env == 0 || q_env == 1 ? 1 : pick_q(1, std::max(q_env, 0));
+        // Sub-chains (CRNN_TC_SUB=n): a tile's rows are cut into n passes that are chains of their own (own step barrier
+        // word, released pass by pass).  The CTA keeps ONE resident weight slice for all of them and works on pass k+1
+        // while pass k waits for the other slices: the exchange latency hides behind useful work of the same CTA.
+        o->pr = 128; o->sub = 0;
+        {
+            // Measured on B200, config 3 (ms per step): split precision (tiles of 128 rows -> 2 x 64) 4.65 -> 3.98, four passes
+            // 5.27; plain bf16 (tiles of 64 rows -> 2 x 32, half-empty M = 64 MMAs and twice as many of them) 3.02 -> 3.26.
+            // At the same slice width (HC = 32) two passes also help plain bf16 a little: 3.06 -> 2.94.  Default: two passes for
+            // tiles of at least 64 rows.
+            const int nsub = env_int("CRNN_TC_SUB", BT >= 64 ? 2 : 0);
+            if (nsub > 1 && o->q_fwd == 1 && o->q_bwd == 1 && !o->swap_fwd && !o->swap_bwd && BT >= 16 * nsub) {
+                const int pr = (ceil_div(BT, nsub) + 7) & ~7;
+                const int np = ceil_div(BT, pr);
+                if (pr <= 128 && np > 1 && o->ntiles * np <= 64) { o->pr = pr; o->sub = 1; o->npass = np; o->box_rows = pr; rows = pr; }
+            }
+        }
         o->zs_fwd = rows * (g1 * HC * o->q_fwd + 1);
         o->zs_bwd = rows * (HC * o->q_bwd + 1);
         o->ring_fwd = o->ring_bwd = tc::RT_RING_BYTES;
@@ -335,12 +352,16 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
     const int hc_max = std::min((h->split ? 128 : 256) / g1, H) & ~15;   // MMA N <= 256 (split operands: N = 2 * columns)
     int best = 0;
     RecPlanTc cand;
-    for (int HC = hc_max; HC >= 16; HC -= 16) {
-        if (hc_env >= 16 && HC > hc_env) continue;
-        if (!fill(HC, &cand)) continue;
-        if (best == 0 || cand.nslices * cand.ntiles > out->nslices * out->ntiles) { best = HC; *out = cand; }
-        if (hc_env >= 16 || cand.nslices * cand.ntiles >= (max_ctas * 3) / 4) break;
-    }
+    // (slice widths that divide H first: a ragged last slice idles most of one CTA per tile - HC = 48 at H = 512 measured
+    //  3.29 ms per step against 2.94 at HC = 32)
+    for (int even = 1; even >= 0 && best == 0; --even)
+        for (int HC = hc_max; HC >= 16; HC -= 16) {
+            if (hc_env >= 16 && HC > hc_env) continue;
+            if (even && hc_env < 16 && H % HC != 0) continue;
+            if (!fill(HC, &cand)) continue;
+            if (best == 0 || cand.nslices * cand.ntiles > out->nslices * out->ntiles) { best = HC; *out = cand; }
+            if (hc_env >= 16 || cand.nslices * cand.ntiles >= (max_ctas * 3) / 4) break;
+        }
     if (best == 0) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory%s", H,
                                   h->split ? " with split operands (use CRNN_PREC_BF16 or CRNN_PREC_FP32)" : "");
     return CRNN_OK;
@@ -542,6 +563,11 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     }
     if (rc != CRNN_OK) { for (cudaStream_t s_ : h->wf_streams) cudaStreamDestroy(s_); if (h->err_word) cudaFreeHost(h->err_word); delete h; return rc; }
     build_workspace(h);
+    if (env_int("CRNN_VERBOSE", 0) && h->tc)
+        fprintf(stderr, "[crnn] plan: HC %d BT %d slices %d tiles %d passes %d x %d rows%s, K split fwd/bwd %d/%d, ring %d/%d KB, smem %zu/%zu, "
+                "wavefront %d layers x %d chunks, workspace %.1f MB\n", h->tcp.HC, h->tcp.BT, h->tcp.nslices, h->tcp.ntiles, h->tcp.npass, h->tcp.pr,
+                h->tcp.sub ? " (sub-chains)" : "", h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
+                h->tcp.smem_bwd, h->wf_W, h->wf_C, h->ws.total / 1e6);
     *out = h;
     return CRNN_OK;
 }
@@ -812,10 +838,11 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     const int HCG = p.HC * Q;                        // units per group (the columns one CTA contracts)
     a.ksplit = Q;
     a.HC = p.HC; a.BT = p.BT; a.nslices = p.nslices; a.ntiles = p.ntiles; a.npass = p.npass; a.box_rows = p.box_rows;
+    a.pr = p.pr; a.sub = p.sub;
     a.fast_act = h->fast_act;
     a.zs_floats = backward ? p.zs_bwd : p.zs_fwd;
     a.swap = backward ? p.swap_bwd : p.swap_fwd;
-    a.m64 = (!a.swap && p.npass == 1 && p.BT <= 64 && h->env.m64) ? 1 : 0;
+    a.m64 = (!a.swap && std::min(p.pr, p.BT) <= 64 && h->env.m64) ? 1 : 0;
     a.dbg = (!backward && h->env.dbg && h->dbg_layer == h->env.dbg_layer) ? h->dbg_ptr : nullptr;
     CUtensorMap t0, t1, w0, w1, t0l, t1l, w0l, w1l;
     int rc;
@@ -880,7 +907,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     if (rc != CRNN_OK) return rc;
     // elements per epilogue thread per batch: one batch per 128-row pass when 8 per thread cover it, so every global
     // load of the pass is in flight before the accumulator arrives
-    const int per_pass = std::min(128, p.BT) * p.HC;
+    const int per_pass = std::min(p.pr, p.BT) * p.HC;
     const bool ub8 = per_pass > tc::RT_EPI_THREADS * 4 && h->env.ub8;
     a.defer = h->env.defer;
     a.acq_poll = h->env.acq_poll;
@@ -915,7 +942,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     // config 3 but eight of them with ~190 KB of shared memory per CTA are not co-scheduled, which costs
     // the layer wavefront far more than that.
     const int cbar_max = h->env.cbar;
-    if (!a.gather && p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
+    if (!a.gather && !a.sub && p.nslices <= cbar_max && (p.nslices == 2 || p.nslices == 4 || p.nslices == 8 || p.nslices == 16)) {
         csize = p.nslices;
         a.cbar = 1;
     }

@@ -58,6 +58,10 @@ struct RecTcArgs {
     int B, H, S;
     int t_begin, t_end;         // steps this launch covers (absolute; chunks of one sequence run as separate launches)
     int HC, BT, nslices, ntiles, npass;
+    int pr;                     // rows per pass (128, or less when a tile is cut into sub-chains)
+    int sub;                    // 1: every pass of a tile is a chain of its own (own step barrier word, published per pass): while
+                                // one pass waits for the other slices, the CTA works on the next - the exchange latency of a
+                                // pass hides behind the other passes' MMAs and cell updates (same resident weights for all)
     int GS;                     // gate-stash row width / H
     int box_rows;               // rows per A-tile TMA box
     int ckb, nst;               // ring geometry, fixed per launch: K tiles per stage, number of stages
@@ -472,8 +476,8 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
 
 // Grid barrier, split: epilogue threads publish, the TMA producer waits before touching
 // rows written by other CTAs (generic-proxy writes -> async-proxy reads need the proxy fence).
-__device__ __forceinline__ void rt_publish(unsigned* counter, int epi_tid) {
-    epi_bar_sync();                                  // every epilogue thread's stores happen-before ...
+__device__ __forceinline__ void rt_publish(unsigned* counter, int epi_tid, int synced = 0) {
+    if (!synced) epi_bar_sync();                     // every epilogue thread's stores happen-before ...
     if (epi_tid == 0)                                // ... this release, which is cumulative over them
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
 }
@@ -692,7 +696,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     extern __shared__ uint8_t smem_raw[];
     constexpr int G1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
     constexpr int GW = MODEL == CRNN_MODEL_GRU ? 3 : G1;
-    const int B = a.B, H = a.H, HC = a.HC;
+    const int B = a.B, H = a.H, HC = a.HC, PR = a.pr;
     const int Q = a.ksplit;                           // K parts per unit group (= cluster size when > 1)
     const int HCG = HC * Q;                           // units whose gate columns this CTA contracts
     const int NCA = G1 * HCG;
@@ -758,12 +762,15 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 if (lane == 0) {
                     const int dbg_phase = (int)phases_done;
                     RT_STAMP(0);
-                    if (!a.gather && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+                    if (!a.gather && !a.sub && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     RT_STAMP(1);
-                    for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * 128, nkb, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb,
+                    for (int ps = 0; ps < a.npass; ++ps) {
+                        // sub-chains: pass ps of this phase only needs pass ps of the previous phase from the other slices
+                        if (a.sub && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
+                        rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * PR, nkb, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb,
                                    a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr, rot,
                                    (!a.gather && dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
+                    }
                     RT_STAMP(2);
                 }
                 ++phases_done;
@@ -777,7 +784,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
-                        rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
+                        rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
                                (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot, a.gather);
                     if (lane == 0) RT_STAMP(3);
                 }
@@ -819,9 +826,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 bool pending = false;
                 const int hq = hcv / VEC;                                        // vectors per row of the slice
                 for (int ps = 0; ps < a.npass; ++ps) {
-                    const int nr = min(128, bt - ps * 128);
+                    const int nr = min(PR, bt - ps * PR);
                     const int nquads = nr * hq;
-                    const int b0row = b0 + ps * 128;
+                    const int b0row = b0 + ps * PR;
                     const int gstride = ph == 0 ? G1 : 1;
                     const int64_t ob = (int64_t)b0row * H + j0;                  // [B,H] tensors
                     float* gp = gt + (tB + b0row) * gw + j0;                     // gate stash rows of this pass
@@ -832,7 +839,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     float* cn_ = MODEL == CRNN_MODEL_LSTM ? a.cx + (int64_t)(t + 1) * BH + ob : nullptr;
                     __nv_bfloat16* rs_ = MODEL == CRNN_MODEL_GRU ? a.rsb + (tB + b0row) * H + j0 : nullptr;
                     for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {
-                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
+                        const bool defer = a.defer && (a.sub || ps == a.npass - 1) && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
                         // ---- issue every global load of this batch before touching the accumulator
 #pragma unroll
                         for (int u = 0; u < UB; ++u) x0[u] = x1[u] = x2[u] = x3[u] = ax[u] = hv[u] = 0.f;
@@ -928,14 +935,16 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     { const int dbg_phase = (t - a.t_begin) * nphase + ph; if (epi_tid == 0) RT_STAMP(8); if (epi_tid == RT_EPI_THREADS - 1) RT_STAMP(9); }
                     epi_bar_sync();          // Zs is reused by the next pass / phase
                     RT_RELEASE_PARTIALS();
-                }
+                    if (!a.sub && ps + 1 < a.npass) continue;
+                    // ---- the pass (sub-chains) or the whole phase is done on this CTA: release it, then the deferred stores
                 const int dbg_phase = (t - a.t_begin) * nphase + ph;
                 if (epi_tid == 0) RT_STAMP(6);
                 if (a.gather) { /* the stored rows are their own signal */ }
-                else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+                else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize);
+                else rt_publish(a.sub ? a.barrier + tile * a.npass + ps : a.barrier + tile, epi_tid, a.sub);
                 if (epi_tid == 0) RT_STAMP(7);
                 if (pending && !(a.expt & 4)) {   // the stores nobody else waits for
-                    const int b0row = b0 + (a.npass - 1) * 128;                  // the deferred batch belongs to the last pass
+                    const int b0row = b0 + ps * PR;                              // the deferred batch belongs to this (the last) pass
                     const int64_t ob = (int64_t)b0row * H + j0;
 #pragma unroll
                     for (int qd = 0; qd < UB / VEC; ++qd) {
@@ -956,7 +965,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         }
                     }
                 }
+                pending = false;
                 if (epi_tid == 0) RT_STAMP(13);
+                }   // passes
             }
         }
     }
@@ -986,7 +997,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     extern __shared__ uint8_t smem_raw[];
     constexpr int G1 = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 2 : 1);
     constexpr int GZ = MODEL == CRNN_MODEL_LSTM ? 4 : (MODEL == CRNN_MODEL_GRU ? 3 : 1);
-    const int B = a.B, H = a.H, HC = a.HC;
+    const int B = a.B, H = a.H, HC = a.HC, PR = a.pr;
     const int Q = a.ksplit;
     const int HCG = HC * Q;
     const int nkb0 = ceil_div(G1 * H, 64) / Q;        // this CTA's part of the gate-column contraction
@@ -1046,20 +1057,24 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (a.gather && phases_done > 0)
                     rt_probe(a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0 + bt - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
                 if (lane == 0) {
-                    if (!a.gather && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
-                    for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * 128, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb0,
+                    if (!a.gather && !a.sub && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+                    for (int ps = 0; ps < a.npass; ++ps) {
+                        if (a.sub && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
+                        rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * PR, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb0,
                                    a.split ? &tmZ0l : nullptr, rot0);
+                    }
                 }
             }
             ++phases_done;
             if (MODEL == CRNN_MODEL_GRU) {
                 if (a.gather) rt_probe(a.dzb + 2 * H, a.dzb_lo, (int64_t)t * B + b0 + bt - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
                 if (lane == 0) {
-                    if (!a.gather) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
-                    for (int ps = 0; ps < a.npass; ++ps)
-                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * 128, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb1,
+                    if (!a.gather && !a.sub) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+                    for (int ps = 0; ps < a.npass; ++ps) {
+                        if (a.sub) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
+                        rt_produce(s, p, &tmZ1, t * B + b0 + ps * PR, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb1,
                                    a.split ? &tmZ1l : nullptr, rot1);
+                    }
                 }
                 ++phases_done;
             }
@@ -1070,9 +1085,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0, a.gather);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0, a.gather);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(128, bt - ps * 128) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1, a.gather);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1, a.gather);
             }
         }
     } else {
@@ -1108,15 +1123,15 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             bool pending = false;
             const int hq = hcv / VEC;
             for (int ps = 0; ps < a.npass; ++ps) {
-                const int nr = min(128, bt - ps * 128);
+                const int nr = min(PR, bt - ps * PR);
                 const int nquads = nr * hq;
-                const int b0row = b0 + ps * 128;
+                const int b0row = b0 + ps * PR;
                 const int64_t ob = (int64_t)b0row * H + j0;
                 const float* gp = a.gates + (tB + b0row) * gw + j0;
                 float* dzp = a.dz + (tB + b0row) * zw + j0;
                 __nv_bfloat16* dzbp = a.dzb + (tB + b0row) * zw + j0;
                 for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {
-                    const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
+                    const bool defer = a.defer && (a.sub || ps == a.npass - 1) && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
                     float dyv[UB], c0v[UB], c1v[UB], cr[UB];
 #pragma unroll
                     for (int u = 0; u < UB; ++u) dyv[u] = v0[u] = v1[u] = v2[u] = v3[u] = v4[u] = c0v[u] = c1v[u] = cr[u] = 0.f;
@@ -1202,11 +1217,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 }
                 epi_bar_sync();
                 if (has_next) RT_RELEASE_PARTIALS();
-            }
+                if (!a.sub && ps + 1 < a.npass) continue;
+                // ---- the pass (sub-chains) or the whole phase is done on this CTA: release it, then the deferred stores
             if (a.gather) { /* the stored rows are their own signal */ }
-            else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+            else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize);
+            else rt_publish(a.sub ? a.barrier + tile * a.npass + ps : a.barrier + tile, epi_tid, a.sub);
             if (pending) {
-                const int b0row = b0 + (a.npass - 1) * 128;
+                const int b0row = b0 + ps * PR;
                 const int64_t ob = (int64_t)b0row * H + j0;
                 float* dzp = a.dz + (tB + b0row) * zw + j0;
 #pragma unroll
@@ -1225,18 +1242,20 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     }
                 }
             }
+            pending = false;
+            }   // passes
             if (MODEL == CRNN_MODEL_GRU) {
                 pending = false;
                 if (a.gather)   // this step's candidate columns [2H, 3H) of dz
                     gpos = rt_validate(gg, gpos, a.dzb + 2 * H, a.dzb_lo, tB + b0, bt, (int)zw, 0, H, nkb1, epi_tid, lane, nullptr);
                 for (int ps = 0; ps < a.npass; ++ps) {
-                    const int nr = min(128, bt - ps * 128);
+                    const int nr = min(PR, bt - ps * PR);
                     const int nquads = nr * hq;
-                    const int b0row = b0 + ps * 128;
+                    const int b0row = b0 + ps * PR;
                     const int64_t ob = (int64_t)b0row * H + j0;
                     const float* gp = a.gates + (tB + b0row) * gw + j0;
                     for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {
-                        const bool defer = a.defer && ps == a.npass - 1 && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
+                        const bool defer = a.defer && (a.sub || ps == a.npass - 1) && base + RT_EPI_THREADS * (UB / VEC) >= nquads;
                         float hp[UB], c1v[UB];
 #pragma unroll
                         for (int u = 0; u < UB; ++u) v0[u] = v1[u] = v4[u] = hp[u] = c1v[u] = 0.f;
@@ -1279,11 +1298,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     }
                     epi_bar_sync();
                     RT_RELEASE_PARTIALS();
-                }
+                    if (!a.sub && ps + 1 < a.npass) continue;
                 if (a.gather) { }
-                else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize); else rt_publish(a.barrier + tile, epi_tid);
+                else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize);
+                else rt_publish(a.sub ? a.barrier + tile * a.npass + ps : a.barrier + tile, epi_tid, a.sub);
                 if (pending) {
-                    const int b0row = b0 + (a.npass - 1) * 128;
+                    const int b0row = b0 + ps * PR;
                     const int64_t ob = (int64_t)b0row * H + j0;
 #pragma unroll
                     for (int qd = 0; qd < UB / VEC; ++qd) {
@@ -1292,6 +1312,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                         stv<VEC>(a.carry0 + ob + e[qd].r * H + e[qd].jj, v4 + VEC * qd);
                     }
                 }
+                pending = false;
+                }   // passes
             }
         }
     }
