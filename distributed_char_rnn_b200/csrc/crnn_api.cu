@@ -327,9 +327,9 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         // buys ~1 k of ~10 k cycles per phase in the forward kernel and nothing over the whole step.  A kernel running
         // alone gains 18 % (6.9 k vs 8.4-9.3 k cycles per phase).  Off by default.
         o->gather = 0; o->g_rp_log2 = o->g_ckb_log2 = 0;
-        if (env_int("CRNN_TC_GATHER", 0) && o->npass == 1 && o->q_fwd == 1 && o->q_bwd == 1 && !o->swap_fwd && !o->swap_bwd) {
+        if (env_int("CRNN_TC_GATHER", 0) && (o->npass == 1 || o->sub) && o->q_fwd == 1 && o->q_bwd == 1 && !o->swap_fwd && !o->swap_bwd) {
             const int tile = tc::rt_tile_bytes(o->box_rows), nsp = 1 + h->split;
-            int rp = 5; while ((1 << rp) < BT) ++rp;
+            int rp = 5; while ((1 << rp) < rows) ++rp;
             int ck = 0;
             while ((2 << ck) <= nkb && nsp * (1 << rp) * (2 << ck) * 8 <= 4096 && (2 << ck) * tile <= 16384) ++ck;
             { const int ck_env = env_int("CRNN_TC_CKB", 0); if (ck_env > 0) { ck = 0; while ((2 << ck) <= ck_env && (2 << ck) <= nkb && nsp * (1 << rp) * (2 << ck) * 8 <= 4096) ++ck; } }

@@ -404,7 +404,7 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
 // Executed by ALL lanes of the (converged) MMA warp with warp-uniform arguments; one elected lane issues.
 __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
                                        int swap, int nrows16, int box_rows, int ckb, int nst, int m64,
-                                       long long* stamps = nullptr, int split = 0, int rot = 0, int checked = 0) {
+                                       long long* stamps = nullptr, int split = 0, int rot = 0, int checked = 0, int lite = 0) {
     const int tile = rt_tile_bytes(box_rows);
     const bool lane0 = (threadIdx.x & 31) == 0;
     // split: lo tiles sit ckb tiles after their hi tiles in the stage, the lo weight region right after the hi one
@@ -437,6 +437,7 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
                 db = desc_kmajor(w0 + (uint32_t)kbr * (uint32_t)(2 * nc) * 128u);
                 const uint64_t db2_step = (uint64_t)((2 * nc * 128) >> 4);
                 for (int j = 0; j < n; ++j, da += da_step, db += db2_step) {
+                    if (lite) { mma_bf16(tmem, da, db, idesc2, (uint32_t)((kb0 + j) != 0)); continue; }   // timing experiment: an eighth of the MMAs
 #pragma unroll
                     for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + k, idesc2, (uint32_t)((kb0 + j + k) != 0));
 #pragma unroll
@@ -454,6 +455,7 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
             } else if (!swap) {
                 for (int j = 0; j < n; ++j, da += da_step, db += db_step) {
                     mma_bf16(tmem, da, db, idesc, (uint32_t)((kb0 + j) != 0));
+                    if (lite) continue;
                     mma_bf16(tmem, da + 2, db + 2, idesc, 1u);
                     mma_bf16(tmem, da + 4, db + 4, idesc, 1u);
                     mma_bf16(tmem, da + 6, db + 6, idesc, 1u);
@@ -755,24 +757,27 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         }
         for (int t = a.t_begin; t < a.t_end; ++t) {
             for (int ph = 0; ph < nphase; ++ph) {
-                if (a.gather && phases_done > 0) {    // (the launch's first phase reads rows an earlier launch or the host wrote)
-                    const bool second = MODEL == CRNN_MODEL_GRU && ph == 1;
-                    rt_probe(second ? a.rsb : a.hxb, second ? a.rsb_lo : a.hxb_lo, (int64_t)t * B + b0 + bt - 1, H, 0, HC, H, a.nslices, lane, a.err);
-                }
+                const int dbg_phase = (int)phases_done;
                 if (lane == 0) {
-                    const int dbg_phase = (int)phases_done;
                     RT_STAMP(0);
                     if (!a.gather && !a.sub && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
                     RT_STAMP(1);
-                    for (int ps = 0; ps < a.npass; ++ps) {
+                }
+                for (int ps = 0; ps < a.npass; ++ps) {
+                    if (a.gather && phases_done > 0) {    // (the launch's first phase reads rows an earlier launch or the host wrote)
+                        const bool second = MODEL == CRNN_MODEL_GRU && ph == 1;
+                        rt_probe(second ? a.rsb : a.hxb, second ? a.rsb_lo : a.hxb_lo, (int64_t)t * B + b0 + ps * PR + min(PR, bt - ps * PR) - 1, H, 0, HC, H,
+                                 a.nslices, lane, a.err);
+                    }
+                    if (lane == 0) {
                         // sub-chains: pass ps of this phase only needs pass ps of the previous phase from the other slices
-                        if (a.sub && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
+                        if (a.sub && !a.gather && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
                         rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * PR, nkb, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb,
                                    a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr, rot,
                                    (!a.gather && dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
                     }
-                    RT_STAMP(2);
                 }
+                if (lane == 0) RT_STAMP(2);
                 ++phases_done;
             }
         }
@@ -785,7 +790,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
                     for (int ps = 0; ps < a.npass; ++ps)
                         rt_mma(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64,
-                               (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot, a.gather);
+                               (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr, a.split, rot, a.gather, a.expt & 32);
                     if (lane == 0) RT_STAMP(3);
                 }
         }
@@ -815,12 +820,6 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 // registers across the step barrier: only the bf16 rows other CTAs stream next (hxb / rsb) are
                 // stored before the release, everything this CTA alone reads later (fp32 h, c, the gate stash for
                 // BPTT) is stored after it - the release waits for every store issued before it.
-                if (a.gather) {   // this phase's rows: h_{t-1} (slot t of hxb) or r*h of this step, as the other slices finish them
-                    const int gph = (t - a.t_begin) * nphase + ph;
-                    long long* gstamp = (dbgs && gph >= 20 && gph < 28) ? dbgs + (gph - 20) * 24 : nullptr;
-                    const bool second = MODEL == CRNN_MODEL_GRU && ph == 1;
-                    gpos = rt_validate(gg, gpos, second ? a.rsb : a.hxb, second ? a.rsb_lo : a.hxb_lo, tB + b0, bt, H, 0, H, nkb, epi_tid, lane, gstamp);
-                }
                 EpiIdx e[UB / VEC];
                 float x0[UB], x1[UB], x2[UB], x3[UB], ax[UB], hv[UB];
                 bool pending = false;
@@ -829,6 +828,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     const int nr = min(PR, bt - ps * PR);
                     const int nquads = nr * hq;
                     const int b0row = b0 + ps * PR;
+                    if (a.gather) {   // this pass's rows: h_{t-1} (slot t of hxb) or r*h of this step, as the other slices finish them
+                        const int gph = (t - a.t_begin) * nphase + ph;
+                        long long* gstamp = (dbgs && gph >= 20 && gph < 28) ? dbgs + (gph - 20) * 24 : nullptr;
+                        const bool second = MODEL == CRNN_MODEL_GRU && ph == 1;
+                        gpos = rt_validate(gg, gpos, second ? a.rsb : a.hxb, second ? a.rsb_lo : a.hxb_lo, tB + b0row, nr, H, 0, H, nkb, epi_tid, lane, gstamp);
+                    }
                     const int gstride = ph == 0 ? G1 : 1;
                     const int64_t ob = (int64_t)b0row * H + j0;                  // [B,H] tensors
                     float* gp = gt + (tB + b0row) * gw + j0;                     // gate stash rows of this pass
@@ -1054,12 +1059,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         for (int t = a.t_end - 1; t >= a.t_begin; --t) {
             // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
             if (t + 1 < a.S) {
-                if (a.gather && phases_done > 0)
-                    rt_probe(a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0 + bt - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
-                if (lane == 0) {
-                    if (!a.gather && !a.sub && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
-                    for (int ps = 0; ps < a.npass; ++ps) {
-                        if (a.sub && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
+                if (lane == 0 && !a.gather && !a.sub && phases_done > 0) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+                for (int ps = 0; ps < a.npass; ++ps) {
+                    if (a.gather && phases_done > 0)
+                        rt_probe(a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0 + ps * PR + min(PR, bt - ps * PR) - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
+                    if (lane == 0) {
+                        if (a.sub && !a.gather && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
                         rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * PR, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb0,
                                    a.split ? &tmZ0l : nullptr, rot0);
                     }
@@ -1067,11 +1072,11 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             }
             ++phases_done;
             if (MODEL == CRNN_MODEL_GRU) {
-                if (a.gather) rt_probe(a.dzb + 2 * H, a.dzb_lo, (int64_t)t * B + b0 + bt - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
-                if (lane == 0) {
-                    if (!a.gather && !a.sub) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
-                    for (int ps = 0; ps < a.npass; ++ps) {
-                        if (a.sub) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
+                if (lane == 0 && !a.gather && !a.sub) { if (a.cbar) rt_await_cluster(s.step_bar, phases_done); else rt_await(a.barrier + tile, phases_done * a.nslices, a.acq_poll); }
+                for (int ps = 0; ps < a.npass; ++ps) {
+                    if (a.gather) rt_probe(a.dzb + 2 * H, a.dzb_lo, (int64_t)t * B + b0 + ps * PR + min(PR, bt - ps * PR) - 1, (int)zw, 0, HC, H, a.nslices, lane, a.err);
+                    if (lane == 0) {
+                        if (a.sub && !a.gather) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
                         rt_produce(s, p, &tmZ1, t * B + b0 + ps * PR, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb1,
                                    a.split ? &tmZ1l : nullptr, rot1);
                     }
@@ -1085,9 +1090,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             mbar_wait(s.w_bar, 0);
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0, a.gather);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0, a.gather, a.expt & 32);
                 if (MODEL == CRNN_MODEL_GRU)
-                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1, a.gather);
+                    for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsb, HCG, nkb1, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot1, a.gather, a.expt & 32);
             }
         }
     } else {
@@ -1116,8 +1121,6 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             // Same split as the forward epilogue: only the bf16 dz rows other CTAs stream next are stored before the
             // step barrier's release; fp32 dz (read by the weight-gradient GEMMs' bias sums after the kernel) and the
             // carries (read back by the same thread) of the phase's last batch go out after it.
-            if (a.gather && has_next)   // dz_{t+1}, gate columns [0, G1*H), as the other slices finish them
-                gpos = rt_validate(gg, gpos, a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0, bt, (int)zw, 0, G1 * H, nkb0, epi_tid, lane, nullptr);
             EpiIdx e[UB / VEC];
             float v0[UB], v1[UB], v2[UB], v3[UB], v4[UB];
             bool pending = false;
@@ -1126,6 +1129,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 const int nr = min(PR, bt - ps * PR);
                 const int nquads = nr * hq;
                 const int b0row = b0 + ps * PR;
+                if (a.gather && has_next)   // dz_{t+1}, gate columns [0, G1*H), as the other slices finish them
+                    gpos = rt_validate(gg, gpos, a.dzb, a.dzb_lo, (int64_t)(t + 1) * B + b0row, nr, (int)zw, 0, G1 * H, nkb0, epi_tid, lane, nullptr);
                 const int64_t ob = (int64_t)b0row * H + j0;
                 const float* gp = a.gates + (tB + b0row) * gw + j0;
                 float* dzp = a.dz + (tB + b0row) * zw + j0;
@@ -1246,12 +1251,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             }   // passes
             if (MODEL == CRNN_MODEL_GRU) {
                 pending = false;
-                if (a.gather)   // this step's candidate columns [2H, 3H) of dz
-                    gpos = rt_validate(gg, gpos, a.dzb + 2 * H, a.dzb_lo, tB + b0, bt, (int)zw, 0, H, nkb1, epi_tid, lane, nullptr);
                 for (int ps = 0; ps < a.npass; ++ps) {
                     const int nr = min(PR, bt - ps * PR);
                     const int nquads = nr * hq;
                     const int b0row = b0 + ps * PR;
+                    if (a.gather)   // this step's candidate columns [2H, 3H) of dz
+                        gpos = rt_validate(gg, gpos, a.dzb + 2 * H, a.dzb_lo, tB + b0row, nr, (int)zw, 0, H, nkb1, epi_tid, lane, nullptr);
                     const int64_t ob = (int64_t)b0row * H + j0;
                     const float* gp = a.gates + (tB + b0row) * gw + j0;
                     for (int base = 0; base < nquads; base += RT_EPI_THREADS * (UB / VEC)) {

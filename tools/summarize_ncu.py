@@ -3,6 +3,8 @@
 
   python tools/summarize_ncu.py launches gpurun_out/launches_c3.csv           # per-kernel share of the step
   python tools/summarize_ncu.py report   gpurun_out/prof_rec_c3.ncu-rep       # key metrics per captured launch
+  python tools/summarize_ncu.py rawcsv   gpurun_out/r02_rec_c3.raw.csv        # the same from `ncu -i X --page raw --csv`
+  python tools/summarize_ncu.py traffic  gpurun_out/r02_rec_c3.raw.csv ...    # {kernel: dram bytes per launch} as JSON
 """
 import collections
 import csv
@@ -52,5 +54,59 @@ def report(path):
             print("   %-70s %s %s" % (hdr[i], r[i], units[i]))
 
 
+HBM_PEAK_GBS = 6455.9      # MEASURED_PEAKS.json (copy bandwidth)
+
+
+def _rows(path):
+    rows = list(csv.reader(open(path)))
+    start = next(i for i, r in enumerate(rows) if "Kernel Name" in r)
+    return rows[start], rows[start + 1], rows[start + 2:]
+
+
+def _num(x):
+    try:
+        return float(x.replace(",", ""))
+    except Exception:
+        return None
+
+
+def rawcsv(path):
+    hdr, units, rows = _rows(path)
+    idx = [hdr.index(w) for w in WANT if w in hdr]
+    for r in rows:
+        if len(r) <= max(idx):
+            continue
+        print(re.sub(r"\(.*", "", r[hdr.index("Kernel Name")]).replace("void ", "").replace("crnn::", ""),
+              " grid", r[hdr.index("Grid Size")] if "Grid Size" in hdr else "")
+        for i in idx:
+            print("   %-70s %s %s" % (hdr[i], r[i], units[i]))
+        t, rd, wr = (_num(r[hdr.index(k)]) if k in hdr else None for k in ("gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum"))
+        if t and rd is not None and wr is not None:
+            tu, bu = units[hdr.index("gpu__time_duration.sum")], units[hdr.index("dram__bytes_read.sum")]
+            sec = t * {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}.get(tu, 1e-9)
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(bu, 1.0)
+            wscale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(units[hdr.index("dram__bytes_write.sum")], 1.0)
+            tot = rd * scale + wr * wscale
+            print("   %-70s %.3f MB -> %.1f GB/s = %.3f of the measured copy peak" % ("DRAM traffic (read + write) / duration", tot / 1e6, tot / sec / 1e9,
+                                                                                     tot / sec / 1e9 / HBM_PEAK_GBS))
+
+
+def traffic(*paths):
+    import json
+    out = {}
+    for path in paths:
+        hdr, units, rows = _rows(path)
+        for r in rows:
+            try:
+                name = re.sub(r"[<(].*", "", r[hdr.index("Kernel Name")]).replace("void ", "").replace("crnn::", "").replace("tc::", "")
+                ri, wi = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+                sc = lambda i: {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(units[i], 1.0)
+                out.setdefault(name, []).append(_num(r[ri]) * sc(ri) + _num(r[wi]) * sc(wi))
+            except Exception:
+                continue
+    print(json.dumps({k: sum(v) / len(v) for k, v in out.items()}, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "report": report}[sys.argv[1]](sys.argv[2])
+    fn = {"launches": launches, "report": report, "rawcsv": rawcsv, "traffic": traffic}[sys.argv[1]]
+    fn(*sys.argv[2:]) if sys.argv[1] == "traffic" else fn(sys.argv[2])
