@@ -244,6 +244,8 @@ __global__ void __launch_bounds__(GT_THREADS) gemm_bf16_tc_kernel(const __grid_c
     }
 }
 
+inline bool env_splits_round_up() { static int v = -1; if (v < 0) { const char* e = getenv("CRNN_GEMM_SPLITS_UP"); v = (e && *e == '1') ? 1 : 0; } return v == 1; }
+
 // Host launcher.  A: op(A) is [M,K]; a_mn = 0 -> stored [M,K] row-major (lda), a_mn = 1 -> stored
 // [K,M] row-major.  B: op(B) is [K,N]; b_mn = 0 -> stored [N,K] row-major (i.e. B^T), b_mn = 1 ->
 // stored [K,N] row-major.  accumulate = 1 adds into C (split-K with atomics when that fills the GPU).
@@ -281,8 +283,12 @@ inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda
     const int total_kb = ceil_div(K, GT_BK);
     int splits = 1;
     const int64_t tiles = (int64_t)grid.x * grid.y;
-    if (accumulate && tiles < 2 * sm_count && total_kb >= 16)
-        splits = (int)std::min<int64_t>(ceil_div64(2 * sm_count, tiles), total_kb / 8);
+    // Split K so that the grid is ONE wave: the split kernel (192 KB of stages) is resident once per SM, the plain one twice.
+    // (Rounding the split count up instead - 336 CTAs on 148 slots for config 3's weight gradients - runs a nearly empty
+    //  third wave.)
+    const int64_t slots = (int64_t)sm_count * (split ? 1 : 2);
+    if (accumulate && tiles < slots && total_kb >= 16)
+        splits = (int)std::min<int64_t>(std::max<int64_t>(1, env_splits_round_up() ? ceil_div64(slots, tiles) : slots / tiles), total_kb / 8);
     splits = std::max(1, splits);
     g.kblocks_per_split = ceil_div(total_kb, splits);
     grid.z = ceil_div(total_kb, g.kblocks_per_split);
