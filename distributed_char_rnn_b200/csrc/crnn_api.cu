@@ -547,7 +547,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             int C = W > 1 ? std::max(1, std::min(16, cfg->seq_length / 10)) : 1;
             const int c_env = env_int("CRNN_WAVEFRONT_CHUNKS", 0);
             if (c_env > 0) C = std::min(std::min(c_env, cfg->seq_length), 32);
-            if (W == 1) C = 1;
+            if (W == 1 && c_env <= 0) C = 1;                 // (chunks without overlap only on request: measures the cost of a launch)
             h->wf_C = C;
             while (C > 1 && 2 * cfg->num_layers * C > 384) --C, h->wf_C = C;   // barrier blocks 0..383
             for (int i = 0; i < 2 * W && W > 1; ++i) {      // [0,W): recurrence streams, [W,2W): GEMM streams
