@@ -228,6 +228,7 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
     const int g1 = model == CRNN_MODEL_LSTM ? 4 : (model == CRNN_MODEL_GRU ? 2 : 1);
     const int nkb = ceil_div(H, 64);
     const int hc_env = env_int("CRNN_TC_HC", 0), nt_env = env_int("CRNN_TC_TILES", 0);
+    const int dbg = h->env.dbg != 0;                         // the stamp area of tools/dbg_rec_timeline.py
     auto fill = [&](int HC, RecPlanTc* o) -> bool {
         const int nslices = ceil_div(H, HC);
         if (nslices > max_ctas) return false;
@@ -253,7 +254,8 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         // bytes per CTA; N grows Q-fold, the K extent and the streamed rows shrink Q-fold; the partial sums
         // are exchanged through distributed shared memory, whose staging area grows with N.
         const size_t wbytes = ((size_t)nkb * g1 * HC * 128 + (model == CRNN_MODEL_GRU ? (size_t)nkb * HC * 128 : 0)) * (size_t)(1 + h->split);
-        auto pick_q = [&](int ncols_per_unit, int env) -> int {
+        int ring_q[2] = {tc::RT_RING_BYTES, tc::RT_RING_BYTES};          // base ring per direction (a K split may trade ring for staging)
+        auto pick_q = [&](int ncols_per_unit, int env, int* ring) -> int {
             for (int Qc = 4; Qc >= 2; Qc >>= 1) {
                 if (env > 0 && Qc != env) continue;
                 // only long K, keep N <= 128
@@ -264,14 +266,19 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
                 if (env == 0 && Qc == 2 && ncols_per_unit > 1) continue;
                 if (H % (64 * Qc) != 0 || H % (HC * Qc) != 0 || nslices % Qc != 0) continue;
                 if (ncols_per_unit * HC * Qc > (h->split ? 128 : 256)) continue;   // split: the MMA's N is twice the columns
-                if ((int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1)) > h->max_smem) continue;
+                // the partial sums' staging area grows with Q: give it ring space down to 32 KB (the K extent per CTA shrinks
+                // Q-fold as well, so a stage still holds several K blocks)
+                int rb = tc::RT_RING_BYTES;
+                while (rb > 32 * 1024 && (int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) rb -= 16 * 1024;
+                if ((int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) continue;
+                *ring = rb;
                 return Qc;
             }
             return 1;
         };
         const int q_env = env_int("CRNN_TC_KSPLIT", -1);       // -1 auto, 0/1 off, 2/4 forced
-        o->q_fwd = q_env == 0 || q_env == 1 ? 1 : pick_q(g1, std::max(q_env, 0));
-        o->q_bwd = q_env == 0 || q_env == 1 ? 1 : pick_q(1, std::max(q_env, 0));
+        o->q_fwd = q_env == 0 || q_env == 1 ? 1 : pick_q(g1, std::max(q_env, 0), &ring_q[0]);
+        o->q_bwd = q_env == 0 || q_env == 1 ? 1 : pick_q(1, std::max(q_env, 0), &ring_q[1]);
         // Sub-chains (CRNN_TC_SUB=n): a tile's rows are cut into n passes that are chains of their own (own step barrier
         // word, released pass by pass).  The CTA keeps ONE resident weight slice for all of them and works on pass k+1
         // while pass k waits for the other slices: the exchange latency hides behind useful work of the same CTA.
@@ -290,9 +297,9 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         }
         o->zs_fwd = rows * (g1 * HC * o->q_fwd + 1);
         o->zs_bwd = rows * (HC * o->q_bwd + 1);
-        o->ring_fwd = o->ring_bwd = tc::RT_RING_BYTES;
-        o->smem_fwd = tc::rt_smem_bytes(wbytes, 0, o->zs_fwd);
-        o->smem_bwd = tc::rt_smem_bytes(wbytes, 0, o->zs_bwd);
+        o->ring_fwd = ring_q[0]; o->ring_bwd = ring_q[1];
+        o->smem_fwd = tc::rt_smem_bytes(wbytes, 0, o->zs_fwd, o->ring_fwd, dbg);
+        o->smem_bwd = tc::rt_smem_bytes(wbytes, 0, o->zs_bwd, o->ring_bwd, dbg);
         if ((int)std::max(o->smem_fwd, o->smem_bwd) > h->max_smem) return false;
         // A larger ring (CRNN_TC_RING_KB) where shared memory is left.  Plain bf16: measured no gain (config 3 at 64 / 96 /
         // 128 KB: 4.20 / 4.22 / 4.22 ms).  Split operands stream twice the bytes per K block, a 64 KB ring holds two
@@ -552,7 +559,13 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             while (C > 1 && 2 * cfg->num_layers * C > 384) --C, h->wf_C = C;   // barrier blocks 0..383
             for (int i = 0; i < 2 * W && W > 1; ++i) {      // [0,W): recurrence streams, [W,2W): GEMM streams
                 cudaStream_t s;
-                if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { rc = set_err(CRNN_ERR_CUDA, "cudaStreamCreate failed"); break; }
+                // The recurrence launches are the step's critical path and need a whole set of free SMs each (cooperative);
+                // the chunk GEMMs only have to be done a chunk later.  Highest priority for the former, lowest for the
+                // latter: an SM that frees up goes to a waiting recurrence CTA before another GEMM CTA (CRNN_WF_PRIO=0: off).
+                int prio_lo = 0, prio_hi = 0;
+                cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+                const int prio = !env_int("CRNN_WF_PRIO", 1) ? 0 : (i < W ? prio_hi : prio_lo);
+                if (cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, prio) != cudaSuccess) { rc = set_err(CRNN_ERR_CUDA, "cudaStreamCreate failed"); break; }
                 h->wf_streams.push_back(s);
             }
         }

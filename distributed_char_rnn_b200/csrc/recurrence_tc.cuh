@@ -194,8 +194,9 @@ __device__ __forceinline__ RtSmem rt_carve(uint8_t* smem_raw, size_t wsa_bytes, 
     return s;
 }
 
-inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats, int ring_bytes = RT_RING_BYTES) {
-    return wsa_bytes + wsb_bytes + ring_bytes + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024 + 2048;
+// (alignment slack + barriers and TMEM slot + the debug stamps, which sit last and exist only in debug runs)
+inline size_t rt_smem_bytes(size_t wsa_bytes, size_t wsb_bytes, int zs_floats, int ring_bytes = RT_RING_BYTES, int dbg = 1) {
+    return wsa_bytes + wsb_bytes + ring_bytes + (size_t)((zs_floats + 3) & ~3) * 4 + 1024 + 1024 + (dbg ? 2048 : 0);
 }
 
 // Role-private pipeline state.
@@ -355,8 +356,15 @@ __device__ __forceinline__ void rt_fill_sentinel(__nv_bfloat16* __restrict__ dst
 // `arow`: first row of the A tile in the 2-D tensor view; `wbase`: resident weight region.
 __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUtensorMap* tmA, int arow, int nkb, int box_rows,
                                            int ckb, int nst, int use3d, int kb_ofs = 0,
-                                           const CUtensorMap* tmAlo = nullptr, int rot = 0, long long* stamps = nullptr) {
+                                           const CUtensorMap* tmAlo = nullptr, int rot = 0, long long* stamps = nullptr,
+                                           const void* lin = nullptr, const void* lin_lo = nullptr) {
     const int tile = rt_tile_bytes(box_rows);
+    // lin != nullptr (CRNN_TC_EXPT=64, timing only - the rows land unswizzled, results are wrong): the same number of bytes
+    // as ONE linear bulk copy per operand half instead of a tensor-map load
+    auto bulk1d = [&](void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+    };
     if (tmAlo) {                                       // split operands: hi tiles then lo tiles, one barrier per stage
         const int stage = 2 * ckb * tile;
         for (int kb = 0; kb < nkb; kb += ckb, p.advance(nst)) {
@@ -367,7 +375,10 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
             uint8_t* hi = s.ring + st * stage;
             uint8_t* lo = hi + ckb * tile;
             const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;      // rotated start (rot is a multiple of ckb)
-            if (use3d) {
+            if (lin && use3d) {
+                bulk1d(hi, lin, (uint32_t)box_rows * 128u * (uint32_t)ckb, &s.a_full[st]);
+                bulk1d(lo, lin_lo, (uint32_t)box_rows * 128u * (uint32_t)ckb, &s.a_full[st]);
+            } else if (use3d) {
                 tma_load_3d(hi, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
                 tma_load_3d(lo, tmAlo, &s.a_full[st], 0, arow, kb_ofs + kbr);
             } else {
@@ -387,7 +398,9 @@ __device__ __forceinline__ void rt_produce(const RtSmem& s, RtPipe& p, const CUt
         const uint32_t bytes = (uint32_t)box_rows * 128u * (uint32_t)(use3d ? ckb : n);
         mbar_expect_tx(&s.a_full[st], bytes);
         const int kbr = kb + rot >= nkb ? kb + rot - nkb : kb + rot;
-        if (use3d) {                                   // whole stage in one instruction (out-of-range k-blocks read zero)
+        if (lin && use3d) {
+            bulk1d(s.ring + st * ckb * tile, lin, bytes, &s.a_full[st]);
+        } else if (use3d) {                            // whole stage in one instruction (out-of-range k-blocks read zero)
             tma_load_3d(s.ring + st * ckb * tile, tmA, &s.a_full[st], 0, arow, kb_ofs + kbr);
             if (stamps && kb <= ckb) stamps[kb == 0 ? 20 : 22] = clock64();
         } else {
@@ -774,7 +787,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         if (a.sub && !a.gather && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
                         rt_produce(s, p, ph == 0 ? &tmH : &tmRS, t * B + b0 + ps * PR, nkb, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb,
                                    a.split ? (ph == 0 ? &tmHl : &tmRSl) : nullptr, rot,
-                                   (!a.gather && dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
+                                   (!a.gather && dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr,
+                                   (a.expt & 64) ? a.hxb + ((int64_t)t * B + b0 + ps * PR) * H : nullptr,
+                                   (a.expt & 64) ? a.hxb + a.hxb_lo + ((int64_t)t * B + b0 + ps * PR) * H : nullptr);
                     }
                 }
                 if (lane == 0) RT_STAMP(2);
@@ -1066,7 +1081,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     if (lane == 0) {
                         if (a.sub && !a.gather && phases_done > 0) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
                         rt_produce(s, p, &tmZ0, (t + 1) * B + b0 + ps * PR, nkb0, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb0,
-                                   a.split ? &tmZ0l : nullptr, rot0);
+                                   a.split ? &tmZ0l : nullptr, rot0, nullptr,
+                                   (a.expt & 64) ? a.dzb + ((int64_t)t * B + b0 + ps * PR) * zw : nullptr,
+                                   (a.expt & 64) ? a.dzb + a.dzb_lo + ((int64_t)t * B + b0 + ps * PR) * zw : nullptr);
                     }
                 }
             }
@@ -1078,7 +1095,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     if (lane == 0) {
                         if (a.sub && !a.gather) rt_await(a.barrier + tile * a.npass + ps, phases_done * a.nslices, a.acq_poll);
                         rt_produce(s, p, &tmZ1, t * B + b0 + ps * PR, nkb1, a.box_rows, a.ckb, a.nst, a.use3d, kq * nkb1,
-                                   a.split ? &tmZ1l : nullptr, rot1);
+                                   a.split ? &tmZ1l : nullptr, rot1, nullptr,
+                                   (a.expt & 64) ? a.dzb + ((int64_t)t * B + b0 + ps * PR) * zw : nullptr,
+                                   (a.expt & 64) ? a.dzb + a.dzb_lo + ((int64_t)t * B + b0 + ps * PR) * zw : nullptr);
                     }
                 }
                 ++phases_done;
