@@ -61,6 +61,7 @@ struct RecPlanTc {
     int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
     int q_fwd, q_bwd;       // K parts per unit group (cluster size) of the forward / backward kernel
     int ring_fwd, ring_bwd; // TMA ring bytes
+    int cx;                 // cluster exchange: all slices of a tile in one cluster, rows delivered through distributed shared memory
     int pr, sub;            // rows per pass; 1: the passes of a tile are independent chains (RecTcArgs::sub)
     int gather;             // 1: direct exchange of the streamed rows (recurrence_tc.cuh: rt_gather) instead of TMA loads behind a step barrier
     int g_rp_log2, g_ckb_log2;
@@ -352,6 +353,25 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
                 grow2(&o->smem_bwd, &o->ring_bwd);
             }
         }
+        // Cluster exchange (recurrence_tc.cuh: cx_push / rt_mma_cx): when ALL slices of a tile fit a portable cluster, the rows
+        // a slice finishes are written straight into every slice's operand buffers (distributed shared memory) and nothing of
+        // the step hand-shake goes through L2.  Needs the phase's whole K extent per buffer: two buffers forward, two (gru:
+        // two + one) backward.  (tools/ubench_dsmem.cu: pays for clusters of <= 8 with a few KB per slice; at config 3's
+        // geometry - 16 slices x 4 KB - the exchange through L2 is faster, and its weights leave no room for the buffers.)
+        o->cx = 0;
+        if (env_int("CRNN_TC_CX", 1) && (nslices == 2 || nslices == 4 || nslices == 8) && nslices <= std::min(8, h->env.cbar) &&
+            o->npass == 1 && !o->sub && !o->gather && o->q_fwd == 1 && o->q_bwd == 1 && !o->swap_fwd && !o->swap_bwd) {
+            const int tile = tc::rt_tile_bytes(o->box_rows), nsp = 1 + h->split;
+            const int nkbg = ceil_div(g1 * H, 64);
+            const int need_f = (2 * nsp * nkb * tile + tc::RT_MROWS_BYTES - tile + 1023) & ~1023;
+            const int need_b = ((2 * nkbg + (model == CRNN_MODEL_GRU ? nkb : 0)) * nsp * tile + tc::RT_MROWS_BYTES - tile + 1023) & ~1023;
+            const int add_f = std::max(0, need_f - o->ring_fwd), add_b = std::max(0, need_b - o->ring_bwd);
+            if ((int)o->smem_fwd + add_f <= h->max_smem && (int)o->smem_bwd + add_b <= h->max_smem) {
+                o->cx = 1;
+                o->ring_fwd += add_f; o->smem_fwd += (size_t)add_f;
+                o->ring_bwd += add_b; o->smem_bwd += (size_t)add_b;
+            }
+        }
         return true;
     };
     // Largest slice that fits (fewest slices -> least L2 traffic for the h all-gather), shrunk
@@ -579,7 +599,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     if (env_int("CRNN_VERBOSE", 0) && h->tc)
         fprintf(stderr, "[crnn] plan: HC %d BT %d slices %d tiles %d passes %d x %d rows%s, K split fwd/bwd %d/%d, ring %d/%d KB, smem %zu/%zu, "
                 "wavefront %d layers x %d chunks, workspace %.1f MB\n", h->tcp.HC, h->tcp.BT, h->tcp.nslices, h->tcp.ntiles, h->tcp.npass, h->tcp.pr,
-                h->tcp.sub ? " (sub-chains)" : "", h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
+                h->tcp.sub ? " (sub-chains)" : (h->tcp.cx ? " (cluster exchange)" : ""), h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
                 h->tcp.smem_bwd, h->wf_W, h->wf_C, h->ws.total / 1e6);
     *out = h;
     return CRNN_OK;
@@ -886,7 +906,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.err = h->err_word;
     if (a.gather) a.ckb = 1 << p.g_ckb_log2;
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb, split, a.ring_bytes);
-    a.use3d = (H % 64 == 0 && h->env.use3d) ? 1 : 0;
+    a.use3d = (H % 64 == 0 && h->env.use3d && !p.cx) ? 1 : 0;      // (cluster exchange: the map only serves the launch's first load, K block by K block)
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
         if (a.use3d) return tc::make_tmap_bf16_kblocks(m, base, rows, cols, ld, p.box_rows, a.ckb);
         return tc::make_tmap_bf16(m, base, rows, cols, ld, p.box_rows);
@@ -927,7 +947,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.expt = h->env.expt;
     // K-split launches read their partial sums from distributed shared memory; there consecutive lanes on consecutive
     // units (scalar epilogue) beat quads (config 4 BPTT 5.4 vs 6.6 ms, split-precision config 3 BPTT 2.9 vs 3.6 ms)
-    const bool vec4 = (h->env.vec4 >= 0 ? h->env.vec4 : (Q > 1 ? 0 : 1)) != 0;
+    const bool vec4 = p.cx || (h->env.vec4 >= 0 ? h->env.vec4 : (Q > 1 ? 0 : 1)) != 0;   // (the cluster exchange pushes quads)
     typedef void (*RecFn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs);
     RecFn fn;
 #define CRNN_PICK(KERNEL, F)                                                                                   \
@@ -960,6 +980,8 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         a.cbar = 1;
     }
     if (Q > 1) { csize = Q; a.cbar = 0; }     // the cluster is the K-split group
+    a.xchg = 0;
+    if (p.cx && Q == 1) { a.xchg = 1; a.cbar = 0; csize = p.nslices; }   // cluster exchange: the rows themselves travel inside the cluster
     if (csize > 8) CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     a.csize = csize;
     void* args[] = {&t0, &t1, &w0, &w1, &t0l, &t1l, &w0l, &w1l, &a};
@@ -977,7 +999,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
         attrs[0].val.clusterDim.x = (unsigned)csize; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
         attrs[1].id = cudaLaunchAttributeCooperative;           // all clusters co-resident: tiles span several clusters
         attrs[1].val.cooperative = 1;
-        cfgl.attrs = attrs; cfgl.numAttrs = a.cbar ? 1 : 2;     // cluster barrier: clusters are independent
+        cfgl.attrs = attrs; cfgl.numAttrs = (a.cbar || a.xchg) ? 1 : 2;     // cluster barrier / exchange: clusters are independent
         CRNN_CUDA(cudaLaunchKernelExC(&cfgl, (const void*)fn, args));
     }
     prof_kernel_mark(h, st, backward ? 1 : 0);

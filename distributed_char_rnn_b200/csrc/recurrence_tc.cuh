@@ -70,6 +70,8 @@ struct RecTcArgs {
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
     int ksplit;                 // Q: the contraction index is split over Q CTAs of a cluster; each contracts the columns of Q*HC
                                 // units over 1/Q of K and the partial sums are exchanged through distributed shared memory
+    int xchg;                   // 1: cluster exchange - the cluster holds ALL slices of a batch tile and every slice writes the bf16 rows it
+                                // finishes straight into the operand buffers of all slices (distributed shared memory), see cx_push
     int cbar;                   // 1: the cluster holds ALL slices of a batch tile: steps are ordered by remote mbarrier arrives, no global counter
     int csize;                  // CTAs per cluster along the slice index (1: no cluster): the K-split group or the slices of one batch tile (cbar)
     int m64;                    // 1: tiles of <= 64 batch rows use M=64 MMAs (half the A-operand read); rows 16i..16i+15 -> TMEM lanes 32i..32i+15
@@ -121,6 +123,50 @@ __device__ __forceinline__ float tanh_ex2(float x) { return 1.0f - __fdividef(2.
 #define fast_sigmoid(x) (FAST ? fmaf(0.5f, tanh_mufu(0.5f * (x)), 0.5f) : sigmoid_ex2(x))
 
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(RT_EPI_THREADS) : "memory"); }
+
+// ---- cluster exchange (RecTcArgs::xchg) ------------------------------------------------------------------------------
+// When all slices of a batch tile sit in ONE cluster (<= 8 CTAs: small hidden sizes, the reference's default 128 among
+// them), the rows a slice finishes do not go through L2 at all: the epilogue threads write them, already in the K-major
+// 128-byte-swizzled operand layout, into the operand buffer of EVERY slice of the cluster with st.async, whose bytes
+// complete the transaction count of the buffer's mbarrier in the receiving CTA, on which that CTA's MMA warp sleeps.
+// No store to global memory, no MEMBAR.GPU, no flag in L2, no poll, no TMA load - not even a fence or an arrive of the
+// writer - are left on the chain.  Buffers are double-buffered by step (or by phase for the GRU), which the data dependencies make safe
+// without an "empty" hand-shake: a slice can only produce rows for use k+1 of a buffer after every peer's MMAs of use k
+// have completed (it needed their results).  Measured (tools/ubench_dsmem.cu, B200): an all-to-all of 8 x 2 KB inside a
+// cluster takes 1.4 k cycles against 3.0-3.8 k for store + release + acquire poll + bulk load through L2; at 16 x 4 KB
+// (config 3's geometry) the cluster network (~16 B/cycle/SM in) loses to L2: 4.3 k against 3.5 k.
+constexpr int RT_CX_MAX = 8;
+__device__ __forceinline__ void st_dsmem_v2(uint32_t cluster_addr, uint32_t x, uint32_t y) {
+    asm volatile("st.shared::cluster.v2.b32 [%0], {%1, %2};" ::"r"(cluster_addr), "r"(x), "r"(y) : "memory");
+}
+// 8 bytes into a peer's shared memory; their arrival is counted (complete_tx) on the peer's mbarrier `cluster_bar`
+__device__ __forceinline__ void st_async_v2(uint32_t cluster_addr, uint32_t x, uint32_t y, uint32_t cluster_bar) {
+    asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];"
+                 ::"r"(cluster_addr), "r"(x), "r"(y), "r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cnt(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+// Four values v[] = K indices kcol .. kcol+3 of row r of the operand buffer at byte offset buf_ofs of every peer's ring
+// (pbase[p] = the ring's address in CTA p's window, pbar[p] = the buffer's barrier there).  Buffer layout: nkb tiles of
+// [box rows][128 B] (K block kb = kcol / 64, 16-byte chunk c of a row stored at chunk c ^ (r % 8)), the lo tiles lo_ofs bytes
+// after the hi tiles (0: not split).  st.async: the bytes count themselves on the receiver's barrier when they land, so the
+// writer needs no fence and no arrive, and the receiver only states how many bytes a complete buffer is (rt_mma_cx).
+__device__ __forceinline__ void cx_push(const uint32_t (&pbase)[RT_CX_MAX], const uint32_t (&pbar)[RT_CX_MAX], int csize, int bidx,
+                                        uint32_t buf_ofs, uint32_t lo_ofs, int tile, int r, int kcol, const float* v) {
+    const uint32_t byte = (uint32_t)(kcol & 63) * 2u;
+    const uint32_t off = buf_ofs + (uint32_t)(kcol >> 6) * (uint32_t)tile + (uint32_t)r * 128u + ((((byte >> 4) ^ (uint32_t)r) & 7u) << 4) + (byte & 15u);
+    const __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+    const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+    const __nv_bfloat162 l0 = __floats2bfloat162_rn(v[0] - f0.x, v[1] - f0.y), l1 = __floats2bfloat162_rn(v[2] - f1.x, v[3] - f1.y);
+#pragma unroll
+    for (int p = 0; p < RT_CX_MAX; ++p)
+        if (p < csize) {
+            const uint32_t bar = pbar[p] + 8u * (uint32_t)bidx;
+            st_async_v2(pbase[p] + off, *reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1), bar);
+            if (lo_ofs) st_async_v2(pbase[p] + off + lo_ofs, *reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1), bar);
+        }
+}
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -489,6 +535,53 @@ __device__ __forceinline__ void rt_mma(const RtSmem& s, RtPipe& p, uint32_t tmem
     ++p.z_i;
 }
 
+// Cluster exchange: the phase's whole streamed operand sits in one buffer `abuf` ([hi: nkb tiles][lo: nkb tiles], written by
+// the slices of the cluster, see cx_push) whose barrier `full` completes when every slice has delivered its rows.
+// Batch rows on M only.  Executed by all lanes of the MMA warp like rt_mma.
+__device__ __forceinline__ void rt_mma_cx(const RtSmem& s, RtPipe& p, uint32_t tmem, const uint8_t* wbase, int nc, int nkb,
+                                          const uint8_t* abuf, int tile, uint64_t* full, uint32_t parity, uint32_t expect_bytes,
+                                          int m64, int split, long long* stamps = nullptr) {
+    const bool lane0 = (threadIdx.x & 31) == 0;
+    if (lane0) mbar_expect_tx(full, expect_bytes);  // the buffer's one arrival; the bytes come from the slices (or the launch's first TMA load)
+    mbar_wait(s.z_empty, (p.z_i & 1) ^ 1);          // epilogue has drained the previous accumulator
+    if (stamps && lane0) stamps[10] = clock64();
+    mbar_wait_cluster(full, parity);                // acquire.cluster: the peers' rows have landed
+    if (stamps && lane0) stamps[11] = clock64();
+    fence_proxy_async();                            // (rows written by st.async -> read by the tensor core)
+    tc_fence_after();
+    if (stamps && lane0) stamps[12] = clock64();
+    const uint32_t idesc = idesc_bf16(m64 ? 64 : 128, nc, 0, 0);
+    const uint64_t a_lo = (uint64_t)(((uint32_t)nkb * (uint32_t)tile) >> 4);
+    uint64_t da = desc_kmajor(smem_u32(abuf));
+    const uint64_t da_step = (uint64_t)(tile >> 4);
+    if (elect_one()) {
+        if (split) {                                 // see rt_mma: [hi rows ; lo rows] per K block of the weights
+            const uint32_t idesc2 = idesc_bf16(m64 ? 64 : 128, 2 * nc, 0, 0);
+            uint64_t db = desc_kmajor(smem_u32(wbase));
+            const uint64_t db_step = (uint64_t)((2 * nc * 128) >> 4);
+            for (int j = 0; j < nkb; ++j, da += da_step, db += db_step) {
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + k, db + k, idesc2, (uint32_t)((j + k) != 0));
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) mma_bf16(tmem, da + a_lo + k, db + k, idesc, 1u);
+            }
+        } else {
+            uint64_t db = desc_kmajor(smem_u32(wbase));
+            const uint64_t db_step = (uint64_t)((nc * 128) >> 4);
+            for (int j = 0; j < nkb; ++j, da += da_step, db += db_step) {
+                mma_bf16(tmem, da, db, idesc, (uint32_t)(j != 0));
+                mma_bf16(tmem, da + 2, db + 2, idesc, 1u);
+                mma_bf16(tmem, da + 4, db + 4, idesc, 1u);
+                mma_bf16(tmem, da + 6, db + 6, idesc, 1u);
+            }
+        }
+        mma_commit(s.z_full);
+    }
+    __syncwarp();
+    if (stamps && lane0) stamps[3] = clock64();
+    ++p.z_i;
+}
+
 // Grid barrier, split: epilogue threads publish, the TMA producer waits before touching
 // rows written by other CTAs (generic-proxy writes -> async-proxy reads need the proxy fence).
 __device__ __forceinline__ void rt_publish(unsigned* counter, int epi_tid, int synced = 0) {
@@ -735,7 +828,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmH); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); mbar_init(&s.a_valid[i], RT_EPI_WARPS); }
+        // (cluster exchange: a_valid[b] is the barrier of operand buffer b: one arrival - the MMA warp's expect_tx - plus the bytes)
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); mbar_init(&s.a_valid[i], a.xchg ? 1u : (uint32_t)RT_EPI_WARPS); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
@@ -744,7 +838,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s.tmem_slot;
-    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive
+    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist (and its ring is zeroed) before any remote arrive / store
+    // cluster exchange: two operand buffers in the ring - lstm / rnn: h_{t-1} in buffer t % 2; gru: h_{t-1} in 0, r*h in 1
+    const int cx_tile = rt_tile_bytes(a.box_rows);
+    const uint32_t cx_buf = (uint32_t)(nsp * nkb * cx_tile);
     int dbg_slot = -1;
     if (a.dbg) dbg_slot = blockIdx.x == 0 ? 0 : blockIdx.x == 1 ? 1 : blockIdx.x == gridDim.x / 2 ? 2 : blockIdx.x == gridDim.x - 1 ? 3 : -1;
     long long* dbgs = dbg_slot >= 0 ? s.dbg : nullptr;
@@ -768,6 +865,18 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         tma_load_2d(s.wsb + (size_t)wblk * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb + kb) * 64, grp * GW * HCG + NCA);
                 }
         }
+        if (a.xchg) {
+            // Only the launch's first contraction reads rows from global memory (an earlier launch or the host left them
+            // there); every later one finds its rows in shared memory, delivered by the slices of the cluster.
+            if (lane == 0) {
+                const int bidx = MODEL == CRNN_MODEL_GRU ? 0 : (a.t_begin & 1);
+                uint8_t* dst = s.ring + (size_t)bidx * cx_buf;      // (the MMA warp expects these bytes on the buffer's barrier)
+                for (int kb = 0; kb < nkb; ++kb) {
+                    tma_load_2d(dst + (size_t)kb * cx_tile, &tmH, &s.a_valid[bidx], kb * 64, a.t_begin * B + b0);
+                    if (a.split) tma_load_2d(dst + (size_t)(nkb + kb) * cx_tile, &tmHl, &s.a_valid[bidx], kb * 64, a.t_begin * B + b0);
+                }
+            }
+        } else
         for (int t = a.t_begin; t < a.t_end; ++t) {
             for (int ph = 0; ph < nphase; ++ph) {
                 const int dbg_phase = (int)phases_done;
@@ -800,6 +909,21 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         {   // the whole warp runs the issue loop (see mma_bf16_elect)
             const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
             mbar_wait(s.w_bar, 0);
+            if (a.xchg) {
+                uint32_t uses[2] = {0u, 0u};
+                for (int t = a.t_begin; t < a.t_end; ++t)
+                    for (int ph = 0; ph < nphase; ++ph) {
+                        const int bidx = MODEL == CRNN_MODEL_GRU ? ph : (t & 1);
+                        const int dbg_phase = (t - a.t_begin) * nphase + ph;
+                        // bytes of a complete buffer: the launch's first one is TMA boxes, the others bt rows x H units from the slices
+                        const uint32_t nbytes = (t == a.t_begin && ph == 0) ? (uint32_t)a.box_rows * 128u * (uint32_t)(nkb * nsp)
+                                                                            : (uint32_t)(nsp * bt) * (uint32_t)H * 2u;
+                        rt_mma_cx(s, p, tmem_u, ph == 0 ? s.wsa : s.wsb, ph == 0 ? NCA : HCG, nkb, s.ring + (size_t)bidx * cx_buf, cx_tile,
+                                  &s.a_valid[bidx], uses[bidx] & 1u, nbytes, a.m64, a.split,
+                                  (dbgs && dbg_phase >= 20 && dbg_phase < 28) ? dbgs + (dbg_phase - 20) * 24 : nullptr);
+                        ++uses[bidx];
+                    }
+            } else
             for (int t = a.t_begin; t < a.t_end; ++t)
                 for (int ph = 0; ph < nphase; ++ph) {
                     const int dbg_phase = (t - a.t_begin) * nphase + ph;
@@ -815,6 +939,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         const int epi_tid = (warp - 2) * 32 + lane;
         uint32_t zpeer[4] = {0, 0, 0, 0};            // the peers' accumulator staging areas (distributed shared memory)
         if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
+        uint32_t pbase[RT_CX_MAX];                    // cluster exchange: every slice's ring
+#pragma unroll
+        for (int r = 0; r < RT_CX_MAX; ++r) pbase[r] = (a.xchg && r < a.csize) ? dsmem_addr(s.ring, (uint32_t)r) : 0u;
+        uint32_t pbar[RT_CX_MAX];                     // ... and its operand-buffer barriers
+#pragma unroll
+        for (int r = 0; r < RT_CX_MAX; ++r) pbar[r] = (a.xchg && r < a.csize) ? dsmem_addr(s.a_valid, (uint32_t)r) : 0u;
         if (a.gather) {
             // the slots this CTA writes in the NEXT launch of the layer's chain (visible there by the kernel boundary)
             for (int t = a.fill_t0; t < a.fill_t1; ++t) {
@@ -922,13 +1052,21 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                 hv[u] = fmaf(x1[u], ax[u] - x0[u], x0[u]);                // u*h + (1-u)*cand
                             }
                         }
+                        if (dbgs && epi_tid == 0 && base == 0) { asm volatile("" ::"f"(hv[0]), "f"(hv[UB - 1])); RT_STAMP(21); }   // cell math done
                         // the rows other CTAs stream in the next phase
+                        const bool to_rs = MODEL == CRNN_MODEL_GRU && ph == 0;
+                        // (cluster exchange: h of the launch's last step is read from global memory by the next launch)
+                        const bool cx_send = a.xchg && (to_rs || t + 1 < a.t_end);
+                        const int cx_b = to_rs ? 1 : (MODEL == CRNN_MODEL_GRU ? 0 : ((t + 1) & 1));
+                        const uint32_t cx_dst = (uint32_t)cx_b * cx_buf;
 #pragma unroll
                         for (int qd = 0; qd < UB / VEC; ++qd) {
-                            if (!e[qd].ok || (a.expt & 1)) continue;
+                            if (!e[qd].ok || ((a.expt & 1) && !a.xchg)) continue;
                             const int o = e[qd].r * H + e[qd].jj;
-                            if (MODEL == CRNN_MODEL_GRU && ph == 0) stv_bf16_split<VEC>(rs_ + o, a.rsb_lo, hv + VEC * qd);
-                            else                                    stv_bf16_split<VEC>(hb_ + o, a.hxb_lo, hv + VEC * qd);
+                            if (a.xchg) {
+                                if (cx_send && VEC == 4) cx_push(pbase, pbar, a.csize, cx_b, cx_dst, a.split ? (uint32_t)(nkb * cx_tile) : 0u, cx_tile, e[qd].r, j0 + e[qd].jj, hv + VEC * qd);
+                            } else if (to_rs) stv_bf16_split<VEC>(rs_ + o, a.rsb_lo, hv + VEC * qd);
+                            else              stv_bf16_split<VEC>(hb_ + o, a.hxb_lo, hv + VEC * qd);
                         }
                         pending = defer;
                         if (!defer) {
@@ -937,6 +1075,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                                 if (!e[qd].ok) continue;
                                 float* g = gp + e[qd].r * (int)gw + e[qd].jj;
                                 const int o = e[qd].r * H + e[qd].jj;
+                                if (a.xchg) {          // the global copies (GEMM operands, the next launch): nobody in this launch waits for them
+                                    if (to_rs) stv_bf16_split<VEC>(rs_ + o, a.rsb_lo, hv + VEC * qd);
+                                    else       stv_bf16_split<VEC>(hb_ + o, a.hxb_lo, hv + VEC * qd);
+                                }
                                 if (MODEL == CRNN_MODEL_LSTM) {
                                     stv<VEC>(hn_ + o, hv + VEC * qd);
                                     stv<VEC>(cn_ + o, ax + VEC * qd);
@@ -959,7 +1101,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                     // ---- the pass (sub-chains) or the whole phase is done on this CTA: release it, then the deferred stores
                 const int dbg_phase = (t - a.t_begin) * nphase + ph;
                 if (epi_tid == 0) RT_STAMP(6);
-                if (a.gather) { /* the stored rows are their own signal */ }
+                if (a.xchg) { /* the pushed rows count themselves on the receivers' barriers */ }
+                else if (a.gather) { /* the stored rows are their own signal */ }
                 else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize);
                 else rt_publish(a.sub ? a.barrier + tile * a.npass + ps : a.barrier + tile, epi_tid, a.sub);
                 if (epi_tid == 0) RT_STAMP(7);
@@ -971,6 +1114,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                         if (!e[qd].ok) continue;
                         float* g = gt + (tB + b0row) * gw + j0 + e[qd].r * (int)gw + e[qd].jj;
                         const int64_t o = ob + e[qd].r * H + e[qd].jj;
+                        if (a.xchg) {
+                            if (MODEL == CRNN_MODEL_GRU && ph == 0) stv_bf16_split<VEC>(a.rsb + tB * H + o, a.rsb_lo, hv + VEC * qd);
+                            else                                    stv_bf16_split<VEC>(hnb + o, a.hxb_lo, hv + VEC * qd);
+                        }
                         if (MODEL == CRNN_MODEL_LSTM) {
                             stv<VEC>(hnext + o, hv + VEC * qd);
                             stv<VEC>(a.cx + (int64_t)(t + 1) * BH + o, ax + VEC * qd);
@@ -1041,7 +1188,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     fence_proxy_async();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmZ0); tma_prefetch_desc(&tmW0);
-        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); mbar_init(&s.a_valid[i], RT_EPI_WARPS); }
+        // (cluster exchange: a_valid[0..1] are the barriers of the two dz_{t+1} buffers - the gru delivers them in two waves,
+        //  du in the first phase of step t+1 and dr in its second -, a_valid[2] the gru's candidate-column buffer)
+        for (int i = 0; i < RT_MAX_STAGES; ++i) { mbar_init(&s.a_full[i], 1); mbar_init(&s.a_empty[i], 1); mbar_init(&s.a_valid[i], a.xchg ? 1u : (uint32_t)RT_EPI_WARPS); }
         mbar_init(s.z_full, 1); mbar_init(s.z_empty, RT_EPI_THREADS); mbar_init(s.w_bar, 1); mbar_init(s.step_bar, (uint32_t)a.nslices); mbar_init(s.zs_ready, (uint32_t)a.ksplit); mbar_init(s.zs_free, (uint32_t)a.ksplit);
         fence_barrier_init();
     }
@@ -1050,7 +1199,10 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s.tmem_slot;
-    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist before any remote arrive
+    if (a.csize > 1) cluster_sync_all();             // every CTA's barriers exist (and its ring is zeroed) before any remote arrive / store
+    // cluster exchange: dz_{t+1} (gate columns [0, G1*H)) in buffer t % 2 of two; gru: this step's candidate columns in a third
+    const int cx_tile = rt_tile_bytes(a.box_rows);
+    const uint32_t cx_buf0 = (uint32_t)(nsp * nkb0 * cx_tile), cx_buf1 = (uint32_t)(nsp * nkb1 * cx_tile);
 
     RtPipe p{0, 0, 0, 0};
     unsigned phases_done = 0;
@@ -1071,6 +1223,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                         tma_load_2d(s.wsb + (size_t)(il ? kb * 2 + half : half * nkb1 + kb) * HCG * 128, half ? &tmW1l : &tmW1, s.w_bar, (kq * nkb1 + kb) * 64, H + jg0);
             }
         }
+        if (a.xchg) {
+            // only the launch's first contraction reads dz_{t+1} from global memory (the previous launch wrote it)
+            const int t = a.t_end - 1;
+            if (lane == 0 && t + 1 < a.S) {
+                uint8_t* dst = s.ring + (size_t)(t & 1) * cx_buf0;      // (the MMA warp expects these bytes on the buffer's barrier)
+                for (int kb = 0; kb < nkb0; ++kb) {
+                    tma_load_2d(dst + (size_t)kb * cx_tile, &tmZ0, &s.a_valid[t & 1], kb * 64, (t + 1) * B + b0);
+                    if (a.split) tma_load_2d(dst + (size_t)(nkb0 + kb) * cx_tile, &tmZ0l, &s.a_valid[t & 1], kb * 64, (t + 1) * B + b0);
+                }
+            }
+        } else
         for (int t = a.t_end - 1; t >= a.t_begin; --t) {
             // contraction 0 reads dz_{t+1} (all CTAs, previous step; at a chunk boundary: previous launch)
             if (t + 1 < a.S) {
@@ -1107,6 +1270,22 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         {   // the whole warp runs the issue loop (see mma_bf16_elect)
             const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
             mbar_wait(s.w_bar, 0);
+            if (a.xchg) {
+                uint32_t uses[3] = {0u, 0u, 0u};
+                for (int t = a.t_end - 1; t >= a.t_begin; --t) {
+                    if (t + 1 < a.S) {
+                        const uint32_t nbytes = t == a.t_end - 1 ? (uint32_t)a.box_rows * 128u * (uint32_t)(nkb0 * nsp)      // TMA boxes
+                                                                 : (uint32_t)(nsp * bt) * (uint32_t)(G1 * H) * 2u;           // bt rows x G1*H gate columns
+                        rt_mma_cx(s, p, tmem_u, s.wsa, HCG, nkb0, s.ring + (size_t)(t & 1) * cx_buf0, cx_tile, &s.a_valid[t & 1], uses[t & 1] & 1u, nbytes, a.m64, a.split);
+                        ++uses[t & 1];
+                    }
+                    if (MODEL == CRNN_MODEL_GRU) {
+                        rt_mma_cx(s, p, tmem_u, s.wsb, HCG, nkb1, s.ring + 2 * (size_t)cx_buf0, cx_tile, &s.a_valid[2], uses[2] & 1u,
+                                  (uint32_t)(nsp * bt) * (uint32_t)H * 2u, a.m64, a.split);
+                        ++uses[2];
+                    }
+                }
+            } else
             for (int t = a.t_end - 1; t >= a.t_begin; --t) {
                 if (t + 1 < a.S)
                     for (int ps = 0; ps < a.npass; ++ps) rt_mma(s, p, tmem_u, s.wsa, HCG, nkb0, a.swap, (min(PR, bt - ps * PR) + 15) & ~15, a.box_rows, a.ckb, a.nst, a.m64, nullptr, a.split, rot0, a.gather, a.expt & 32);
@@ -1120,6 +1299,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
         const int epi_tid = (warp - 2) * 32 + lane;
         uint32_t zpeer[4] = {0, 0, 0, 0};
         if (Q > 1) for (int r = 0; r < Q; ++r) zpeer[r] = dsmem_addr(Zs, (uint32_t)r);
+        uint32_t pbase[RT_CX_MAX];                    // cluster exchange: every slice's ring
+#pragma unroll
+        for (int r = 0; r < RT_CX_MAX; ++r) pbase[r] = (a.xchg && r < a.csize) ? dsmem_addr(s.ring, (uint32_t)r) : 0u;
+        uint32_t pbar[RT_CX_MAX];                     // ... and its operand-buffer barriers
+#pragma unroll
+        for (int r = 0; r < RT_CX_MAX; ++r) pbar[r] = (a.xchg && r < a.csize) ? dsmem_addr(s.a_valid, (uint32_t)r) : 0u;
+        const uint32_t cx_lo0 = a.split ? (uint32_t)(nkb0 * cx_tile) : 0u, cx_lo1 = a.split ? (uint32_t)(nkb1 * cx_tile) : 0u;
         if (a.gather) {
             // the dz slots this CTA writes in the NEXT (earlier) launch of the layer's chain
             for (int t = a.fill_t0; t < a.fill_t1; ++t)
@@ -1207,11 +1393,29 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                             v4[u] = dht;
                         }
                     }
+                    // (cluster exchange: dz of the launch's first step t_begin is read from global memory by the next launch)
+                    const bool cx_next = a.xchg && t > a.t_begin;
+                    const uint32_t cx_r = (uint32_t)((t - 1) & 1) * cx_buf0;      // dz_t is the operand of step t-1
 #pragma unroll
                     for (int qd = 0; qd < UB / VEC; ++qd) {
                         if (!e[qd].ok) continue;
                         __nv_bfloat16* dzb = dzbp + e[qd].r * (int)zw + e[qd].jj;
-                        if (MODEL == CRNN_MODEL_LSTM) {
+                        const int kc = j0 + e[qd].jj;
+                        if (a.xchg && VEC == 4) {
+                            if (MODEL == CRNN_MODEL_LSTM) {
+                                if (cx_next) {
+                                    cx_push(pbase, pbar, a.csize, (t - 1) & 1, cx_r, cx_lo0, cx_tile, e[qd].r, kc, v0 + VEC * qd);
+                                    cx_push(pbase, pbar, a.csize, (t - 1) & 1, cx_r, cx_lo0, cx_tile, e[qd].r, H + kc, v1 + VEC * qd);
+                                    cx_push(pbase, pbar, a.csize, (t - 1) & 1, cx_r, cx_lo0, cx_tile, e[qd].r, 2 * H + kc, v2 + VEC * qd);
+                                    cx_push(pbase, pbar, a.csize, (t - 1) & 1, cx_r, cx_lo0, cx_tile, e[qd].r, 3 * H + kc, v3 + VEC * qd);
+                                }
+                            } else if (MODEL == CRNN_MODEL_RNN) {
+                                if (cx_next) cx_push(pbase, pbar, a.csize, (t - 1) & 1, cx_r, cx_lo0, cx_tile, e[qd].r, kc, v0 + VEC * qd);
+                            } else {
+                                cx_push(pbase, pbar, a.csize, 2, 2u * cx_buf0, cx_lo1, cx_tile, e[qd].r, kc, v2 + VEC * qd);     // candidate: this step's second contraction
+                                if (cx_next) cx_push(pbase, pbar, a.csize, (t - 1) & 1, cx_r, cx_lo0, cx_tile, e[qd].r, H + kc, v1 + VEC * qd);
+                            }
+                        } else if (MODEL == CRNN_MODEL_LSTM) {
                             stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
                             stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + 3 * H, a.dzb_lo, v3 + VEC * qd);
                         } else if (MODEL == CRNN_MODEL_RNN) {
@@ -1227,6 +1431,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                             if (!e[qd].ok) continue;
                             float* dz = dzp + e[qd].r * (int)zw + e[qd].jj;
                             const int64_t o = ob + e[qd].r * H + e[qd].jj;
+                            if (a.xchg) {              // the global bf16 copies: GEMM operands and the next launch
+                                __nv_bfloat16* dzb = dzbp + e[qd].r * (int)zw + e[qd].jj;
+                                if (MODEL == CRNN_MODEL_LSTM) {
+                                    stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
+                                    stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + 3 * H, a.dzb_lo, v3 + VEC * qd);
+                                } else if (MODEL == CRNN_MODEL_RNN) {
+                                    stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd);
+                                } else {
+                                    stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
+                                }
+                            }
                             if (MODEL == CRNN_MODEL_LSTM) {
                                 stv<VEC>(a.carry0 + o, v4 + VEC * qd);
                                 stv<VEC>(dz, v0 + VEC * qd); stv<VEC>(dz + H, v1 + VEC * qd); stv<VEC>(dz + 2 * H, v2 + VEC * qd); stv<VEC>(dz + 3 * H, v3 + VEC * qd);
@@ -1243,7 +1458,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 if (has_next) RT_RELEASE_PARTIALS();
                 if (!a.sub && ps + 1 < a.npass) continue;
                 // ---- the pass (sub-chains) or the whole phase is done on this CTA: release it, then the deferred stores
-            if (a.gather) { /* the stored rows are their own signal */ }
+            if (a.xchg) { /* the pushed rows count themselves on the receivers' barriers */ }
+            else if (a.gather) { /* the stored rows are their own signal */ }
             else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize);
             else rt_publish(a.sub ? a.barrier + tile * a.npass + ps : a.barrier + tile, epi_tid, a.sub);
             if (pending) {
@@ -1255,6 +1471,17 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     if (!e[qd].ok) continue;
                     float* dz = dzp + e[qd].r * (int)zw + e[qd].jj;
                     const int64_t o = ob + e[qd].r * H + e[qd].jj;
+                    if (a.xchg) {
+                        __nv_bfloat16* dzb = a.dzb + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj;
+                        if (MODEL == CRNN_MODEL_LSTM) {
+                            stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
+                            stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + 3 * H, a.dzb_lo, v3 + VEC * qd);
+                        } else if (MODEL == CRNN_MODEL_RNN) {
+                            stv_bf16_split<VEC>(dzb, a.dzb_lo, v0 + VEC * qd);
+                        } else {
+                            stv_bf16_split<VEC>(dzb + 2 * H, a.dzb_lo, v2 + VEC * qd); stv_bf16_split<VEC>(dzb + H, a.dzb_lo, v1 + VEC * qd);
+                        }
+                    }
                     if (MODEL == CRNN_MODEL_LSTM) {
                         stv<VEC>(a.carry0 + o, v4 + VEC * qd);
                         stv<VEC>(dz, v0 + VEC * qd); stv<VEC>(dz + H, v1 + VEC * qd); stv<VEC>(dz + 2 * H, v2 + VEC * qd); stv<VEC>(dz + 3 * H, v3 + VEC * qd);
@@ -1308,13 +1535,16 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
 #pragma unroll
                         for (int qd = 0; qd < UB / VEC; ++qd) {
                             if (!e[qd].ok) continue;
-                            stv_bf16_split<VEC>(a.dzb + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, a.dzb_lo, v0 + VEC * qd);
+                            if (a.xchg && VEC == 4) {
+                                if (t > a.t_begin) cx_push(pbase, pbar, a.csize, (t - 1) & 1, (uint32_t)((t - 1) & 1) * cx_buf0, cx_lo0, cx_tile, e[qd].r, j0 + e[qd].jj, v0 + VEC * qd);
+                            } else stv_bf16_split<VEC>(a.dzb + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, a.dzb_lo, v0 + VEC * qd);
                         }
                         pending = defer;
                         if (!defer) {
 #pragma unroll
                             for (int qd = 0; qd < UB / VEC; ++qd) {
                                 if (!e[qd].ok) continue;
+                                if (a.xchg) stv_bf16_split<VEC>(a.dzb + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, a.dzb_lo, v0 + VEC * qd);
                                 stv<VEC>(a.dz + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, v0 + VEC * qd);
                                 stv<VEC>(a.carry0 + ob + e[qd].r * H + e[qd].jj, v4 + VEC * qd);
                             }
@@ -1323,7 +1553,8 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                     epi_bar_sync();
                     RT_RELEASE_PARTIALS();
                     if (!a.sub && ps + 1 < a.npass) continue;
-                if (a.gather) { }
+                if (a.xchg) { }
+                else if (a.gather) { }
                 else if (a.cbar) rt_publish_cluster(s.step_bar, epi_tid, a.csize);
                 else rt_publish(a.sub ? a.barrier + tile * a.npass + ps : a.barrier + tile, epi_tid, a.sub);
                 if (pending) {
@@ -1332,6 +1563,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
 #pragma unroll
                     for (int qd = 0; qd < UB / VEC; ++qd) {
                         if (!e[qd].ok) continue;
+                        if (a.xchg) stv_bf16_split<VEC>(a.dzb + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, a.dzb_lo, v0 + VEC * qd);
                         stv<VEC>(a.dz + (tB + b0row) * zw + j0 + e[qd].r * (int)zw + e[qd].jj, v0 + VEC * qd);
                         stv<VEC>(a.carry0 + ob + e[qd].r * H + e[qd].jj, v4 + VEC * qd);
                     }
