@@ -812,6 +812,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     const int nsp = 1 + a.split;                      // operand copies resident / streamed
     const RtSmem s = rt_carve(smem_raw, (size_t)nsp * nkb * NCA * 128, MODEL == CRNN_MODEL_GRU ? (size_t)nsp * nkb * HCG * 128 : 0, a.zs_floats, a.ring_bytes);
     float* Zs = s.zs;
+    // life-cycle stamps of CTA 0 (CRNN_TC_DEBUG): entry, set-up done, weights resident, first contraction issued, loop end, exit
+    long long* life = (a.dbg && blockIdx.x == 0) ? a.dbg + 4 * 192 : nullptr;
+    if (life && threadIdx.x == 0) { life[0] = clock64(); unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); life[8] = (long long)g; }
     const int ldz = NCA + 1;                          // (GRU candidate pass uses the first HCG columns)
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for ptxas
     const int slice = blockIdx.x % a.nslices, tile = blockIdx.x / a.nslices;
@@ -842,6 +845,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
     // cluster exchange: two operand buffers in the ring - lstm / rnn: h_{t-1} in buffer t % 2; gru: h_{t-1} in 0, r*h in 1
     const int cx_tile = rt_tile_bytes(a.box_rows);
     const uint32_t cx_buf = (uint32_t)(nsp * nkb * cx_tile);
+    if (life && threadIdx.x == 0) life[1] = clock64();
     int dbg_slot = -1;
     if (a.dbg) dbg_slot = blockIdx.x == 0 ? 0 : blockIdx.x == 1 ? 1 : blockIdx.x == gridDim.x / 2 ? 2 : blockIdx.x == gridDim.x - 1 ? 3 : -1;
     long long* dbgs = dbg_slot >= 0 ? s.dbg : nullptr;
@@ -909,10 +913,12 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         {   // the whole warp runs the issue loop (see mma_bf16_elect)
             const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
             mbar_wait(s.w_bar, 0);
+            if (life && lane == 0) life[2] = clock64();
             if (a.xchg) {
                 uint32_t uses[2] = {0u, 0u};
                 for (int t = a.t_begin; t < a.t_end; ++t)
                     for (int ph = 0; ph < nphase; ++ph) {
+                        if (life && lane == 0 && t == a.t_begin + 1 && ph == 0) life[3] = clock64();
                         const int bidx = MODEL == CRNN_MODEL_GRU ? ph : (t & 1);
                         const int dbg_phase = (t - a.t_begin) * nphase + ph;
                         // bytes of a complete buffer: the launch's first one is TMA boxes, the others bt rows x H units from the slices
@@ -1138,9 +1144,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
             }
         }
     }
+    if (life && warp == 1 && lane == 0) life[4] = clock64();
+    if (life && warp == 2 && lane == 0) life[7] = clock64();
     __syncthreads();
+    if (life && threadIdx.x == 0) life[5] = clock64();
     if (dbgs) for (int i = threadIdx.x; i < 192; i += RT_THREADS) a.dbg[dbg_slot * 192 + i] = dbgs[i];
     if (a.csize > 1) cluster_sync_all();             // no CTA leaves while a peer may still signal its barriers
+    if (life && threadIdx.x == 0) { life[6] = clock64(); unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); life[9] = (long long)g; }
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem, tcols);

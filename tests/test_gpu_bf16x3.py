@@ -132,6 +132,11 @@ SHAPES = [
     ("gru", 96, 2, 12, 70, 96, {"CRNN_TC_GATHER": 1}), ("lstm", 128, 2, 10, 50, 65, {"CRNN_TC_GATHER": 1}),
     ("rnn", 160, 2, 9, 33, 40, {"CRNN_TC_GATHER": 1}), ("gru", 512, 2, 12, 64, 96, {"CRNN_TC_GATHER": 1}),
     ("gru", 512, 2, 12, 64, 96, {}),                        # config-3 layers, a short sequence
+    # cluster exchange (all slices of a tile in one cluster, rows pushed with st.async): the default where it fits - here
+    # across chunk boundaries (a launch's first contraction reads global memory), ragged tiles, 2 / 4 / 8 slices - and off
+    ("lstm", 128, 2, 12, 50, 65, {"CRNN_WAVEFRONT_CHUNKS": 3}), ("gru", 128, 2, 9, 37, 30, {"CRNN_WAVEFRONT_CHUNKS": 3}),
+    ("rnn", 64, 2, 9, 21, 13, {"CRNN_WAVEFRONT_CHUNKS": 2}), ("gru", 256, 1, 6, 90, 13, {}), ("lstm", 32, 1, 7, 3, 9, {}),
+    ("lstm", 128, 2, 12, 50, 65, {"CRNN_TC_CX": 0}), ("gru", 64, 2, 8, 20, 17, {"CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 4}),
 ]
 
 

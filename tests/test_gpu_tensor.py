@@ -135,6 +135,11 @@ BF16_SHAPES = [
     ("gru", 128, 2, 8, 24, 13, {"CRNN_TC_HC": 16, "CRNN_TC_KSPLIT": 2, "CRNN_WAVEFRONT_CHUNKS": 3}),
     # cluster step barrier (remote mbarrier arrives) at 16 slices, and switched off
     ("gru", 256, 1, 5, 20, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 16}), ("lstm", 128, 2, 6, 40, 13, {"CRNN_TC_HC": 16, "CRNN_TC_CBAR": 0}),
+    # cluster exchange (default where all slices of a tile fit one cluster) across chunk boundaries, and the cluster step
+    # barrier that it replaced (CRNN_TC_CX=0)
+    ("lstm", 128, 2, 12, 50, 65, {"CRNN_WAVEFRONT_CHUNKS": 3}), ("gru", 128, 2, 9, 37, 30, {"CRNN_WAVEFRONT_CHUNKS": 3}),
+    ("rnn", 64, 2, 9, 21, 13, {"CRNN_WAVEFRONT_CHUNKS": 2}), ("gru", 256, 1, 6, 90, 13, {}),
+    ("lstm", 128, 2, 12, 50, 65, {"CRNN_TC_CX": 0}), ("gru", 64, 2, 8, 20, 17, {"CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 4}),
 ]
 
 

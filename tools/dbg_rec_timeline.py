@@ -22,3 +22,7 @@ for c in (0,3):
     for p in range(1,7):
         ref=d[c,p,R]
         print(c,p,'|',' '.join(str(int(d[c,p,i]-ref)).rjust(12) for i in order),'|',int(d[c,p+1,R]-d[c,p,R]))
+
+life=m.workspace[24576+8*4*192:24576+8*4*192+8*16].view(torch.int64).cpu().numpy()
+print('CTA 0 life cycle (cycles after entry): setup_done %d  weights_resident %d  second_step_begins %d  mma_loop_end %d  epilogue_loop_end %d  all_warps_done %d  exit %d ; globaltimer entry..exit %.2f us for %d steps'
+      % tuple([int(life[i]-life[0]) for i in (1,2,3,4,7,5,6)]+[(life[9]-life[8])/1e3, S_]))

@@ -1,12 +1,4 @@
 cd $GRAFT_REPO_ROOT
-run1() { env "$@" timeout 100 python tools/quick_bench.py c1 bf16x3 20 2>&1 | grep -E "QB|rror" | cut -c1-200; }
-run1 CRNN_WAVEFRONT_CHUNKS=1
-run1 CRNN_WAVEFRONT_CHUNKS=2
-run1 CRNN_WAVEFRONT_CHUNKS=3
-run1 CRNN_WAVEFRONT_CHUNKS=4
-run1 CRNN_WAVEFRONT_CHUNKS=5
-run1 CRNN_WAVEFRONT=1
-run1 CRNN_TC_TILES=1
-run1 CRNN_TC_TILES=2
-run1 CRNN_TC_TILES=2 CRNN_WAVEFRONT_CHUNKS=3
-run1 CRNN_TC_HC=32
+for S in 50 10; do
+DBG_MODEL=lstm DBG_H=128 DBG_B=50 DBG_S=$S DBG_REF=11 timeout 120 python tools/dbg_rec_timeline.py bf16x3 2>&1 | grep -E "life|rror"
+done
