@@ -272,6 +272,7 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
                 int rb = tc::RT_RING_BYTES;
                 while (rb > 32 * 1024 && (int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) rb -= 16 * 1024;
                 if ((int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) continue;
+                if (tc::rt_num_stages(o->box_rows, 1, h->split, rb) < 2) continue;      // the ring must still hold two stages
                 *ring = rb;
                 return Qc;
             }
@@ -389,6 +390,13 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
             if (best == 0 || cand.nslices * cand.ntiles > out->nslices * out->ntiles) { best = HC; *out = cand; }
             if (hc_env >= 16 || cand.nslices * cand.ntiles >= (max_ctas * 3) / 4) break;
         }
+    // LSTM slices of 8 units (32 gate columns, N = 32 / 64 MMAs) where 16 do not fit: hi + lo slices of H = 1024 (config 4 in
+    // split precision) are 128 KB per CTA at 128 slices.  BPTT contracts one column per unit, so its MMA needs the K split
+    // (N = 8 Q >= 16) or M = 64 tiles (N = 8 is legal there).
+    if ((best == 0 || hc_env == 8) && model == CRNN_MODEL_LSTM && H % 8 == 0 && fill(8, &cand) &&
+        (cand.q_bwd >= 2 || std::min(cand.pr, cand.BT) <= 64) && !cand.swap_fwd && !cand.swap_bwd) {
+        best = 8; *out = cand;
+    }
     if (best == 0) return set_err(CRNN_ERR_UNSUP, "rnn_size %d: recurrent weight slice does not fit in shared memory%s", H,
                                   h->split ? " with split operands (use CRNN_PREC_BF16 or CRNN_PREC_FP32)" : "");
     return CRNN_OK;

@@ -137,6 +137,9 @@ SHAPES = [
     ("lstm", 128, 2, 12, 50, 65, {"CRNN_WAVEFRONT_CHUNKS": 3}), ("gru", 128, 2, 9, 37, 30, {"CRNN_WAVEFRONT_CHUNKS": 3}),
     ("rnn", 64, 2, 9, 21, 13, {"CRNN_WAVEFRONT_CHUNKS": 2}), ("gru", 256, 1, 6, 90, 13, {}), ("lstm", 32, 1, 7, 3, 9, {}),
     ("lstm", 128, 2, 12, 50, 65, {"CRNN_TC_CX": 0}), ("gru", 64, 2, 8, 20, 17, {"CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 4}),
+    # LSTM slices of 8 units (what config 4 needs in split precision): M = 64 tiles, 128-row tiles with the K split, exchange off
+    ("lstm", 64, 2, 6, 20, 13, {"CRNN_TC_HC": 8}), ("lstm", 128, 1, 5, 100, 13, {"CRNN_TC_HC": 8, "CRNN_TC_KSPLIT": 2, "CRNN_TC_TILES": 1}),
+    ("lstm", 64, 2, 6, 20, 13, {"CRNN_TC_HC": 8, "CRNN_TC_CX": 0}),
 ]
 
 
@@ -230,10 +233,11 @@ def test_dropout_and_sampling_in_split_mode():
 
 
 def test_shapes_that_do_not_fit_are_refused_not_degraded():
-    """LSTM 3x1024 (config 4): hi + lo recurrent slices exceed shared memory -> a clear error, no silent fallback."""
+    """LSTM 2048: hi + lo recurrent slices exceed shared memory even at 8 units per slice -> a clear error, no silent
+    fallback.  (LSTM 1024 - config 4 - fits since slices of 8 units exist: tests/test_gpu_configs.py.)"""
     from distributed_char_rnn_b200.model import Model
     from distributed_char_rnn_b200._lib import CrnnError
-    args = argparse.Namespace(model="lstm", rnn_size=1024, num_layers=1, seq_length=4, batch_size=16, vocab_size=20,
+    args = argparse.Namespace(model="lstm", rnn_size=2048, num_layers=1, seq_length=4, batch_size=16, vocab_size=20,
                               grad_clip=5.0, output_keep_prob=1.0, input_keep_prob=1.0)
-    with pytest.raises(CrnnError, match="split operands"):
+    with pytest.raises(CrnnError, match="split operands|slices > "):
         Model(args, device="cuda:0", precision="bf16x3")

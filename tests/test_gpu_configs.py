@@ -94,6 +94,12 @@ def test_config4_layer_geometry_bf16():
     print("config 4 layer (bf16): worst gradient error %.2e" % _check_gradients(cfg, params, m, "bf16", seed=44))
 
 
+def test_config4_layer_geometry_split_precision():
+    """The same layer at the fp32 bar: hi + lo slices of 8 units (128 slices x 128 KB), 1e-4 against the exact oracle."""
+    cfg, params, m = _make("lstm", 1024, 1, 6, 128, 96, "bf16x3", seed=4)
+    print("config 4 layer (bf16x3): worst gradient error %.2e" % _check_gradients(cfg, params, m, "bf16x3", seed=44))
+
+
 @pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
 def test_config5_layer_geometry(precision):
     """tanh RNN H=2048, B=512, V=256 (config 5's layer: K split over 2 CTAs, four 128-row passes per tile)."""

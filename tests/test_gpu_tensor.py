@@ -140,6 +140,7 @@ BF16_SHAPES = [
     ("lstm", 128, 2, 12, 50, 65, {"CRNN_WAVEFRONT_CHUNKS": 3}), ("gru", 128, 2, 9, 37, 30, {"CRNN_WAVEFRONT_CHUNKS": 3}),
     ("rnn", 64, 2, 9, 21, 13, {"CRNN_WAVEFRONT_CHUNKS": 2}), ("gru", 256, 1, 6, 90, 13, {}),
     ("lstm", 128, 2, 12, 50, 65, {"CRNN_TC_CX": 0}), ("gru", 64, 2, 8, 20, 17, {"CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 4}),
+    ("lstm", 64, 2, 6, 20, 13, {"CRNN_TC_HC": 8}),          # LSTM slices of 8 units
 ]
 
 
