@@ -54,6 +54,9 @@ struct WsPlan {
     std::vector<size_t> csum;        // per layer (+ one for softmax_b): row-block partials of the bias-gradient column sums
     size_t es_part, es_sq;           // ordered embedding scatter: per-segment tables [nseg][V][H], partial sums of squares
     int es_nseg, es_tps;             // segments / tokens per segment (0: the table does not fit shared memory -> atomics)
+    // sorted form (elementwise.cuh: es_rank_kernel ...): token order by id, per-piece partial rows
+    int es_sorted, es_nblk, es_pmax, es_piece_rows;
+    size_t es_lrank, es_order, es_hist, es_off, es_poff, es_piece, es_np;
     size_t total;
 };
 
@@ -92,6 +95,7 @@ struct crnn_handle {
     // wavefront over layers (tensor path): wf_W layer streams, each sequence cut into wf_C chunks
     int wf_W, wf_C;
     std::vector<cudaStream_t> wf_streams;
+    cudaStream_t aux_stream = nullptr;   // small id-only work that runs beside the step (the scatter's token sort)
     std::vector<cudaEvent_t> wf_events;
     // dropout (training calls only): keep probabilities, seed, and the count of training calls so far
     float ikp, okp;
@@ -489,7 +493,8 @@ static void build_workspace(crnn_handle* h) {
     for (int l = 0; l <= L; ++l) w.csum.push_back(take(l < L ? colsum_scratch_floats(S * B, h->GZ * H) : ceil_div64(S * B, 128) * V));
     // ordered embedding scatter: token segments of >= 128 rows, at most 32 MB of per-segment tables
     w.es_nseg = 0; w.es_tps = 0; w.es_part = w.es_sq = 0;
-    if ((int64_t)es_smem_bytes((int)V) + 1024 <= h->max_smem && H % 4 == 0) {
+    const bool es_sort_ok = env_int("CRNN_ES_SORT", 1) && H % 4 == 0 && V <= 8192 && S * B < (1LL << 31);
+    if (!es_sort_ok && (int64_t)es_smem_bytes((int)V) + 1024 <= h->max_smem && H % 4 == 0) {
         // segments: about two CTAs per SM over all column chunks, at least 128 rows each, at most 32 MB of tables
         const int64_t N = S * B, tab = V * H * 4, nchunk = ceil_div64(H, ES_COLS);
         int64_t nseg = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(N / 128, (32LL << 20) / tab), std::max<int64_t>(1, 2 * h->sm_count / nchunk)));
@@ -497,6 +502,23 @@ static void build_workspace(crnn_handle* h) {
         w.es_nseg = (int)ceil_div64(N, w.es_tps);
         w.es_part = take((int64_t)w.es_nseg * V * H);
         w.es_sq = take(2 * (int64_t)w.es_nseg * ceil_div64(H, ES_COLS));
+    }
+    // sorted form: the default when the vocabulary's counters fit one block's shared memory (CRNN_ES_SORT=0: table form)
+    w.es_sorted = 0;
+    if (es_sort_ok) {
+        const int64_t N = S * B;
+        w.es_sorted = 1;
+        w.es_nblk = (int)ceil_div64(N, ES_SORT_BLOCK);
+        // pieces of 64 tokens, or of 32 where 64 would leave the GPU short of CTAs (measured, config 3: 0.048 -> 0.041 ms with
+        // 32; config 5: 0.23 -> 0.34 ms, its per-piece partial rows double)
+        w.es_piece_rows = (N / 64 + V) * ceil_div64(H, 4 * ES_SUM_THREADS) < 4LL * h->sm_count ? 32 : 64;
+        w.es_pmax = (int)(N / w.es_piece_rows + V + 1);
+        w.es_lrank = take(N); w.es_order = take(N);
+        w.es_hist = take((int64_t)w.es_nblk * V);
+        w.es_off = take(V + 1); w.es_poff = take(V + 1);
+        w.es_piece = take(2 * (int64_t)w.es_pmax); w.es_np = take(4);
+        w.es_part = take((int64_t)w.es_pmax * H);
+        w.es_sq = take(2 * (int64_t)w.es_pmax * ceil_div64(H, 4 * ES_SUM_THREADS));
     }
     w.total = off;
 }
@@ -602,7 +624,8 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         if (cudaHostAlloc((void**)&h->err_word, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); rc = set_err(CRNN_ERR_CUDA, "cudaHostAlloc failed"); }
         else *h->err_word = 0u;
     }
-    if (rc != CRNN_OK) { for (cudaStream_t s_ : h->wf_streams) cudaStreamDestroy(s_); if (h->err_word) cudaFreeHost(h->err_word); delete h; return rc; }
+    if (rc == CRNN_OK && h->tc && cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking) != cudaSuccess) { h->aux_stream = nullptr; rc = set_err(CRNN_ERR_CUDA, "cudaStreamCreate failed"); }
+    if (rc != CRNN_OK) { for (cudaStream_t s_ : h->wf_streams) cudaStreamDestroy(s_); if (h->aux_stream) cudaStreamDestroy(h->aux_stream); if (h->err_word) cudaFreeHost(h->err_word); delete h; return rc; }
     build_workspace(h);
     if (env_int("CRNN_VERBOSE", 0) && h->tc)
         fprintf(stderr, "[crnn] plan: HC %d BT %d slices %d tiles %d passes %d x %d rows%s, K split fwd/bwd %d/%d, ring %d/%d KB, smem %zu/%zu, "
@@ -619,6 +642,7 @@ void crnn_destroy(crnn_handle* h) {
     for (cudaEvent_t e : h->kev) cudaEventDestroy(e);
     for (cudaEvent_t e : h->wf_events) if (e) cudaEventDestroy(e);
     for (cudaStream_t s : h->wf_streams) cudaStreamDestroy(s);
+    if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
     if (h->err_word) cudaFreeHost(h->err_word);
     delete h;
 }
@@ -730,6 +754,29 @@ static int grid_for(int64_t n_threads_needed, int sm_count) {
 
 static inline double* ws_loss_part(void* ws) { return reinterpret_cast<double*>((char*)ws + 8192); }   // one slot per softmax block (<= 8 * SMs)
 
+// Token order by id for the sorted embedding scatter: depends on the ids only, so it runs early in the step (beside the
+// forward pass where a second stream exists).
+static int scatter_sort(crnn_handle* h, const int32_t* x, int64_t ld, void* ws, cudaStream_t st) {
+    if (!h->ws.es_sorted) return CRNN_OK;
+    const crnn_config& c = h->cfg;
+    const int V = c.vocab_size, B = c.batch_size;
+    const int64_t N = (int64_t)c.seq_length * B;
+    int* hist = reinterpret_cast<int*>((char*)ws + h->ws.es_hist);
+    int* lrank = reinterpret_cast<int*>((char*)ws + h->ws.es_lrank);
+    int* order = reinterpret_cast<int*>((char*)ws + h->ws.es_order);
+    int* off = reinterpret_cast<int*>((char*)ws + h->ws.es_off);
+    int* poff = reinterpret_cast<int*>((char*)ws + h->ws.es_poff);
+    int2* piece = reinterpret_cast<int2*>((char*)ws + h->ws.es_piece);
+    int* np = reinterpret_cast<int*>((char*)ws + h->ws.es_np);
+    es_rank_kernel<<<h->ws.es_nblk, ES_SORT_BLOCK, V * sizeof(int), st>>>(x, ld, B, N, V, hist, lrank);
+    CRNN_LAUNCH_CHECK("es_rank_kernel");
+    es_offsets_kernel<<<1, 1024, 2 * V * sizeof(int), st>>>(h->ws.es_nblk, V, h->ws.es_piece_rows, hist, off, poff, piece, np);
+    CRNN_LAUNCH_CHECK("es_offsets_kernel");
+    es_place_kernel<<<grid_for(N, h->sm_count), 256, 0, st>>>(x, ld, B, N, V, hist, off, lrank, order);
+    CRNN_LAUNCH_CHECK("es_place_kernel");
+    return CRNN_OK;
+}
+
 // Embedding gradient (scatter-add of the slices) + sum of squares of the slices + the two trailing scalars.
 static int scatter_and_finalize(crnn_handle* h, const int32_t* x, int64_t ld, const float* dX, float* grads, void* ws,
                                 int nloss, cudaStream_t st) {
@@ -737,7 +784,20 @@ static int scatter_and_finalize(crnn_handle* h, const int32_t* x, int64_t ld, co
     const int H = c.rnn_size, V = c.vocab_size, S = c.seq_length, B = c.batch_size;
     const int64_t SB = (int64_t)S * B;
     prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
-    if (h->ws.es_nseg > 0) {
+    if (h->ws.es_sorted) {                            // (the token order was built by scatter_sort, early in the step)
+        const int nchunk = ceil_div(H, 4 * ES_SUM_THREADS);
+        const int* order = reinterpret_cast<const int*>((char*)ws + h->ws.es_order);
+        const int2* piece = reinterpret_cast<const int2*>((char*)ws + h->ws.es_piece);
+        const int* np = reinterpret_cast<const int*>((char*)ws + h->ws.es_np);
+        const int* poff = reinterpret_cast<const int*>((char*)ws + h->ws.es_poff);
+        float* part = wsf(ws, h->ws.es_part);
+        double* sqp = reinterpret_cast<double*>((char*)ws + h->ws.es_sq);
+        if (h->ws.es_piece_rows == 32) es_sum_kernel<32><<<dim3(nchunk, h->ws.es_pmax), ES_SUM_THREADS, 0, st>>>(H, dX, order, piece, np, part, sqp);
+        else                           es_sum_kernel<64><<<dim3(nchunk, h->ws.es_pmax), ES_SUM_THREADS, 0, st>>>(H, dX, order, piece, np, part, sqp);
+        CRNN_LAUNCH_CHECK("es_sum_kernel");
+        es_finish_kernel<<<grid_for((int64_t)V * H, h->sm_count), 256, 0, st>>>(grads + h->emb_off, V, H, poff, part, sqp, np, nchunk, ws_sq(ws));
+        CRNN_LAUNCH_CHECK("es_finish_kernel");
+    } else if (h->ws.es_nseg > 0) {
         const int nchunk = ceil_div(H, ES_COLS);
         const int smem = (int)es_smem_bytes(V);
         static bool attr_done[64] = {};
@@ -1309,7 +1369,17 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
     CRNN_CUDA(cudaMemsetAsync(ws, 0, kScratchBytes, st));
     int fused = 0;
-    int rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st, call, y, &fused);
+    // the scatter's token order depends on the ids only: built on a side stream while the forward pass runs
+    const int ev_sort = 4 * L * C + 128;
+    int rc = CRNN_OK;
+    if (h->ws.es_sorted) {
+        rc = wf_record(h, ev_sort, st);
+        if (rc == CRNN_OK) rc = wf_wait(h, ev_sort, h->aux_stream);
+        if (rc == CRNN_OK) rc = scatter_sort(h, x, ld, ws, h->aux_stream);
+        if (rc == CRNN_OK) rc = wf_record(h, ev_sort + 1, h->aux_stream);
+        if (rc != CRNN_OK) return rc;
+    }
+    rc = run_forward_bf16(h, x, ld, state_in, state_out, params, ws, st, call, y, &fused);
     if (rc != CRNN_OK) return rc;
     const bf16_t* pbf = wsb(ws, h->ws.pbf);
     float* logits = wsf(ws, h->ws.logits);
@@ -1454,6 +1524,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         if (rc == CRNN_OK && drop) rc = drop_apply(h, call, 0, dn, dn, nullptr, 0, SB * H, st);
         if (rc != CRNN_OK) return rc;
     }
+    if (h->ws.es_sorted) { rc = wf_wait(h, ev_sort + 1, st); if (rc != CRNN_OK) return rc; }
     rc = scatter_and_finalize(h, x, ld, wsf(ws, h->ws.gx0), grads, ws, nloss, st);
     if (rc != CRNN_OK) return rc;
     prof_mark(h, st, -1);
@@ -1561,7 +1632,8 @@ int crnn_forward_backward(crnn_handle* h, const int32_t* x, const int32_t* y, in
         std::swap(dcur, dnext);
     }
     // dcur = dX [S,B,H] = the IndexedSlices values of the embedding gradient
-    rc = scatter_and_finalize(h, x, ld, dcur, grads, ws, nloss, st);
+    rc = scatter_sort(h, x, ld, ws, st);
+    if (rc == CRNN_OK) rc = scatter_and_finalize(h, x, ld, dcur, grads, ws, nloss, st);
     if (rc != CRNN_OK) return rc;
     prof_mark(h, st, -1);
     return CRNN_OK;

@@ -176,6 +176,165 @@ __global__ void __launch_bounds__(256) embed_scatter_reduce_kernel(float* __rest
     }
 }
 
+// Sorted form of the ordered scatter (the default of the training step): the token ids are known when the step starts, so
+// the tokens are first sorted stably by id (three small kernels that run beside the forward pass), which turns the scatter
+// into a segmented sum over contiguous runs of the index array:
+//   es_rank_kernel     block of 1024 tokens (time-major order i = t*B + b): per-block histogram, and for every token the
+//                      number of EARLIER tokens of its block with the same id;
+//   es_offsets_kernel  one block: exclusive sums over blocks (per id) and over ids, and the list of "pieces" - runs of at
+//                      most 64 (or 32) tokens of one id;
+//   es_place_kernel    order[offset(id) + base(block, id) + rank] = i;
+//   es_sum_kernel      CTA (piece, 512-column chunk): thread c adds column quad c of the piece's rows in a register, in
+//                      time order - independent 16-byte loads, no shared memory, no atomics, every byte of dout read once;
+//   es_finish_kernel   dtable[v] = sum of v's pieces in order; block 0 adds the pieces' sums of squares in order.
+// Same bits on every run and every replica: every sum has a fixed order that does not depend on the grid.
+constexpr int ES_PIECE_MAX = 64;     // tokens per piece: 64, or 32 where that is needed to fill the GPU (es_sum_kernel<PIECE>)
+constexpr int ES_SORT_BLOCK = 1024;
+__global__ void __launch_bounds__(ES_SORT_BLOCK) es_rank_kernel(const int32_t* __restrict__ x, int64_t ldx, int B, int64_t N, int V,
+                                                                int* __restrict__ hist, int* __restrict__ lrank) {
+    __shared__ int ids[ES_SORT_BLOCK];
+    extern __shared__ int es_hist_s[];                 // [V]
+    const int tid = threadIdx.x;
+    const int64_t i = (int64_t)blockIdx.x * ES_SORT_BLOCK + tid;
+    for (int v = tid; v < V; v += ES_SORT_BLOCK) es_hist_s[v] = 0;
+    int id = -1;
+    if (i < N) {
+        const int t = (int)(i / B), b = (int)(i % B);
+        id = min(max(__ldg(x + (int64_t)b * ldx + t), 0), V - 1);
+    }
+    ids[tid] = id;
+    __syncthreads();
+    if (i < N) {
+        atomicAdd(&es_hist_s[id], 1);                  // (a count: the order of the adds does not matter)
+        int r = 0;
+        for (int j = 0; j < tid; ++j) r += ids[j] == id;
+        lrank[i] = r;
+    }
+    __syncthreads();
+    for (int v = tid; v < V; v += ES_SORT_BLOCK) hist[(int64_t)blockIdx.x * V + v] = es_hist_s[v];
+}
+// hist[blk][v] becomes the number of tokens with id v in EARLIER blocks; off[v] the first position of id v in `order`;
+// poff[v] the first piece of id v; piece[p] = {k0, k1} positions in `order`; *npieces their number.
+__global__ void __launch_bounds__(1024) es_offsets_kernel(int nblk, int V, int ES_PIECE, int* __restrict__ hist, int* __restrict__ off,
+                                                          int* __restrict__ poff, int2* __restrict__ piece, int* __restrict__ npieces) {
+    extern __shared__ int es_cnt[];                    // [V] counts, then [V] piece counts
+    int* cnt = es_cnt;
+    int* pc = es_cnt + V;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        int run = 0;
+        for (int b = 0; b < nblk; ++b) { const int t = hist[(int64_t)b * V + v]; hist[(int64_t)b * V + v] = run; run += t; }
+        cnt[v] = run;
+        pc[v] = (run + ES_PIECE - 1) / ES_PIECE;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {                            // V is a vocabulary of characters: a serial scan is a few hundred adds
+        int o = 0, p = 0;
+        for (int v = 0; v < V; ++v) { off[v] = o; poff[v] = p; o += cnt[v]; p += pc[v]; }
+        off[V] = o; poff[V] = p;
+        *npieces = p;
+    }
+    __syncthreads();
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        const int o = off[v], n = cnt[v], p0 = poff[v];
+        for (int j = 0; j < pc[v]; ++j) piece[p0 + j] = make_int2(o + j * ES_PIECE, o + min(n, (j + 1) * ES_PIECE));
+    }
+}
+__global__ void __launch_bounds__(256) es_place_kernel(const int32_t* __restrict__ x, int64_t ldx, int B, int64_t N, int V,
+                                                       const int* __restrict__ hist, const int* __restrict__ off,
+                                                       const int* __restrict__ lrank, int* __restrict__ order) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
+        const int t = (int)(i / B), b = (int)(i % B);
+        const int id = min(max(__ldg(x + (int64_t)b * ldx + t), 0), V - 1);
+        order[off[id] + hist[(i / ES_SORT_BLOCK) * V + id] + lrank[i]] = (int)i;
+    }
+}
+constexpr int ES_SUM_THREADS = 128;  // x 4 columns
+template <int ES_PIECE>
+__global__ void __launch_bounds__(ES_SUM_THREADS) es_sum_kernel(int H, const float* __restrict__ dout, const int* __restrict__ order,
+                                                                const int2* __restrict__ piece, const int* __restrict__ npieces,
+                                                                float* __restrict__ partial, double* __restrict__ sqpart) {
+    __shared__ double sh[32];
+    const int p = blockIdx.y;
+    if (p >= *npieces) return;
+    const int col = (blockIdx.x * ES_SUM_THREADS + threadIdx.x) * 4;
+    const bool live = col < H;                         // H % 4 == 0 (host)
+    const int2 pc = piece[p];
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    double ss = 0.0;
+    if (live) {
+        const float* src = dout + col;
+        if (ES_PIECE == 32) {
+            // short pieces (small inputs: latency matters): the piece's row indices first - one round trip for all of them -,
+            // then its rows in two batches of sixteen independent 16-byte loads, added in time order
+            int idx[32];
+            const int n = pc.y - pc.x;
+#pragma unroll
+            for (int u = 0; u < 32; ++u) idx[u] = u < n ? __ldg(order + pc.x + u) : -1;
+#pragma unroll
+            for (int h0 = 0; h0 < 32; h0 += 16) {
+                float4 g[16];
+#pragma unroll
+                for (int u = 0; u < 16; ++u)
+                    g[u] = idx[h0 + u] >= 0 ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)idx[h0 + u] * H)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 16; ++u) {
+                    acc.x += g[u].x; acc.y += g[u].y; acc.z += g[u].z; acc.w += g[u].w;
+                    ss += (double)g[u].x * g[u].x + (double)g[u].y * g[u].y + (double)g[u].z * g[u].z + (double)g[u].w * g[u].w;
+                }
+            }
+        } else {
+            // long pieces (large inputs: bandwidth matters, many CTAs per SM hide the latency): eight rows in flight
+            int k = pc.x;
+            for (; k + 8 <= pc.y; k += 8) {
+                float4 g[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) g[u] = __ldg(reinterpret_cast<const float4*>(src + (int64_t)__ldg(order + k + u) * H));
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    acc.x += g[u].x; acc.y += g[u].y; acc.z += g[u].z; acc.w += g[u].w;
+                    ss += (double)g[u].x * g[u].x + (double)g[u].y * g[u].y + (double)g[u].z * g[u].z + (double)g[u].w * g[u].w;
+                }
+            }
+            for (; k < pc.y; ++k) {
+                const float4 g = __ldg(reinterpret_cast<const float4*>(src + (int64_t)__ldg(order + k) * H));
+                acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+                ss += (double)g.x * g.x + (double)g.y * g.y + (double)g.z * g.z + (double)g.w * g.w;
+            }
+        }
+        *reinterpret_cast<float4*>(partial + (int64_t)p * H + col) = acc;
+    }
+    const double tot = block_sum_d(ss, sh);
+    if (threadIdx.x == 0) sqpart[(int64_t)p * gridDim.x + blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(256) es_finish_kernel(float* __restrict__ dtable, int V, int H, const int* __restrict__ poff,
+                                                        const float* __restrict__ partial, const double* __restrict__ sqpart,
+                                                        const int* __restrict__ npieces, int nchunk, double* __restrict__ sqnorm) {
+    const int64_t VH = (int64_t)V * H;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < VH; i += (int64_t)gridDim.x * blockDim.x) {
+        const int v = (int)(i / H), c = (int)(i % H);
+        float acc = 0.f;
+        int p = poff[v];
+        const int p1 = poff[v + 1];
+        for (; p + 8 <= p1; p += 8) {                  // eight loads in flight, added in piece order
+            float g[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) g[u] = __ldg(partial + (int64_t)(p + u) * H + c);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc += g[u];
+        }
+        for (; p < p1; ++p) acc += __ldg(partial + (int64_t)p * H + c);
+        dtable[i] = acc;
+    }
+    if (blockIdx.x == 0 && sqnorm) {                  // fixed order: strided per thread, then the block's fixed tree
+        __shared__ double sh[32];
+        const int nsq = *npieces * nchunk;
+        double t = 0.0;
+        for (int i = threadIdx.x; i < nsq; i += blockDim.x) t += sqpart[i];
+        t = block_sum_d(t, sh);
+        if (threadIdx.x == 0) *sqnorm = t;
+    }
+}
+
 // ---- dropout (model.py:31-34,58-59; train.py:58-61) ----------------------------------------
 // tf.nn.dropout: x * floor(keep + u) / keep, a fresh mask per element and per step.  Masks are not
 // stored: they are a pure function of (seed, training-call index, stage, element index), regenerated
