@@ -64,7 +64,7 @@ struct RecPlanTc {
     int HC, BT, nslices, ntiles, npass, box_rows, zs_fwd, zs_bwd, swap_fwd, swap_bwd;
     int q_fwd, q_bwd;       // K parts per unit group (cluster size) of the forward / backward kernel
     int ring_fwd, ring_bwd; // TMA ring bytes
-    int cx;                 // cluster exchange: all slices of a tile in one cluster, rows delivered through distributed shared memory
+    int cx_fwd, cx_bwd;     // cluster exchange (per direction): all slices of a tile in one cluster, rows delivered through distributed shared memory
     int pr, sub;            // rows per pass; 1: the passes of a tile are independent chains (RecTcArgs::sub)
     int gather;             // 1: direct exchange of the streamed rows (recurrence_tc.cuh: rt_gather) instead of TMA loads behind a step barrier
     int g_rp_log2, g_ckb_log2;
@@ -363,19 +363,18 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
         // the step hand-shake goes through L2.  Needs the phase's whole K extent per buffer: two buffers forward, two (gru:
         // two + one) backward.  (tools/ubench_dsmem.cu: pays for clusters of <= 8 with a few KB per slice; at config 3's
         // geometry - 16 slices x 4 KB - the exchange through L2 is faster, and its weights leave no room for the buffers.)
-        o->cx = 0;
+        o->cx_fwd = o->cx_bwd = 0;
         if (env_int("CRNN_TC_CX", 1) && (nslices == 2 || nslices == 4 || nslices == 8) && nslices <= std::min(8, h->env.cbar) &&
             o->npass == 1 && !o->sub && !o->gather && o->q_fwd == 1 && o->q_bwd == 1 && !o->swap_fwd && !o->swap_bwd) {
             const int tile = tc::rt_tile_bytes(o->box_rows), nsp = 1 + h->split;
             const int nkbg = ceil_div(g1 * H, 64);
             const int need_f = (2 * nsp * nkb * tile + tc::RT_MROWS_BYTES - tile + 1023) & ~1023;
             const int need_b = ((2 * nkbg + (model == CRNN_MODEL_GRU ? nkb : 0)) * nsp * tile + tc::RT_MROWS_BYTES - tile + 1023) & ~1023;
+            // (each direction on its own: BPTT's buffers hold the G1*H gate columns and stop fitting first - LSTM 256 in
+            //  split precision exchanges inside the cluster forward and through L2 backward)
             const int add_f = std::max(0, need_f - o->ring_fwd), add_b = std::max(0, need_b - o->ring_bwd);
-            if ((int)o->smem_fwd + add_f <= h->max_smem && (int)o->smem_bwd + add_b <= h->max_smem) {
-                o->cx = 1;
-                o->ring_fwd += add_f; o->smem_fwd += (size_t)add_f;
-                o->ring_bwd += add_b; o->smem_bwd += (size_t)add_b;
-            }
+            if ((int)o->smem_fwd + add_f <= h->max_smem) { o->cx_fwd = 1; o->ring_fwd += add_f; o->smem_fwd += (size_t)add_f; }
+            if ((int)o->smem_bwd + add_b <= h->max_smem) { o->cx_bwd = 1; o->ring_bwd += add_b; o->smem_bwd += (size_t)add_b; }
         }
         return true;
     };
@@ -394,6 +393,17 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
             if (best == 0 || cand.nslices * cand.ntiles > out->nslices * out->ntiles) { best = HC; *out = cand; }
             if (hc_env >= 16 || cand.nslices * cand.ntiles >= (max_ctas * 3) / 4) break;
         }
+    // A slice width at which the tile's slices fit one cluster (cluster exchange, at least forward) beats more, narrower
+    // slices that must exchange through L2 (measured, split precision, 2 layers, B = 64, S = 50: LSTM 256 1.03 -> 0.97 ms,
+    // GRU 256 1.47 -> 0.95, tanh-RNN 256 0.76 -> 0.53); among such widths the one with the most CTAs.
+    if (best != 0 && hc_env < 16 && !out->cx_fwd) {
+        RecPlanTc bx; int best_x = 0;
+        for (int HC = hc_max; HC >= 16; HC -= 16) {
+            if (H % HC != 0 || !fill(HC, &cand) || !cand.cx_fwd) continue;
+            if (best_x == 0 || cand.nslices * cand.ntiles > bx.nslices * bx.ntiles) { best_x = HC; bx = cand; }
+        }
+        if (best_x != 0) { best = best_x; *out = bx; }
+    }
     // LSTM slices of 8 units (32 gate columns, N = 32 / 64 MMAs) where 16 do not fit: hi + lo slices of H = 1024 (config 4 in
     // split precision) are 128 KB per CTA at 128 slices.  BPTT contracts one column per unit, so its MMA needs the K split
     // (N = 8 Q >= 16) or M = 64 tiles (N = 8 is legal there).
@@ -630,7 +640,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     if (env_int("CRNN_VERBOSE", 0) && h->tc)
         fprintf(stderr, "[crnn] plan: HC %d BT %d slices %d tiles %d passes %d x %d rows%s, K split fwd/bwd %d/%d, ring %d/%d KB, smem %zu/%zu, "
                 "wavefront %d layers x %d chunks, workspace %.1f MB\n", h->tcp.HC, h->tcp.BT, h->tcp.nslices, h->tcp.ntiles, h->tcp.npass, h->tcp.pr,
-                h->tcp.sub ? " (sub-chains)" : (h->tcp.cx ? " (cluster exchange)" : ""), h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
+                h->tcp.sub ? " (sub-chains)" : (h->tcp.cx_fwd && h->tcp.cx_bwd ? " (cluster exchange)" : h->tcp.cx_fwd ? " (cluster exchange forward)" : h->tcp.cx_bwd ? " (cluster exchange backward)" : ""), h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
                 h->tcp.smem_bwd, h->wf_W, h->wf_C, h->ws.total / 1e6);
     *out = h;
     return CRNN_OK;
@@ -974,7 +984,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.err = h->err_word;
     if (a.gather) a.ckb = 1 << p.g_ckb_log2;
     a.nst = tc::rt_num_stages(p.box_rows, a.ckb, split, a.ring_bytes);
-    a.use3d = (H % 64 == 0 && h->env.use3d && !p.cx) ? 1 : 0;      // (cluster exchange: the map only serves the launch's first load, K block by K block)
+    a.use3d = (H % 64 == 0 && h->env.use3d && !(backward ? p.cx_bwd : p.cx_fwd)) ? 1 : 0;      // (cluster exchange: the map only serves the launch's first load, K block by K block)
     auto amap = [&](CUtensorMap* m, const bf16_t* base, int64_t rows, int64_t cols, int64_t ld) -> int {
         if (a.use3d) return tc::make_tmap_bf16_kblocks(m, base, rows, cols, ld, p.box_rows, a.ckb);
         return tc::make_tmap_bf16(m, base, rows, cols, ld, p.box_rows);
@@ -1015,7 +1025,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     a.expt = h->env.expt;
     // K-split launches read their partial sums from distributed shared memory; there consecutive lanes on consecutive
     // units (scalar epilogue) beat quads (config 4 BPTT 5.4 vs 6.6 ms, split-precision config 3 BPTT 2.9 vs 3.6 ms)
-    const bool vec4 = p.cx || (h->env.vec4 >= 0 ? h->env.vec4 : (Q > 1 ? 0 : 1)) != 0;   // (the cluster exchange pushes quads)
+    const bool vec4 = (backward ? p.cx_bwd : p.cx_fwd) || (h->env.vec4 >= 0 ? h->env.vec4 : (Q > 1 ? 0 : 1)) != 0;   // (the cluster exchange pushes quads)
     typedef void (*RecFn)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, tc::RecTcArgs);
     RecFn fn;
 #define CRNN_PICK(KERNEL, F)                                                                                   \
@@ -1049,7 +1059,7 @@ static int launch_rec_tc(crnn_handle* h, bool backward, tc::RecTcArgs& a, const 
     }
     if (Q > 1) { csize = Q; a.cbar = 0; }     // the cluster is the K-split group
     a.xchg = 0;
-    if (p.cx && Q == 1) { a.xchg = 1; a.cbar = 0; csize = p.nslices; }   // cluster exchange: the rows themselves travel inside the cluster
+    if ((backward ? p.cx_bwd : p.cx_fwd) && Q == 1) { a.xchg = 1; a.cbar = 0; csize = p.nslices; }   // cluster exchange: the rows themselves travel inside the cluster
     if (csize > 8) CRNN_CUDA(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     a.csize = csize;
     void* args[] = {&t0, &t1, &w0, &w1, &t0l, &t1l, &w0l, &w1l, &a};

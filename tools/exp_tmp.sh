@@ -1,5 +1,6 @@
 cd $GRAFT_REPO_ROOT
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_configs.py -x -q -m gpu -k "scatter or resume or gnorm or embedding" 2>&1 | tail -3
-for c in c3 c1; do timeout 120 python tools/quick_bench.py $c bf16x3 20 2>&1 | grep -E "QB|phases|rror" | cut -c1-330; done
-timeout 300 python tools/quick_bench.py c5 bf16x3 5 2>&1 | grep -E "phases|rror" | cut -c1-400
-timeout 300 python tools/quick_bench.py c4 bf16 5 2>&1 | grep -E "phases|rror" | cut -c1-400
+run() { env "$@" CRNN_VERBOSE=1 timeout 100 python tools/quick_bench.py custom $P 10 2>&1 | grep -E "QB|rror|plan" | cut -c1-220; }
+P=bf16x3
+export QB_CFG=lstm,256,2,50,512,65; run CRNN_X=0; run CRNN_TC_SUB=0
+export QB_CFG=gru,256,2,50,512,65; run CRNN_X=0; run CRNN_TC_SUB=0
+export QB_CFG=rnn,256,2,50,1024,65; run CRNN_X=0; run CRNN_TC_SUB=0

@@ -4,6 +4,9 @@ sys.path.insert(0, os.getcwd())
 import bench as BN
 from distributed_char_rnn_b200.model import Model
 cname = sys.argv[1]; precs = sys.argv[2].split(','); K = int(sys.argv[3]) if len(sys.argv) > 3 else 20
+if cname == "custom":     # QB_CFG=model,H,L,S,B,V
+    mo, H_, L_, S_, B_, V_ = os.environ["QB_CFG"].split(",")
+    BN.CONFIGS["custom"] = dict(model=mo, rnn_size=int(H_), num_layers=int(L_), seq_length=int(S_), batch_size=int(B_), vocab_size=int(V_), desc="custom")
 c = BN.CONFIGS[cname]
 margs = argparse.Namespace(grad_clip=5.0, output_keep_prob=1.0, input_keep_prob=1.0, **{k: v for k, v in c.items() if k != "desc"})
 B, S = c["batch_size"], c["seq_length"]
