@@ -382,6 +382,13 @@ def hbm_phases(c, phases, P, pk, nsp=2):
         by.pop("softmax_xent", None)
         by["logits_gemm"] = SB * c["rnn_size"] * 2 * nsp + SB * Vp * 2 * nsp + SB * 4
     out = {}
+    if phases.get("xproj_gemm", 0.0) < 1e-6 and c["num_layers"] > 1 and "embed_scatter" in by:
+        # layer wavefront: the sorted embedding scatter runs on a side stream beside the last weight-gradient GEMMs (crnn_api.cu:
+        # early_scatter); what is left of its phase on the main stream is one scalar kernel, not the bytes - no live figure
+        # (profiles/r02_ncu_hbm_c3.txt has the kernel alone: 52.7 MB in 23.4 us cold)
+        b = by.pop("embed_scatter")
+        out["embed_scatter"] = {"ms": None, "algorithmic_bytes": b, "achieved_gbs": None, "frac": None,
+                                "note": "overlapped with the weight-gradient GEMMs on a side stream; see profiles/r02_ncu_hbm_c3.txt"}
     for name, b in by.items():
         ms = phases.get(name, 0.0)
         if ms > 1e-6:

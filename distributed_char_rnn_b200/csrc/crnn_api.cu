@@ -793,7 +793,7 @@ static int scatter_and_finalize(crnn_handle* h, const int32_t* x, int64_t ld, co
     const crnn_config& c = h->cfg;
     const int H = c.rnn_size, V = c.vocab_size, S = c.seq_length, B = c.batch_size;
     const int64_t SB = (int64_t)S * B;
-    prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
+    if (nloss >= 0) prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);      // (nloss < 0: on a side stream, outside the phase profile)
     if (h->ws.es_sorted) {                            // (the token order was built by scatter_sort, early in the step)
         const int nchunk = ceil_div(H, 4 * ES_SUM_THREADS);
         const int* order = reinterpret_cast<const int*>((char*)ws + h->ws.es_order);
@@ -826,6 +826,7 @@ static int scatter_and_finalize(crnn_handle* h, const int32_t* x, int64_t ld, co
         embed_scatter_kernel<<<grid_for(SB * H, h->sm_count), 256, 0, st>>>(grads + h->emb_off, V, H, x, ld, B, S, dX, ws_sq(ws));
         CRNN_LAUNCH_CHECK("embed_scatter_kernel");
     }
+    if (nloss < 0) return CRNN_OK;                    // (scatter only: the caller finalises after joining its streams)
     finalize_scalars_kernel<<<1, 256, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P, ws_loss_part(ws), nloss);
     CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
     return CRNN_OK;
@@ -1518,6 +1519,15 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             }
         }
     }
+    // The embedding scatter needs layer 0's input gradients only, which are complete a whole set of weight-gradient GEMMs
+    // before the join: it runs on the side stream beside those GEMMs (HBM-bound next to tensor-bound work).
+    const bool early_scatter = wf && !hoist0 && h->ws.es_sorted;
+    if (early_scatter) {
+        rc = wf_wait(h, wf_id(h, 3, 0, 0), h->aux_stream);           // layer 0's last input-gradient chunk (chunk 0)
+        if (rc == CRNN_OK) rc = scatter_and_finalize(h, x, ld, wsf(ws, h->ws.gx0), grads, ws, -1, h->aux_stream);
+        if (rc == CRNN_OK) rc = wf_record(h, ev_sort + 1, h->aux_stream);
+        if (rc != CRNN_OK) return rc;
+    }
     rc = wf_join(h, st, 2 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
     if (hoist0) {                                    // layer 0's input gradients for the whole sequence
@@ -1534,9 +1544,15 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
         if (rc == CRNN_OK && drop) rc = drop_apply(h, call, 0, dn, dn, nullptr, 0, SB * H, st);
         if (rc != CRNN_OK) return rc;
     }
-    if (h->ws.es_sorted) { rc = wf_wait(h, ev_sort + 1, st); if (rc != CRNN_OK) return rc; }
-    rc = scatter_and_finalize(h, x, ld, wsf(ws, h->ws.gx0), grads, ws, nloss, st);
-    if (rc != CRNN_OK) return rc;
+    if (h->ws.es_sorted) { rc = wf_wait(h, ev_sort + 1, st); if (rc != CRNN_OK) return rc; }   // the token order, or the whole early scatter
+    if (early_scatter) {
+        prof_mark(h, st, CRNN_PHASE_EMBED_SCATTER);
+        finalize_scalars_kernel<<<1, 256, 0, st>>>(ws_sq(ws), ws_loss(ws), (double)SB, grads + h->P, ws_loss_part(ws), nloss);
+        CRNN_LAUNCH_CHECK("finalize_scalars_kernel");
+    } else {
+        rc = scatter_and_finalize(h, x, ld, wsf(ws, h->ws.gx0), grads, ws, nloss, st);
+        if (rc != CRNN_OK) return rc;
+    }
     prof_mark(h, st, -1);
     return CRNN_OK;
 }
