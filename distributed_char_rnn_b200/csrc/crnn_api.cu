@@ -96,6 +96,7 @@ struct crnn_handle {
     int wf_W, wf_C;
     std::vector<cudaStream_t> wf_streams;
     cudaStream_t aux_stream = nullptr;   // small id-only work that runs beside the step (the scatter's token sort)
+    int persist = 0;                     // wavefront with ONE recurrence launch per layer and direction (chunk flags + stream memory operations)
     std::vector<cudaEvent_t> wf_events;
     // dropout (training calls only): keep probabilities, seed, and the count of training calls so far
     float ikp, okp;
@@ -169,6 +170,33 @@ static const float kBeta1 = 0.9f, kBeta2 = 0.999f, kEps = 1e-8f;
 static const size_t kScratchBytes = 32768 + 512 * 256;   // 512 barrier blocks after the first 32 KB
 // one 256-byte block of barrier counters per recurrence launch (2 per layer), after the first 8 KB
 static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>((char*)ws + 32768 + (size_t)i * 256); }
+// Persistent form of the wavefront (one recurrence launch per layer and direction): chunk flags of (direction, layer) in the
+// barrier blocks 448..511 - word 0: "the chunk's batch GEMM is done" (written by a stream memory operation, read by the
+// kernel), word 32: chunks finished, summed over the kernel's CTAs (read by cuStreamWaitValue32).  Zeroed with the blocks.
+static inline unsigned* ws_pflag(void* ws, int dir, int l) { return ws_barrier(ws, 448 + dir * 32 + l); }
+typedef CUresult (*StreamValueFn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static StreamValueFn stream_value_fn(bool write) {
+    static StreamValueFn fn[2] = {nullptr, nullptr};
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        const char* names[2] = {"cuStreamWaitValue32", "cuStreamWriteValue32"};
+        for (int i = 0; i < 2; ++i) {
+            void* p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint(names[i], &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn[i] = (StreamValueFn)p;
+        }
+    }
+    return fn[write ? 1 : 0];
+}
+static int wf_wait_value(cudaStream_t s, unsigned* addr, unsigned v) {       // stream s continues once *addr >= v
+    const CUresult r = stream_value_fn(false)((CUstream)s, (CUdeviceptr)(uintptr_t)addr, v, CU_STREAM_WAIT_VALUE_GEQ);
+    return r == CUDA_SUCCESS ? CRNN_OK : set_err(CRNN_ERR_CUDA, "cuStreamWaitValue32 failed (%d)", (int)r);
+}
+static int wf_write_value(cudaStream_t s, unsigned* addr, unsigned v) {      // *addr = v once the stream's earlier work is done
+    const CUresult r = stream_value_fn(true)((CUstream)s, (CUdeviceptr)(uintptr_t)addr, v, CU_STREAM_WRITE_VALUE_DEFAULT);
+    return r == CUDA_SUCCESS ? CRNN_OK : set_err(CRNN_ERR_CUDA, "cuStreamWriteValue32 failed (%d)", (int)r);
+}
 static inline double* ws_loss(void* ws) { return reinterpret_cast<double*>((char*)ws + 256); }
 static inline double* ws_sq(void* ws) { return reinterpret_cast<double*>((char*)ws + 264); }
 static inline double* ws_partials(void* ws) { return reinterpret_cast<double*>((char*)ws + 1024); }
@@ -630,6 +658,17 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             }
         }
     }
+    // One launch per layer and direction instead of one per chunk (each launch costs ~10 us: set-up, resident weights,
+    // the gap to the next kernel): needs the driver's stream memory operations; not with the direct exchange, whose
+    // launches pre-fill the next launch's slots.  CRNN_WF_PERSIST=0: a launch per chunk, ordered by events.
+    // Measured (ms per step, split precision): config 1 0.60 -> 0.56; config 3 4.21 -> 4.51 - its two resident kernels leave
+    // the chunk GEMMs 20 SMs for the whole pass, where a launch per chunk lets them use the SMs between launches -, so the
+    // default is on only while all recurrence CTAs of the wavefront take at most half of the SMs.
+    h->persist = 0;
+    if (rc == CRNN_OK && h->tc && h->wf_W > 1 && h->wf_C > 1 && !h->tcp.gather && stream_value_fn(false) && stream_value_fn(true)) {
+        const bool small = h->wf_W * h->tcp.nslices * h->tcp.ntiles * 2 <= h->sm_count;
+        h->persist = env_int("CRNN_WF_PERSIST", small ? 1 : 0) ? 1 : 0;
+    }
     if (rc == CRNN_OK && h->tc) {
         if (cudaHostAlloc((void**)&h->err_word, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); rc = set_err(CRNN_ERR_CUDA, "cudaHostAlloc failed"); }
         else *h->err_word = 0u;
@@ -639,9 +678,9 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     build_workspace(h);
     if (env_int("CRNN_VERBOSE", 0) && h->tc)
         fprintf(stderr, "[crnn] plan: HC %d BT %d slices %d tiles %d passes %d x %d rows%s, K split fwd/bwd %d/%d, ring %d/%d KB, smem %zu/%zu, "
-                "wavefront %d layers x %d chunks, workspace %.1f MB\n", h->tcp.HC, h->tcp.BT, h->tcp.nslices, h->tcp.ntiles, h->tcp.npass, h->tcp.pr,
+                "wavefront %d layers x %d chunks%s, workspace %.1f MB\n", h->tcp.HC, h->tcp.BT, h->tcp.nslices, h->tcp.ntiles, h->tcp.npass, h->tcp.pr,
                 h->tcp.sub ? " (sub-chains)" : (h->tcp.cx_fwd && h->tcp.cx_bwd ? " (cluster exchange)" : h->tcp.cx_fwd ? " (cluster exchange forward)" : h->tcp.cx_bwd ? " (cluster exchange backward)" : ""), h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
-                h->tcp.smem_bwd, h->wf_W, h->wf_C, h->ws.total / 1e6);
+                h->tcp.smem_bwd, h->wf_W, h->wf_C, h->persist ? " (one launch per layer and direction)" : "", h->ws.total / 1e6);
     *out = h;
     return CRNN_OK;
 }
@@ -1283,11 +1322,13 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
                 if (c.model == CRNN_MODEL_GRU) CRNN_CUDA(cudaMemsetAsync(wsb(ws, h->ws.rsb[l]) + half * lo.act, 0xFF, n0 * sizeof(bf16_t), s));
             }
         }
+        const bool persist = wf && h->persist;
+        const unsigned nctas = (unsigned)(h->tcp.nslices * h->tcp.ntiles);
         for (int ck = 0; ck < C; ++ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
             if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
-                rc = wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
+                rc = persist ? wf_wait_value(gs, ws_pflag(ws, 0, l - 1) + 32, (unsigned)(ck + 1) * nctas) : wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }
             const bool hoisted = hoist0 && l == 0;   // done above for the whole sequence
@@ -1310,17 +1351,26 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
                 rc = gemm_tc(h, rows, GH, H, ain, H, 0, in_lo, pbf + lp.oW, GH, 1, lo.pbf, gch, gw, lp.b, 0, gs);
             }
             if (rc != CRNN_OK) return rc;
-            if (wf) {
+            if (persist) {                           // the kernel (launched below, once) reads the flag at the chunk's first step
+                if (!hoisted) { rc = wf_write_value(gs, ws_pflag(ws, 0, l), (unsigned)(ck + 1)); if (rc != CRNN_OK) return rc; }
+                if (ck == 0) {                       // the launch itself waits for the first chunk: a kernel that only spins would keep its SMs from the chunk GEMMs
+                    rc = wf_record(h, wf_id(h, 1, l, 0), gs);
+                    if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 1, l, 0), s);
+                    if (rc != CRNN_OK) return rc;
+                }
+                if (ck + 1 < C) continue;
+            } else if (wf) {
                 rc = wf_record(h, wf_id(h, 1, l, ck), gs);
                 if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 1, l, ck), s);
                 if (rc != CRNN_OK) return rc;
             }
             tc::RecTcArgs a{};
-            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
+            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = persist ? 0 : t0; a.t_end = persist ? S : t1;
             a.gates = gates; a.hx = hx; a.cx = cx; a.hxb = hxb;
             a.rsb = c.model == CRNN_MODEL_GRU ? wsb(ws, h->ws.rsb[l]) : nullptr;
             a.fill_t0 = t1; a.fill_t1 = ck + 1 < C ? wf_t0(h, ck + 2) : t1;
-            a.barrier = ws_barrier(ws, l * C + ck);
+            a.barrier = ws_barrier(ws, persist ? l * C : l * C + ck);
+            if (persist) { a.pchunks = C; a.in_flag = hoisted ? nullptr : ws_pflag(ws, 0, l); a.out_flag = ws_pflag(ws, 0, l) + 32; }
             if (!wf) prof_mark(h, st, CRNN_PHASE_REC_FWD);
             rc = launch_rec_tc_model(h, false, a, nullptr, nullptr, wsb(ws, h->ws.wr[l]), s);
             if (rc != CRNN_OK) return rc;
@@ -1441,24 +1491,34 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             for (int half = 0; half <= h->split; ++half)
                 CRNN_CUDA(cudaMemsetAsync(dzb + r0 + half * lo.dzb, 0xFF, n0 * sizeof(bf16_t), s));
         }
+        const bool persist = wf && h->persist;
+        const unsigned nctas = (unsigned)(h->tcp.nslices * h->tcp.ntiles);
         for (int ck = C - 1; ck >= 0; --ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
-            if (wf && l < L - 1) {                   // layer l+1 has produced this chunk's output gradients
-                rc = wf_wait(h, wf_id(h, 3, l + 1, ck), s);
+            if (wf && (!persist || ck == C - 1) && l < L - 1) {   // layer l+1 has produced this chunk's output gradients
+                rc = wf_wait(h, wf_id(h, 3, l + 1, ck), s);         // (persistent form: the launch waits for the first chunk only)
                 if (rc != CRNN_OK) return rc;
             }
-            tc::RecTcArgs a{};
-            a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = t0; a.t_end = t1;
-            a.gates = gates; a.hx = hx; a.cx = cx;
-            a.dy = wsf(ws, h->ws.gout[l]); a.dz = dz; a.dzb = dzb;
-            a.carry0 = wsf(ws, h->ws.carry0v[l]); a.carry1 = wsf(ws, h->ws.carry1v[l]);
-            a.fill_t0 = ck > 0 ? wf_t0(h, ck - 1) : t0; a.fill_t1 = t0;
-            a.barrier = ws_barrier(ws, L * C + l * C + ck);
-            if (!wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
-            rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, s);
-            if (rc != CRNN_OK) return rc;
-            if (wf) {
+            if (!persist || ck == C - 1) {           // persistent form: ONE launch for the whole sequence, before the chunk GEMMs that follow it
+                tc::RecTcArgs a{};
+                a.B = B; a.H = H; a.S = S; a.GS = h->GS; a.t_begin = persist ? 0 : t0; a.t_end = persist ? S : t1;
+                a.gates = gates; a.hx = hx; a.cx = cx;
+                a.dy = wsf(ws, h->ws.gout[l]); a.dz = dz; a.dzb = dzb;
+                a.carry0 = wsf(ws, h->ws.carry0v[l]); a.carry1 = wsf(ws, h->ws.carry1v[l]);
+                a.fill_t0 = ck > 0 ? wf_t0(h, ck - 1) : t0; a.fill_t1 = t0;
+                a.barrier = ws_barrier(ws, persist ? L * C + l * C : L * C + l * C + ck);
+                if (persist) {   // dy of chunk k (processing order) is there when the layer above's GEMM stream has written k + 1
+                    a.pchunks = C; a.in_flag = l < L - 1 ? ws_pflag(ws, 1, l) : nullptr; a.out_flag = ws_pflag(ws, 1, l) + 32;
+                }
+                if (!wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
+                rc = launch_rec_tc_model(h, true, a, pbf + lp.oW, c.model == CRNN_MODEL_GRU ? pbf + lp.oWc : nullptr, nullptr, s);
+                if (rc != CRNN_OK) return rc;
+            }
+            if (persist) {                           // the chunk's dz rows: every CTA of the kernel has finished the chunk
+                rc = wf_wait_value(gs, ws_pflag(ws, 1, l) + 32, (unsigned)(C - ck) * nctas);
+                if (rc != CRNN_OK) return rc;
+            } else if (wf) {
                 rc = wf_record(h, wf_id(h, 2, l, ck), s);
                 if (rc == CRNN_OK) rc = wf_wait(h, wf_id(h, 2, l, ck), gs);
                 if (rc != CRNN_OK) return rc;
@@ -1478,6 +1538,10 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             }
             if (rc == CRNN_OK && drop) rc = drop_apply(h, call, l, dn, dn, nullptr, (int64_t)t0 * BH, (int64_t)rows * H, gs);
             if (rc != CRNN_OK) return rc;
+            if (persist && l > 0) {                  // the layer below reads its dy chunk once this is written
+                rc = wf_write_value(gs, ws_pflag(ws, 1, l - 1), (unsigned)(C - ck));
+                if (rc != CRNN_OK) return rc;
+            }
             if (wf) {
                 rc = wf_record(h, wf_id(h, 3, l, ck), gs);
                 if (rc != CRNN_OK) return rc;

@@ -70,6 +70,15 @@ struct RecTcArgs {
     int swap;                   // 1: weights are the MMA A operand (M), batch rows the N dimension
     int ksplit;                 // Q: the contraction index is split over Q CTAs of a cluster; each contracts the columns of Q*HC
                                 // units over 1/Q of K and the partial sums are exchanged through distributed shared memory
+    // One launch per layer and direction (pchunks > 0): the launch covers the whole sequence, cut into pchunks chunks for
+    // the layer wavefront.  Before the first step of chunk k (in processing order) the kernel waits until *in_flag >= k + 1 -
+    // written by a stream memory operation that follows the chunk's batch GEMM (hoisted x-projection forward, input gradients
+    // of the layer above backward) on a stream whose work was enqueued BEFORE this launch -, and after the last step of a
+    // chunk every CTA adds 1 to *out_flag, which the next layer's GEMM stream waits for (cuStreamWaitValue32).  No launch
+    // ever waits for work enqueued after it; the waits are bounded and report through `err`.
+    int pchunks;
+    const unsigned* in_flag;
+    unsigned* out_flag;
     int xchg;                   // 1: cluster exchange - the cluster holds ALL slices of a batch tile and every slice writes the bf16 rows it
                                 // finishes straight into the operand buffers of all slices (distributed shared memory), see cx_push
     int cbar;                   // 1: the cluster holds ALL slices of a batch tile: steps are ordered by remote mbarrier arrives, no global counter
@@ -623,6 +632,24 @@ __device__ __forceinline__ void rt_await(const unsigned* counter, unsigned targe
     asm volatile("fence.proxy.async;" ::: "memory");
 }
 
+// Persistent form: wait for the chunk flag (see RecTcArgs::pchunks).  One thread per CTA; bounded (~4 s), false on expiry.
+__device__ __forceinline__ bool rt_wait_chunk(const unsigned* flag, unsigned target, unsigned* err) {
+    unsigned v, spins = 0;
+    unsigned long long t0 = 0;
+    for (;;) {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v >= target) return true;
+        __nanosleep(128);
+        if ((++spins & 255u) == 0u) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000ull) { if (err) *err = 1u; return false; }
+        }
+    }
+}
+__device__ __forceinline__ int rt_chunk_t0(int S, int c, int C) { return (int)((long long)S * c / C); }
+
 // Accumulator -> shared Zs[r*ldz + c] for batch rows r < nr and gate columns c < nc (ldz odd).
 // A warp can only read its own TMEM lane quarter; quarters holding nothing useful skip the load.
 // pair != 0: the accumulator holds two column halves [0, nc) and [nc, 2nc) whose sum is the result (split operands).
@@ -960,7 +987,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
         }
         const RtGatherGeom gg{smem_u32(s.ring), smem_u32(s.a_full), smem_u32(s.a_valid), nsp, rt_tile_bytes(a.box_rows), a.g_ckb_log2, a.g_rp_log2, a.nst, a.expt, a.err};
         uint32_t gpos = 0;                            // ring position of the gather (stage | phase bit << 16)
+        int pck = 0;                                  // persistent form: chunk in progress
+        bool pdead = false;
         for (int t = a.t_begin; t < a.t_end; ++t) {
+            if (a.pchunks && t == rt_chunk_t0(a.S, pck, a.pchunks)) {   // first step of a chunk: its hoisted x-projection must be in place
+                if (a.in_flag && epi_tid == 0 && !pdead) pdead = !rt_wait_chunk(a.in_flag, (unsigned)pck + 1u, a.err);
+                epi_bar_sync();
+            }
             const int64_t tB = (int64_t)t * B;
             float* gt = a.gates;
             const float* hprev = a.hx + (int64_t)t * BH;
@@ -1141,6 +1174,11 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
                 pending = false;
                 if (epi_tid == 0) RT_STAMP(13);
                 }   // passes
+            }
+            if (a.pchunks && t + 1 == rt_chunk_t0(a.S, pck + 1, a.pchunks)) {   // the chunk is complete on this CTA (all its stores issued)
+                epi_bar_sync();
+                if (epi_tid == 0 && a.out_flag) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.out_flag) : "memory");
+                ++pck;
             }
         }
     }
@@ -1330,7 +1368,13 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 a.carry0[(int64_t)(b0 + r) * H + j0 + jj] = 0.f;
             }
         }
+        int pck = 0;                                  // persistent form: chunks done (they are processed last to first)
+        bool pdead = false;
         for (int t = a.t_end - 1; t >= a.t_begin; --t) {
+            if (a.pchunks && t == rt_chunk_t0(a.S, a.pchunks - pck, a.pchunks) - 1) {   // first processed step of a chunk: its dy must be in place
+                if (a.in_flag && epi_tid == 0 && !pdead) pdead = !rt_wait_chunk(a.in_flag, (unsigned)pck + 1u, a.err);
+                epi_bar_sync();
+            }
             const bool has_next = t + 1 < a.S;
             const int64_t tB = (int64_t)t * B;
             // Same split as the forward epilogue: only the bf16 dz rows other CTAs stream next are stored before the
@@ -1580,6 +1624,11 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
                 }
                 pending = false;
                 }   // passes
+            }
+            if (a.pchunks && t == rt_chunk_t0(a.S, a.pchunks - 1 - pck, a.pchunks)) {   // the chunk is complete on this CTA
+                epi_bar_sync();
+                if (epi_tid == 0 && a.out_flag) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.out_flag) : "memory");
+                ++pck;
             }
         }
     }

@@ -140,6 +140,12 @@ SHAPES = [
     # LSTM slices of 8 units (what config 4 needs in split precision): M = 64 tiles, 128-row tiles with the K split, exchange off
     ("lstm", 64, 2, 6, 20, 13, {"CRNN_TC_HC": 8}), ("lstm", 128, 1, 5, 100, 13, {"CRNN_TC_HC": 8, "CRNN_TC_KSPLIT": 2, "CRNN_TC_TILES": 1}),
     ("lstm", 64, 2, 6, 20, 13, {"CRNN_TC_HC": 8, "CRNN_TC_CX": 0}),
+    # embedding scatter: the per-CTA table form (the sorted form is the default), and a vocabulary above the fused projection's 256
+    ("gru", 64, 2, 6, 40, 13, {"CRNN_ES_SORT": 0}), ("lstm", 32, 1, 5, 9, 300, {}), ("rnn", 48, 2, 70, 3, 11, {}),
+    # wavefront with one launch per layer and direction (chunk flags + stream memory operations; the default while the
+    # recurrence CTAs take at most half of the SMs) forced on at config 3's layers, forced off at small ones, three layers
+    ("gru", 512, 2, 12, 64, 96, {"CRNN_WF_PERSIST": 1}), ("lstm", 128, 2, 12, 50, 65, {"CRNN_WF_PERSIST": 0, "CRNN_WAVEFRONT_CHUNKS": 3}),
+    ("gru", 64, 3, 9, 20, 17, {"CRNN_WAVEFRONT_CHUNKS": 4}), ("rnn", 64, 2, 9, 21, 13, {"CRNN_WF_PERSIST": 1, "CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 9}),
 ]
 
 

@@ -141,6 +141,8 @@ BF16_SHAPES = [
     ("rnn", 64, 2, 9, 21, 13, {"CRNN_WAVEFRONT_CHUNKS": 2}), ("gru", 256, 1, 6, 90, 13, {}),
     ("lstm", 128, 2, 12, 50, 65, {"CRNN_TC_CX": 0}), ("gru", 64, 2, 8, 20, 17, {"CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 4}),
     ("lstm", 64, 2, 6, 20, 13, {"CRNN_TC_HC": 8}),          # LSTM slices of 8 units
+    # one launch per layer and direction forced on (config 3's layers) / off (small layers)
+    ("gru", 512, 2, 12, 64, 96, {"CRNN_WF_PERSIST": 1}), ("lstm", 128, 2, 12, 50, 65, {"CRNN_WF_PERSIST": 0, "CRNN_WAVEFRONT_CHUNKS": 3}),
 ]
 
 
