@@ -299,10 +299,11 @@ static int plan_recurrence_tc(const crnn_handle* h, int max_ctas, RecPlanTc* out
                 if (env == 0 && Qc == 2 && ncols_per_unit > 1) continue;
                 if (H % (64 * Qc) != 0 || H % (HC * Qc) != 0 || nslices % Qc != 0) continue;
                 if (ncols_per_unit * HC * Qc > (h->split ? 128 : 256)) continue;   // split: the MMA's N is twice the columns
-                // the partial sums' staging area grows with Q: give it ring space down to 32 KB (the K extent per CTA shrinks
-                // Q-fold as well, so a stage still holds several K blocks)
+                // (the partial sums' staging area grows with Q; taking ring space for it does not pay: config 5 in plain bf16 with
+                //  Q = 4 and a 32 KB ring 71.4 ms per step against 66.0 with Q = 2 and 64 KB - CRNN_TC_RING_MIN_KB for experiments)
                 int rb = tc::RT_RING_BYTES;
-                while (rb > 32 * 1024 && (int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) rb -= 16 * 1024;
+                const int rb_min = std::max(16, env_int("CRNN_TC_RING_MIN_KB", 64)) * 1024;
+                while (rb > rb_min && (int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) rb -= 16 * 1024;
                 if ((int)tc::rt_smem_bytes(wbytes, 0, rows * (ncols_per_unit * HC * Qc + 1), rb, dbg) > h->max_smem) continue;
                 if (tc::rt_num_stages(o->box_rows, 1, h->split, rb) < 2) continue;      // the ring must still hold two stages
                 *ring = rb;
@@ -661,13 +662,15 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     // One launch per layer and direction instead of one per chunk (each launch costs ~10 us: set-up, resident weights,
     // the gap to the next kernel): needs the driver's stream memory operations; not with the direct exchange, whose
     // launches pre-fill the next launch's slots.  CRNN_WF_PERSIST=0: a launch per chunk, ordered by events.
-    // Measured (ms per step, split precision): config 1 0.60 -> 0.56; config 3 4.21 -> 4.51 - its two resident kernels leave
-    // the chunk GEMMs 20 SMs for the whole pass, where a launch per chunk lets them use the SMs between launches -, so the
-    // default is on only while all recurrence CTAs of the wavefront take at most half of the SMs.
+    // Measured (ms per step, split precision): config 1 0.60 -> 0.56 with both directions in this form; config 3 4.21 ->
+    // 4.51 with both - in the forward pass its two resident kernels leave the chunk GEMMs 20 SMs all the time, where a launch
+    // per chunk lets them use the SMs between launches - but 4.21 -> 4.14 (bf16: 3.04 -> 2.97) with BPTT alone.  Default:
+    // both directions while all recurrence CTAs of the wavefront take at most half of the SMs, else BPTT only.
     h->persist = 0;
     if (rc == CRNN_OK && h->tc && h->wf_W > 1 && h->wf_C > 1 && !h->tcp.gather && stream_value_fn(false) && stream_value_fn(true)) {
         const bool small = h->wf_W * h->tcp.nslices * h->tcp.ntiles * 2 <= h->sm_count;
-        h->persist = env_int("CRNN_WF_PERSIST", small ? 1 : 0) ? 1 : 0;
+        const int pe = env_int("CRNN_WF_PERSIST", small ? 1 : 2);          // 1: both directions, 2: BPTT only, 3: forward only
+        h->persist = pe == 1 ? 3 : (pe == 2 ? 2 : (pe == 3 ? 1 : 0));          // bit 0: forward, bit 1: BPTT
     }
     if (rc == CRNN_OK && h->tc) {
         if (cudaHostAlloc((void**)&h->err_word, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); rc = set_err(CRNN_ERR_CUDA, "cudaHostAlloc failed"); }
@@ -680,7 +683,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         fprintf(stderr, "[crnn] plan: HC %d BT %d slices %d tiles %d passes %d x %d rows%s, K split fwd/bwd %d/%d, ring %d/%d KB, smem %zu/%zu, "
                 "wavefront %d layers x %d chunks%s, workspace %.1f MB\n", h->tcp.HC, h->tcp.BT, h->tcp.nslices, h->tcp.ntiles, h->tcp.npass, h->tcp.pr,
                 h->tcp.sub ? " (sub-chains)" : (h->tcp.cx_fwd && h->tcp.cx_bwd ? " (cluster exchange)" : h->tcp.cx_fwd ? " (cluster exchange forward)" : h->tcp.cx_bwd ? " (cluster exchange backward)" : ""), h->tcp.q_fwd, h->tcp.q_bwd, h->tcp.ring_fwd / 1024, h->tcp.ring_bwd / 1024, h->tcp.smem_fwd,
-                h->tcp.smem_bwd, h->wf_W, h->wf_C, h->persist ? " (one launch per layer and direction)" : "", h->ws.total / 1e6);
+                h->tcp.smem_bwd, h->wf_W, h->wf_C, h->persist == 3 ? " (one launch per layer and direction)" : h->persist == 2 ? " (BPTT: one launch per layer)" : h->persist == 1 ? " (forward: one launch per layer)" : "", h->ws.total / 1e6);
     *out = h;
     return CRNN_OK;
 }
@@ -1322,7 +1325,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
                 if (c.model == CRNN_MODEL_GRU) CRNN_CUDA(cudaMemsetAsync(wsb(ws, h->ws.rsb[l]) + half * lo.act, 0xFF, n0 * sizeof(bf16_t), s));
             }
         }
-        const bool persist = wf && h->persist;
+        const bool persist = wf && (h->persist & 1);
         const unsigned nctas = (unsigned)(h->tcp.nslices * h->tcp.ntiles);
         for (int ck = 0; ck < C; ++ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
@@ -1491,7 +1494,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
             for (int half = 0; half <= h->split; ++half)
                 CRNN_CUDA(cudaMemsetAsync(dzb + r0 + half * lo.dzb, 0xFF, n0 * sizeof(bf16_t), s));
         }
-        const bool persist = wf && h->persist;
+        const bool persist = wf && (h->persist & 2);
         const unsigned nctas = (unsigned)(h->tcp.nslices * h->tcp.ntiles);
         for (int ck = C - 1; ck >= 0; --ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
