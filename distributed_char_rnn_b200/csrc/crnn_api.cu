@@ -94,6 +94,7 @@ struct crnn_handle {
     RecPlanTc tcp;
     // wavefront over layers (tensor path): wf_W layer streams, each sequence cut into wf_C chunks
     int wf_W, wf_C;
+    int wf_Cb;                           // chunks of the BPTT wavefront (CRNN_WAVEFRONT_CHUNKS_BWD; default: as forward)
     std::vector<cudaStream_t> wf_streams;
     cudaStream_t aux_stream = nullptr;   // small id-only work that runs beside the step (the scatter's token sort)
     int persist = 0;                     // wavefront with ONE recurrence launch per layer and direction (chunk flags + stream memory operations)
@@ -171,8 +172,9 @@ static const size_t kScratchBytes = 32768 + 512 * 256;   // 512 barrier blocks a
 // one 256-byte block of barrier counters per recurrence launch (2 per layer), after the first 8 KB
 static inline unsigned* ws_barrier(void* ws, int i) { return reinterpret_cast<unsigned*>((char*)ws + 32768 + (size_t)i * 256); }
 // Persistent form of the wavefront (one recurrence launch per layer and direction): chunk flags of (direction, layer) in the
-// barrier blocks 448..511 - word 0: "the chunk's batch GEMM is done" (written by a stream memory operation, read by the
-// kernel), word 32: chunks finished, summed over the kernel's CTAs (read by cuStreamWaitValue32).  Zeroed with the blocks.
+// barrier blocks 448..511 - word 0: "the batch GEMMs of chunks 0..v-1 are done" (written by a stream memory operation, read by
+// the kernel), words 32..63: per chunk (in processing order), the number of CTAs that have finished it (read by
+// cuStreamWaitValue32; at most 32 chunks).  Zeroed with the blocks.
 static inline unsigned* ws_pflag(void* ws, int dir, int l) { return ws_barrier(ws, 448 + dir * 32 + l); }
 typedef CUresult (*StreamValueFn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 static StreamValueFn stream_value_fn(bool write) {
@@ -619,7 +621,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
                        env_int("CRNN_TC_CKB", 0), env_int("CRNN_TC_ROTATE", 0), env_int("CRNN_TC_MIN_STAGES", 2), env_int("CRNN_TC_3D", 1),
                        env_int("CRNN_TC_UB8", 1), env_int("CRNN_TC_DEFER", 1), env_int("CRNN_TC_ACQ_POLL", 1), env_int("CRNN_TC_EXPT", 0),
                        env_int("CRNN_TC_VEC4", -1), env_int("CRNN_TC_CBAR", 8), env_int("CRNN_WF_HOIST0", 0), env_int("CRNN_FUSE_PROJ", 1)};
-    h->wf_W = 1; h->wf_C = 1;
+    h->wf_W = 1; h->wf_C = 1; h->wf_Cb = 1;
     if (rc == CRNN_OK && h->tc) {
         // Layers are independent chains once their inputs exist: run up to W of them at once, each on
         // 1/W of the SMs, the sequence cut into C chunks so layer l+1 starts when layer l has produced
@@ -646,6 +648,9 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
             if (W == 1 && c_env <= 0) C = 1;                 // (chunks without overlap only on request: measures the cost of a launch)
             h->wf_C = C;
             while (C > 1 && 2 * cfg->num_layers * C > 384) --C, h->wf_C = C;   // barrier blocks 0..383
+            h->wf_Cb = h->wf_C;
+            { const int cb = env_int("CRNN_WAVEFRONT_CHUNKS_BWD", 0);
+              if (cb > 0 && W > 1 && cfg->num_layers * (h->wf_C + std::min(cb, cfg->seq_length)) <= 384) h->wf_Cb = std::min(std::min(cb, cfg->seq_length), 32); }
             for (int i = 0; i < 2 * W && W > 1; ++i) {      // [0,W): recurrence streams, [W,2W): GEMM streams
                 cudaStream_t s;
                 // The recurrence launches are the step's critical path and need a whole set of free SMs each (cooperative);
@@ -671,6 +676,13 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
         const bool small = h->wf_W * h->tcp.nslices * h->tcp.ntiles * 2 <= h->sm_count;
         const int pe = env_int("CRNN_WF_PERSIST", small ? 1 : 2);          // 1: both directions, 2: BPTT only, 3: forward only
         h->persist = pe == 1 ? 3 : (pe == 2 ? 2 : (pe == 3 ? 1 : 0));          // bit 0: forward, bit 1: BPTT
+        // Chunks cost no launch in this form, so BPTT of the large wavefronts is cut finer (less skew between the layers):
+        // config 3, ms per step at 10 / 20 / 25 / 32 chunks: 4.16 / 4.13 / 4.09 / 4.15 (config 1 prefers its 5).
+        if ((h->persist & 2) && !small && env_int("CRNN_WAVEFRONT_CHUNKS_BWD", 0) <= 0) {
+            int cb = std::max(h->wf_C, std::min(32, cfg->seq_length / 4));
+            while (cb > h->wf_C && cfg->num_layers * (h->wf_C + cb) > 384) --cb;
+            h->wf_Cb = cb;
+        }
     }
     if (rc == CRNN_OK && h->tc) {
         if (cudaHostAlloc((void**)&h->err_word, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); rc = set_err(CRNN_ERR_CUDA, "cudaHostAlloc failed"); }
@@ -1331,7 +1343,7 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
             if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
-                rc = persist ? wf_wait_value(gs, ws_pflag(ws, 0, l - 1) + 32, (unsigned)(ck + 1) * nctas) : wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
+                rc = persist ? wf_wait_value(gs, ws_pflag(ws, 0, l - 1) + 32 + ck, nctas) : wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }
             const bool hoisted = hoist0 && l == 0;   // done above for the whole sequence
@@ -1427,7 +1439,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     const int64_t BH = (int64_t)B * H, SB = (int64_t)S * B;
     const int gw = h->GS * H, zw = h->GZ * H, Vp = h->Vp;
     const int sc = h->sm_count;
-    const int C = h->wf_C;
+    int C = h->wf_C;                             // chunks of the forward wavefront; the BPTT count from the fork below on
     const bool wf = h->wf_W > 1;
     prof_mark(h, st, CRNN_PHASE_MISC);
     CRNN_CUDA(cudaMemsetAsync(grads, 0, (h->P + CRNN_GRAD_TAIL) * sizeof(float), st));
@@ -1473,6 +1485,11 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
     // l+1 has turned that chunk's dz into input gradients; "rec_bwd" then times the whole fork..join
     // span (recurrences + interleaved input-gradient GEMMs), weight gradients included at its tail.
     const bool hoist0 = wf && h->env.hoist0;     // see run_forward_bf16
+    // BPTT may use its own chunk count: the helpers (wf_t0, wf_id, fork / join slots) read h->wf_C, restored on every exit
+    struct ChunkGuard { crnn_handle* h; int saved; ~ChunkGuard() { h->wf_C = saved; } } chunk_guard{h, h->wf_C};
+    const int Cf = h->wf_C;                      // the forward count: its barrier blocks 0 .. L*Cf-1 are used up
+    C = h->wf_Cb;
+    h->wf_C = C;
     if (wf) prof_mark(h, st, CRNN_PHASE_REC_BWD);
     rc = wf_fork(h, st, 1 + 2 * h->wf_W);
     if (rc != CRNN_OK) return rc;
@@ -1510,7 +1527,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
                 a.dy = wsf(ws, h->ws.gout[l]); a.dz = dz; a.dzb = dzb;
                 a.carry0 = wsf(ws, h->ws.carry0v[l]); a.carry1 = wsf(ws, h->ws.carry1v[l]);
                 a.fill_t0 = ck > 0 ? wf_t0(h, ck - 1) : t0; a.fill_t1 = t0;
-                a.barrier = ws_barrier(ws, persist ? L * C + l * C : L * C + l * C + ck);
+                a.barrier = ws_barrier(ws, persist ? L * Cf + l * C : L * Cf + l * C + ck);
                 if (persist) {   // dy of chunk k (processing order) is there when the layer above's GEMM stream has written k + 1
                     a.pchunks = C; a.in_flag = l < L - 1 ? ws_pflag(ws, 1, l) : nullptr; a.out_flag = ws_pflag(ws, 1, l) + 32;
                 }
@@ -1519,7 +1536,7 @@ static int forward_backward_bf16(crnn_handle* h, const int32_t* x, const int32_t
                 if (rc != CRNN_OK) return rc;
             }
             if (persist) {                           // the chunk's dz rows: every CTA of the kernel has finished the chunk
-                rc = wf_wait_value(gs, ws_pflag(ws, 1, l) + 32, (unsigned)(C - ck) * nctas);
+                rc = wf_wait_value(gs, ws_pflag(ws, 1, l) + 32 + (C - 1 - ck), nctas);      // (counters are indexed in processing order)
                 if (rc != CRNN_OK) return rc;
             } else if (wf) {
                 rc = wf_record(h, wf_id(h, 2, l, ck), s);

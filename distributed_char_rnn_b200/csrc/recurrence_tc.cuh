@@ -74,8 +74,10 @@ struct RecTcArgs {
     // the layer wavefront.  Before the first step of chunk k (in processing order) the kernel waits until *in_flag >= k + 1 -
     // written by a stream memory operation that follows the chunk's batch GEMM (hoisted x-projection forward, input gradients
     // of the layer above backward) on a stream whose work was enqueued BEFORE this launch -, and after the last step of a
-    // chunk every CTA adds 1 to *out_flag, which the next layer's GEMM stream waits for (cuStreamWaitValue32).  No launch
-    // ever waits for work enqueued after it; the waits are bounded and report through `err`.
+    // chunk k every CTA adds 1 to out_flag[k] - one counter per chunk: batch tiles are independent chains and drift apart, a
+    // single sum over all chunks would reach "chunk k done" while some tile is still inside it -, which the next layer's GEMM
+    // stream waits for (cuStreamWaitValue32(out_flag + k, >= CTAs)).  No launch ever waits for work enqueued after it; the
+    // waits are bounded and report through `err`.
     int pchunks;
     const unsigned* in_flag;
     unsigned* out_flag;
@@ -1177,7 +1179,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_fwd_tc_kernel(const __grid_
             }
             if (a.pchunks && t + 1 == rt_chunk_t0(a.S, pck + 1, a.pchunks)) {   // the chunk is complete on this CTA (all its stores issued)
                 epi_bar_sync();
-                if (epi_tid == 0 && a.out_flag) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.out_flag) : "memory");
+                if (epi_tid == 0 && a.out_flag) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.out_flag + pck) : "memory");
                 ++pck;
             }
         }
@@ -1627,7 +1629,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) rec_bwd_tc_kernel(const __grid_
             }
             if (a.pchunks && t == rt_chunk_t0(a.S, a.pchunks - 1 - pck, a.pchunks)) {   // the chunk is complete on this CTA
                 epi_bar_sync();
-                if (epi_tid == 0 && a.out_flag) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.out_flag) : "memory");
+                if (epi_tid == 0 && a.out_flag) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.out_flag + pck) : "memory");
                 ++pck;
             }
         }

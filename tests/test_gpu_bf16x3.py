@@ -145,7 +145,8 @@ SHAPES = [
     # wavefront with one launch per layer and direction (chunk flags + stream memory operations; the default while the
     # recurrence CTAs take at most half of the SMs) forced on at config 3's layers, forced off at small ones, three layers
     ("gru", 512, 2, 12, 64, 96, {"CRNN_WF_PERSIST": 1}), ("lstm", 128, 2, 12, 50, 65, {"CRNN_WF_PERSIST": 0, "CRNN_WAVEFRONT_CHUNKS": 3}),
-    ("gru", 64, 3, 9, 20, 17, {"CRNN_WAVEFRONT_CHUNKS": 4}), ("rnn", 64, 2, 9, 21, 13, {"CRNN_WF_PERSIST": 1, "CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 9}),
+    ("gru", 64, 3, 9, 20, 17, {"CRNN_WAVEFRONT_CHUNKS": 4}), ("lstm", 64, 2, 24, 20, 17, {"CRNN_WAVEFRONT_CHUNKS": 3, "CRNN_WAVEFRONT_CHUNKS_BWD": 8}),
+    ("gru", 128, 2, 40, 130, 17, {"CRNN_WF_PERSIST": 2}),   # BPTT alone in the one-launch form, cut finer than the forward pass ("rnn", 64, 2, 9, 21, 13, {"CRNN_WF_PERSIST": 1, "CRNN_TC_CX": 0, "CRNN_WAVEFRONT_CHUNKS": 9}),
 ]
 
 
