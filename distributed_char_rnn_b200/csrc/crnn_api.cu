@@ -675,7 +675,7 @@ int crnn_create(const crnn_config* cfg, crnn_handle** out) {
     if (rc == CRNN_OK && h->tc && h->wf_W > 1 && h->wf_C > 1 && !h->tcp.gather && stream_value_fn(false) && stream_value_fn(true)) {
         const bool small = h->wf_W * h->tcp.nslices * h->tcp.ntiles * 2 <= h->sm_count;
         const int pe = env_int("CRNN_WF_PERSIST", small ? 1 : 2);          // 1: both directions, 2: BPTT only, 3: forward only
-        h->persist = pe == 1 ? 3 : (pe == 2 ? 2 : (pe == 3 ? 1 : 0));          // bit 0: forward, bit 1: BPTT
+        h->persist = pe == 1 ? 3 : (pe == 2 ? 2 : (pe == 3 ? 1 : (pe == 4 ? 6 : 0)));   // bit 0: forward, bit 1: BPTT, bit 2: forward, layer 0 only
         // Chunks cost no launch in this form, so BPTT of the large wavefronts is cut finer (less skew between the layers):
         // config 3, ms per step at 10 / 20 / 25 / 32 chunks: 4.16 / 4.13 / 4.09 / 4.15 (config 1 prefers its 5).
         if ((h->persist & 2) && !small && env_int("CRNN_WAVEFRONT_CHUNKS_BWD", 0) <= 0) {
@@ -1337,13 +1337,15 @@ static int run_forward_bf16(crnn_handle* h, const int32_t* x, int64_t ldx, const
                 if (c.model == CRNN_MODEL_GRU) CRNN_CUDA(cudaMemsetAsync(wsb(ws, h->ws.rsb[l]) + half * lo.act, 0xFF, n0 * sizeof(bf16_t), s));
             }
         }
-        const bool persist = wf && (h->persist & 1);
+        // (persist & 4: forward pass, layer 0 only - the first layer's launches are the forward pass's critical chain)
+        const bool persist = wf && ((h->persist & 1) || ((h->persist & 4) && l == 0));
+        const bool persist_below = wf && l > 0 && ((h->persist & 1) || ((h->persist & 4) && l == 1));
         const unsigned nctas = (unsigned)(h->tcp.nslices * h->tcp.ntiles);
         for (int ck = 0; ck < C; ++ck) {
             const int t0 = wf_t0(h, ck), t1 = wf_t0(h, ck + 1);
             const int rows = (t1 - t0) * B;
             if (wf && l > 0) {                       // layer l-1 has produced this chunk's inputs
-                rc = persist ? wf_wait_value(gs, ws_pflag(ws, 0, l - 1) + 32 + ck, nctas) : wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
+                rc = persist_below ? wf_wait_value(gs, ws_pflag(ws, 0, l - 1) + 32 + ck, nctas) : wf_wait(h, wf_id(h, 0, l - 1, ck), gs);
                 if (rc != CRNN_OK) return rc;
             }
             const bool hoisted = hoist0 && l == 0;   // done above for the whole sequence
