@@ -4,7 +4,7 @@
 // reverse-mode mirror (model.py:88-91): per time step only h_{t-1} * W_h (forward) or
 // dz_{t+1} * W_h^T (backward) remains once the x halves are hoisted into batch GEMMs.
 //
-// One cooperative launch per layer, direction and sequence chunk.  CTA (slice, tile) owns hidden units [j0, j0+HC) for batch rows [b0, b0+BT).
+// One launch per layer, direction and sequence chunk (or per layer and direction, see below).  CTA (slice, tile) owns hidden units [j0, j0+HC) for batch rows [b0, b0+BT).
 // Its slice of the recurrent weights is loaded by TMA ONCE into shared memory as a K-major, 128-byte-swizzled
 // UMMA operand and stays resident for all steps.  Per step and contraction:
 //   warp 0, one thread: waits (acquire polls) until every slice of the tile has released the previous step,
@@ -18,6 +18,14 @@
 //           and only then writes what no other CTA waits for (fp32 state, gate stash for BPTT).
 // CRNN_PREC_BF16X3 ("split"): every bf16 array has a lo twin; weights are resident as [hi ; lo] rows per K
 // block and each K step issues A_hi*[W_hi|W_lo] and A_lo*W_hi (see rt_mma).
+// Variants the planner (crnn_api.cu) chooses between, all in these two kernels:
+//   sub-chains      a tile's rows as two passes with their own step barrier, so one pass's exchange hides behind the other;
+//   K split         the contraction index over 2 / 4 CTAs of a cluster, partial sums through distributed shared memory;
+//   cluster exchange (xchg)  all slices of a tile in one cluster of <= 8: finished rows are written with st.async straight
+//                   into every slice's operand buffer, nothing of the step hand-shake touches L2 (cx_push, rt_mma_cx);
+//   one launch per layer (pchunks)  the launch covers the whole sequence and gates its chunks on flags that stream memory
+//                   operations of EARLIER-enqueued work write (RecTcArgs::pchunks);
+//   direct exchange (gather)  no step barrier, sentinel-filled slots checked in shared memory (opt-in, slower in situ).
 #pragma once
 #include "tc_common.cuh"
 
