@@ -249,15 +249,15 @@ inline bool env_splits_round_up() { static int v = -1; if (v < 0) { const char* 
 // Host launcher.  A: op(A) is [M,K]; a_mn = 0 -> stored [M,K] row-major (lda), a_mn = 1 -> stored
 // [K,M] row-major.  B: op(B) is [K,N]; b_mn = 0 -> stored [N,K] row-major (i.e. B^T), b_mn = 1 ->
 // stored [K,N] row-major.  accumulate = 1 adds into C (split-K with atomics when that fills the GPU).
-inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda, int a_mn,
+template <int BN, int STAGES>
+inline int gemm_bf16_tc_impl(int M, int N, int K, const __nv_bfloat16* A, int64_t lda, int a_mn,
                         const __nv_bfloat16* B, int64_t ldb, int b_mn, float* C, int64_t ldc,
-                        const float* bias, int accumulate, cudaStream_t st, int sm_count = 148,
-                        const __nv_bfloat16* A_lo = nullptr, const __nv_bfloat16* B_lo = nullptr) {
+                        const float* bias, int accumulate, cudaStream_t st, int sm_count,
+                        const __nv_bfloat16* A_lo, const __nv_bfloat16* B_lo) {
     if (M <= 0 || N <= 0) return CRNN_OK;
     if (K <= 0) return set_err(CRNN_ERR_ARG, "gemm_bf16_tc: K must be positive");
     if ((A_lo == nullptr) != (B_lo == nullptr)) return set_err(CRNN_ERR_ARG, "gemm_bf16_tc: both operands or neither must be split");
     const bool split = A_lo != nullptr;
-    constexpr int BN = 128, STAGES = 3;
     CUtensorMap tmA, tmB, tmAl, tmBl;
     int rc = a_mn ? make_tmap_bf16(&tmA, A, K, M, lda, 64) : make_tmap_bf16(&tmA, A, M, K, lda, GT_BM);
     if (rc != CRNN_OK) return rc;
@@ -293,21 +293,41 @@ inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda
     g.kblocks_per_split = ceil_div(total_kb, splits);
     grid.z = ceil_div(total_kb, g.kblocks_per_split);
     g.mode = accumulate ? (grid.z > 1 ? 2 : 1) : 0;
-    static bool attr_done[64] = {};                      // per device (function attributes are per context)
+    static bool attr_done[2][64] = {};                   // per variant and device (function attributes are per context)
     int dev = 0;
     CRNN_CUDA(cudaGetDevice(&dev));
-    bool& attr_set = attr_done[dev & 63];
-    if (!attr_set) {
-        CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       GemmTcSmem<BN, STAGES, false>::TOTAL));
-        CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       GemmTcSmem<BN, STAGES, true>::TOTAL));
+    bool& attr_set = attr_done[split ? 1 : 0][dev & 63];
+    if (!attr_set) {                                     // (only the variant that is launched: <256, 3, split> would not fit)
+        if (split) CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  GemmTcSmem<BN, STAGES, true>::TOTAL));
+        else       CRNN_CUDA(cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  GemmTcSmem<BN, STAGES, false>::TOTAL));
         attr_set = true;
     }
     if (split) gemm_bf16_tc_kernel<BN, STAGES, true><<<grid, GT_THREADS, GemmTcSmem<BN, STAGES, true>::TOTAL, st>>>(tmA, tmB, tmAl, tmBl, tmC, g);
     else       gemm_bf16_tc_kernel<BN, STAGES, false><<<grid, GT_THREADS, GemmTcSmem<BN, STAGES, false>::TOTAL, st>>>(tmA, tmB, tmAl, tmBl, tmC, g);
     CRNN_LAUNCH_CHECK("gemm_bf16_tc_kernel");
     return CRNN_OK;
+}
+
+inline int gemm_bf16_tc(int M, int N, int K, const __nv_bfloat16* A, int64_t lda, int a_mn,
+                        const __nv_bfloat16* B, int64_t ldb, int b_mn, float* C, int64_t ldc,
+                        const float* bias, int accumulate, cudaStream_t st, int sm_count = 148,
+                        const __nv_bfloat16* A_lo = nullptr, const __nv_bfloat16* B_lo = nullptr) {
+    // Split operands: a stage of the 128 x 128 tile (A hi+lo 32 KB, B hi+lo 32 KB) feeds twelve MMAs of 64 cycles - the TMA
+    // stream (64 KB per 768 tensor cycles) and the tensor pipe are then about level and the kernel reaches ~0.7 of the tensor
+    // peak; 128 x 256 tiles (96 KB per stage, twelve MMAs of 128 cycles, two stages) are tensor-bound.  CRNN_GEMM_BN256=0: off.
+    static const int bn256 = [] { const char* e = getenv("CRNN_GEMM_BN256"); return (e && *e == '0') ? 0 : 1; }();
+    // Only where the wider tiles still fill the GPU (measured, ms per step: config 5 113.8 -> 109.8 with them, config 3's chunk
+    // GEMMs - 80 tiles on the SMs the recurrence kernels leave - 4.09 -> 4.14, config 1 0.58 -> 0.62): at least two waves of
+    // tiles, or a long-K accumulating GEMM whose split K fills the rest.
+    const int64_t tiles256 = (int64_t)ceil_div(M, GT_BM) * (N / 256);
+    const bool big = tiles256 >= 2LL * sm_count || (accumulate && K >= 256 * GT_BK && tiles256 >= 64);
+    // (plain bf16 operands keep 128 x 128 with two CTAs per SM: 128 x 256 x 3 stages, one CTA per SM, measured slower -
+    //  config 4's x-projection 0.86 -> 1.14 ms, config 5's 4.19 -> 5.19)
+    if (A_lo != nullptr && bn256 && N >= 256 && N % 256 == 0 && big)
+        return gemm_bf16_tc_impl<256, 2>(M, N, K, A, lda, a_mn, B, ldb, b_mn, C, ldc, bias, accumulate, st, sm_count, A_lo, B_lo);
+    return gemm_bf16_tc_impl<128, 3>(M, N, K, A, lda, a_mn, B, ldb, b_mn, C, ldc, bias, accumulate, st, sm_count, A_lo, B_lo);
 }
 
 // fp32 -> bf16 cast of a row-major matrix (optionally re-pitched): the bf16 shadow copies.

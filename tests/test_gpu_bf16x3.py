@@ -37,6 +37,8 @@ GEMM_CASES = [
     (0, 0, 2560, 512, 1536, False, 0),    # config-3 input gradients
     (1, 1, 512, 1536, 5120, False, 1),    # config-3 weight gradients: split-K
     (1, 1, 72, 40, 1000, False, 1), (0, 1, 100, 96, 512, True, 0), (0, 0, 1, 8, 8, True, 0),
+    # shapes that take the 128 x 256 tiles (two waves of tiles / a long-K accumulating GEMM): all four operand layouts, ragged M
+    (0, 1, 4900, 2048, 192, True, 0), (0, 0, 4900, 2048, 192, False, 0), (1, 1, 1024, 2048, 16448, False, 1), (1, 0, 4900, 2048, 128, True, 0),
 ]
 
 
@@ -76,7 +78,8 @@ def test_gemm_split_operands_is_fp32_grade(lib, a_mn, b_mn, M, N, K, bias, acc):
     # per-product error ~3 * 2^-18; the sum of K of them against |a||b| ~ sqrt(K): 2e-5 of the largest entry is ample,
     # and two hundred times tighter than what plain bf16 operands give on the same data
     scale = max(np.abs(ref).max(), 1.0)
-    assert np.abs(got - ref).max() <= 2e-5 * scale
+    # (beyond K ~ 10^4 in ONE accumulator the tensor core's fp32 accumulate - it truncates - adds a drift of ~1e-9 per K step)
+    assert np.abs(got - ref).max() <= (2e-5 + 1e-9 * K) * scale
     plain = At.to(torch.bfloat16).double().cpu().numpy() @ Bt.to(torch.bfloat16).double().cpu().numpy()
     if K >= 64:
         assert np.abs(got - ref).max() < 0.02 * np.abs(plain + (b if bias else 0) + (C0 if acc else 0) - ref).max()
