@@ -226,6 +226,20 @@ print("ONE_STEP_OK", m.precision)
 """
 
 
+_ONE_STEP_WIDE = _ONE_STEP.replace('"lstm", 128, 2, 50, 50, 65', '"gru", 512, 2, 40, 96, 65').replace(
+    'model="lstm", rnn_size=128, num_layers=2, seq_length=50, batch_size=50', 'model="gru", rnn_size=512, num_layers=2, seq_length=40, batch_size=96').replace(
+    "(50, 50)", "(96, 40)")
+
+
+@pytest.mark.parametrize("env", [{"CUDA_LAUNCH_BLOCKING": "1"}, {"CUDA_DEVICE_MAX_CONNECTIONS": "1"}])
+def test_wide_layers_finish_when_launches_are_serialised(env):
+    """Config 3's layers (a launch per forward chunk, ONE BPTT launch per layer gated by chunk flags and stream memory
+    operations) with every launch serialised."""
+    r = subprocess.run([sys.executable, "-c", _ONE_STEP_WIDE % ROOT], capture_output=True, text=True, timeout=180,
+                       env=dict(os.environ, PYTHONPATH=ROOT, **env))
+    assert r.returncode == 0 and "ONE_STEP_OK bf16x3" in r.stdout, r.stderr[-2000:]
+
+
 @pytest.mark.parametrize("env", [{"CUDA_LAUNCH_BLOCKING": "1"}, {"CUDA_DEVICE_MAX_CONNECTIONS": "1"}])
 def test_step_finishes_when_launches_are_serialised(env):
     """Config 1 (the reference's default shape) with every launch serialised: no kernel of the step may wait for
